@@ -1,0 +1,1137 @@
+// Game rules of the B200-native MicroRTS simulator: the serial ("leader thread") part of one
+// environment step.  One thread group owns one game whose state is staged in shared memory;
+// the group's leader runs the functions below, the whole group runs the output phases in
+// mrts_encode.h.  Compiles for device and host (see mrts_types.h).
+//
+// What each function replaces in the reference (relative to /root/reference/,
+// J/ = gym_microrts/microrts/src/):
+//   unit_mask            Unit.getUnitActions                J/rts/units/Unit.java:368-522
+//                        + UnitAction.getValidActionArray   J/rts/UnitAction.java:717-757
+//   decode_actions       PlayerAction.fromVectorAction      J/rts/PlayerAction.java:384-417
+//                        + UnitAction.fromVectorAction      J/rts/UnitAction.java:681-715
+//                        + fillWithNones                    J/rts/PlayerAction.java:217-235
+//   issue_safe           GameState.issueSafe / issue        J/rts/GameState.java:338-408, 249-328
+//   cycle                GameState.cycle / UnitAction.execute  J/rts/GameState.java:553-571, J/rts/UnitAction.java:344-471
+//   make_views           PartiallyObservableGameState       J/rts/PartiallyObservableGameState.java:23-58
+//   step_game            JNIGridnetClient.gameStep / JNIGridnetClientSelfPlay.gameStep /
+//                        JNIGridnetVecClient.gameStep       J/tests/JNIGridnet*.java
+//   rewards              J/ai/reward/{WinLoss,ResourceGather,ProduceWorker,ProduceBuilding,Attack,ProduceCombatUnit}RewardFunction.java
+#pragma once
+#include <stddef.h>
+
+#include "mrts_types.h"
+
+namespace mrts {
+
+struct PAct {  // one entry of a PlayerAction (unit, UnitAction)
+    uint16_t unit;  // unit index
+    int8_t type;
+    int8_t utype;
+    int16_t param;
+    int16_t x, y;   // attack target (may be off-map before the legality rewrite)
+    int16_t pad;
+};
+
+// 78-bit legal-action set of one unit, in the mask layout of getValidActionArray:
+// [0..5] action types, [6..9] move dir, [10..13] harvest dir, [14..17] return dir,
+// [18..21] produce dir, [22..28] produce type, [29..77] attack offset (3+dy)*7+(3+dx).
+struct Mask78 {
+    uint32_t w[3];
+};
+enum { MB_TYPE = 0, MB_MOVE = 6, MB_HARVEST = 10, MB_RETURN = 14, MB_PDIR = 18, MB_PTYPE = 22, MB_ATTACK = 29 };
+MRTS_HD void mset(Mask78& m, int b) { m.w[b >> 5] |= 1u << (b & 31); }
+MRTS_HD bool mget(const Mask78& m, int b) { return (m.w[b >> 5] >> (b & 31)) & 1u; }
+
+struct Sim {
+    // ---- configuration
+    int W, H, HW, cap;
+    int none_mode, partial, max_steps;
+    int ai;         // scripted opponent of a bot game (AI_*), AI_NONE for a self-play game
+    // ---- state staged for this step
+    GameHdr* hdr;
+    Unit* u;
+    AbstractAct* aa;
+    uint16_t* grid;  // HW cells: unit index, G_NONE or G_WALL
+    // ---- leader scratch
+    PAct* pa;        // cap entries: PlayerAction being issued
+    int npa;
+    PAct* pa2;       // cap entries: the bot's PlayerAction
+    int npa2;
+    uint32_t* bitsA; // reservation bitmaps over linear positions -W .. HW+W-1 (bit index pos+W)
+    uint32_t* bitsB;
+    uint32_t* bitsC;
+    int nbits_words;
+    int16_t* astar;  // bot games: A* scratch, 5 arrays of (HW+1) int16 + HW bytes
+    // ---- per-step results
+    int rew[2][6];   // integer reward terms per player view (exact small integers)
+    int gameover, winner;
+
+    // ------------------------------------------------------------------ small helpers
+    MRTS_HD int nunits() const { return hdr->nunits; }
+    MRTS_HD bool alive(int i) const { return !(u[i].flags & UF_DEAD); }
+    // membership of unit i in the state the caller looks at: vp < 0 = the true state,
+    // vp = p = player p's partially observable view taken this step
+    MRTS_HD bool inview(int i, int vp) const { return vp < 0 || ((u[i].vis >> vp) & 1); }
+    MRTS_HD int unit_at(int x, int y) const {  // PhysicalGameState.getUnitAt; -1 = none
+        if (x < 0 || y < 0 || x >= W || y >= H) return -1;
+        uint16_t g = grid[x + y * W];
+        return g < G_WALL ? (int)g : -1;
+    }
+    MRTS_HD int unit_at_v(int x, int y, int vp) const {
+        int i = unit_at(x, y);
+        return (i >= 0 && inview(i, vp)) ? i : -1;
+    }
+    MRTS_HD bool wall_at(int x, int y) const { return grid[x + y * W] == G_WALL; }
+    MRTS_HD int eta(int ut, int type, int param, int prod) const {  // UnitAction.ETA, UnitAction.java:313-335
+        switch (type) {
+            case T_NONE: return param;
+            case T_MOVE: return ut_move_time(ut);
+            case T_ATTACK: return ut_attack_time(ut);
+            case T_HARVEST: return ut_harvest_time(ut);
+            case T_RETURN: return ut_move_time(ut);  // sic, UnitAction.java:327-328
+            case T_PRODUCE: return ut_produce_time(prod);
+        }
+        return 0;
+    }
+    MRTS_HD int none_param(int duration) const { return none_mode == NONE_FORK ? -1 : duration; }
+    // UnitAction.resourceUsage (UnitAction.java:252-302): linear target index for MOVE/PRODUCE, else -0x7fff
+    MRTS_HD int usage_pos(const Unit& un, int type, int param) const {
+        if (type != T_MOVE && type != T_PRODUCE) return -0x7fff;
+        int pos = un.x + un.y * W;
+        switch (param) {
+            case D_UP: pos -= W; break;
+            case D_RIGHT: pos++; break;
+            case D_DOWN: pos += W; break;
+            case D_LEFT: pos--; break;
+        }
+        return pos;
+    }
+    MRTS_HD void bits_clear(uint32_t* b) const {
+        for (int i = 0; i < nbits_words; i++) b[i] = 0;
+    }
+    MRTS_HD bool bit_get(const uint32_t* b, int pos) const {
+        int k = pos + W;
+        if (k < 0 || k >= nbits_words * 32) return false;
+        return (b[k >> 5] >> (k & 31)) & 1u;
+    }
+    MRTS_HD void bit_set(uint32_t* b, int pos) const {
+        int k = pos + W;
+        if (k < 0 || k >= nbits_words * 32) return;
+        b[k >> 5] |= 1u << (k & 31);
+    }
+
+    // ------------------------------------------------------------------ legal actions
+    // Unit.getUnitActions on the TRUE state, folded into the mask layout.  Legality of a
+    // concrete action (Unit.canExecuteAction, Unit.java:531-534) is a bit test on this set:
+    // getUnitActions emits the full product {affordable types} x {free directions} for
+    // PRODUCE, so (dir bit AND type bit) is exact.
+    MRTS_HD Mask78 unit_mask(int i) const {
+        Mask78 m;
+        m.w[0] = m.w[1] = m.w[2] = 0;
+        const Unit& un = u[i];
+        const int t = un.type, x = un.x, y = un.y, pl = un.player;
+        int nb[4];      // neighbour unit index or -1
+        bool inb[4];    // neighbour cell on the map
+        bool freec[4];  // on the map, no wall
+#pragma unroll
+        for (int d = 0; d < 4; d++) {
+            int nx = x + dir_dx(d), ny = y + dir_dy(d);
+            inb[d] = nx >= 0 && ny >= 0 && nx < W && ny < H;
+            uint16_t g = inb[d] ? grid[nx + ny * W] : (uint16_t)G_WALL;
+            nb[d] = g < G_WALL ? (int)g : -1;
+            freec[d] = inb[d] && g != G_WALL;
+        }
+        if (ut_can_attack(t)) {
+            if (ut_range(t) == 1) {
+#pragma unroll
+                for (int d = 0; d < 4; d++)
+                    if (nb[d] >= 0 && u[nb[d]].player != pl && u[nb[d]].player >= 0) {
+                        mset(m, MB_TYPE + T_ATTACK);
+                        mset(m, MB_ATTACK + (3 + dir_dy(d)) * 7 + 3 + dir_dx(d));
+                    }
+            } else {
+                const int r = ut_range(t), sq = r * r;
+                for (int dy = -r; dy <= r; dy++)
+                    for (int dx = -r; dx <= r; dx++) {
+                        if (dx * dx + dy * dy > sq) continue;
+                        int o = unit_at(x + dx, y + dy);
+                        if (o >= 0 && u[o].player >= 0 && u[o].player != pl) {
+                            mset(m, MB_TYPE + T_ATTACK);
+                            mset(m, MB_ATTACK + (3 + dy) * 7 + 3 + dx);
+                        }
+                    }
+            }
+        }
+        if (ut_can_harvest(t)) {
+#pragma unroll
+            for (int d = 0; d < 4; d++) {
+                if (nb[d] < 0) continue;
+                if (un.res == 0 && ut_is_resource(u[nb[d]].type)) {
+                    mset(m, MB_TYPE + T_HARVEST);
+                    mset(m, MB_HARVEST + d);
+                }
+                if (un.res > 0 && ut_is_stockpile(u[nb[d]].type) && u[nb[d]].player == pl) {
+                    mset(m, MB_TYPE + T_RETURN);
+                    mset(m, MB_RETURN + d);
+                }
+            }
+        }
+        const int prod = ut_produces(t);
+        if (prod && pl >= 0) {
+            int afford = 0;
+            for (int k = 1; k < N_UTYPES; k++)
+                if (((prod >> k) & 1) && hdr->res[pl] >= ut_cost(k)) afford |= 1 << k;
+            int dirs = 0;
+#pragma unroll
+            for (int d = 0; d < 4; d++)
+                if (freec[d] && nb[d] < 0) dirs |= 1 << d;
+            if (afford && dirs) {
+                mset(m, MB_TYPE + T_PRODUCE);
+                m.w[0] |= (uint32_t)dirs << MB_PDIR;
+                m.w[0] |= (uint32_t)afford << MB_PTYPE;
+            }
+        }
+        if (ut_can_move(t)) {
+#pragma unroll
+            for (int d = 0; d < 4; d++)
+                if (freec[d] && nb[d] < 0) {
+                    mset(m, MB_TYPE + T_MOVE);
+                    mset(m, MB_MOVE + d);
+                }
+        }
+        mset(m, MB_TYPE + T_NONE);
+        return m;
+    }
+
+    MRTS_HD bool can_execute(int i, const PAct& a) const {
+        if (a.type == T_NONE) return true;  // NONE(noneDuration = ETA(a)) is always in the list
+        Mask78 m = unit_mask(i);
+        const int p = a.param;
+        switch (a.type) {
+            case T_MOVE: return p >= 0 && p < 4 && mget(m, MB_MOVE + p);
+            case T_HARVEST: return p >= 0 && p < 4 && mget(m, MB_HARVEST + p);
+            case T_RETURN: return p >= 0 && p < 4 && mget(m, MB_RETURN + p);
+            case T_PRODUCE:
+                return p >= 0 && p < 4 && a.utype >= 0 && a.utype < N_UTYPES && mget(m, MB_PDIR + p) && mget(m, MB_PTYPE + a.utype);
+            case T_ATTACK: {
+                int dx = a.x - u[i].x, dy = a.y - u[i].y;
+                if (dx < -3 || dx > 3 || dy < -3 || dy > 3) return false;
+                return mget(m, MB_ATTACK + (3 + dy) * 7 + 3 + dx);
+            }
+        }
+        return false;
+    }
+
+    // ------------------------------------------------------------------ resource usage of pending assignments
+    // GameState.getResourceUsage / the base_ru loop of fromVectorAction (PlayerAction.java:387-394):
+    // positions into `bits`, costs into cost[2]; vp selects the state the caller sees.
+    MRTS_HD void pending_usage(uint32_t* bits, int* cost, int vp) const {
+        bits_clear(bits);
+        cost[0] = cost[1] = 0;
+        const int n = nunits();
+        for (int i = 0; i < n; i++) {
+            const Unit& un = u[i];
+            if (un.a_type != T_MOVE && un.a_type != T_PRODUCE) continue;
+            if (!inview(i, vp)) continue;
+            bit_set(bits, usage_pos(un, un.a_type, un.a_param));
+            if (un.a_type == T_PRODUCE) cost[un.player] += ut_cost(un.a_utype);
+        }
+    }
+    // ResourceUsage.consistentWith(other) for a single-action `other` against an accumulated base
+    // (ResourceUsage.java:31-50)
+    MRTS_HD bool consistent_single(const uint32_t* bits, const int* cost, int pos, int pl, int c) const {
+        if (pos != -0x7fff && bit_get(bits, pos)) return false;
+        if (c != 0) {
+            int s = cost[pl] + c;
+            if (s > 0 && s > hdr->res[pl]) return false;
+        }
+        return true;
+    }
+
+    // ------------------------------------------------------------------ fromVectorAction + fillWithNones
+    // `actions` = this player view's (HW,7) block.  The reference visits the cells flagged by the
+    // previous get_action_mask in ascending index (vec_env.py:974) and Java keeps a cell iff it
+    // holds an idle unit of the player; both reduce to "own idle units in ascending cell order".
+    MRTS_HD void decode_actions(int player, const int32_t* actions, int vp) {
+        int cost[2];
+        pending_usage(bitsA, cost, vp);
+        npa = 0;
+        const int n = nunits();
+        // own idle units sorted by cell index (insertion sort over the handful of candidates)
+        for (int i = 0; i < n; i++) {
+            const Unit& un = u[i];
+            if (un.player != player || un.a_type >= 0 || !inview(i, vp)) continue;
+            int pos = un.x + un.y * W;
+            int k = npa++;
+            while (k > 0 && (u[pa[k - 1].unit].x + u[pa[k - 1].unit].y * W) > pos) {
+                pa[k] = pa[k - 1];
+                k--;
+            }
+            pa[k].unit = (uint16_t)i;
+        }
+        int kept = 0;
+        for (int k = 0; k < npa; k++) {
+            const int i = pa[k].unit;
+            const Unit& un = u[i];
+            const int32_t* a = actions + (size_t)(un.x + un.y * W) * 7;
+            PAct e;
+            e.unit = (uint16_t)i;
+            e.type = (int8_t)a[0];
+            e.param = -1;  // DIRECTION_NONE, UnitAction.java:114
+            e.utype = -1;
+            e.x = e.y = 0;
+            e.pad = 0;
+            switch (a[0]) {
+                case T_NONE: break;
+                case T_MOVE: e.param = (int16_t)a[1]; break;
+                case T_HARVEST: e.param = (int16_t)a[2]; break;
+                case T_RETURN: e.param = (int16_t)a[3]; break;
+                case T_PRODUCE:
+                    e.param = (int16_t)a[4];
+                    e.utype = (int8_t)a[5];
+                    break;
+                case T_ATTACK:
+                    e.x = (int16_t)(un.x + (a[6] % 7 - 3));
+                    e.y = (int16_t)(un.y + (a[6] / 7 - 3));
+                    break;
+                default: e.type = T_NONE; break;  // out-of-range type: treated as a no-op
+            }
+            if (e.type == T_PRODUCE && (e.utype < 0 || e.utype >= N_UTYPES)) {  // utt.getUnitType would throw
+                e.type = T_NONE;
+                e.param = -1;
+                e.utype = -1;
+            }
+            const int pos = usage_pos(un, e.type, e.param);
+            const int c = e.type == T_PRODUCE ? ut_cost(e.utype) : 0;
+            if (consistent_single(bitsA, cost, pos, player, c)) {
+                if (pos != -0x7fff) bit_set(bitsA, pos);
+                cost[player] += c;
+                pa[kept++] = e;  // kept <= k: never overwrites an unread candidate
+            }
+        }
+        npa = kept;
+        fill_with_nones(pa, npa, player, 1, vp);
+    }
+
+    // PlayerAction.fillWithNones: idle own units not yet in the action, in unit order
+    MRTS_HD void fill_with_nones(PAct* list, int& cnt, int player, int duration, int vp) {
+        const int n = nunits();
+        const int have = cnt;
+        for (int i = 0; i < n; i++) {
+            const Unit& un = u[i];
+            if (un.player != player || un.a_type >= 0 || !inview(i, vp)) continue;
+            bool found = false;
+            for (int k = 0; k < have; k++)
+                if (list[k].unit == i) {
+                    found = true;
+                    break;
+                }
+            if (found) continue;
+            PAct e;
+            e.unit = (uint16_t)i;
+            e.type = T_NONE;
+            e.param = (int16_t)none_param(duration);
+            e.utype = -1;
+            e.x = e.y = 0;
+            e.pad = 0;
+            list[cnt++] = e;
+        }
+    }
+
+    // ------------------------------------------------------------------ issueSafe + issue
+    MRTS_HD void reward_for_issued(const PAct& a) {
+        const Unit& un = u[a.unit];
+        const int p = un.player;
+        if (p < 0) return;
+        if (a.type == T_HARVEST || a.type == T_RETURN) rew[p][1] += 1;  // ResourceGatherRewardFunction.java:22-31
+        if (a.type == T_PRODUCE && a.utype >= 0) {
+            if (a.utype == UT_WORKER) rew[p][2] += 1;                                      // ProduceWorker :20-30
+            if (a.utype == UT_BASE || a.utype == UT_BARRACKS) rew[p][3] += 1;              // ProduceBuilding :20-30
+            if (a.utype == UT_LIGHT || a.utype == UT_HEAVY || a.utype == UT_RANGED) rew[p][5] += 1;  // ProduceCombatUnit
+        }
+        if (a.type == T_ATTACK) {  // AttackRewardFunction.java:20-36: occupant of the target cell in the pre-cycle snapshot
+            int o = unit_at(a.x, a.y);
+            if (o >= 0) {
+                if (u[o].player == 1 - p) rew[p][4] += 1;
+                else if (u[o].player == p) rew[p][4] -= 1;
+            }
+        }
+    }
+
+    MRTS_HD void issue_safe(PAct* list, int cnt) {
+        const int time = hdr->time;
+        for (int k = 0; k < cnt; k++) {
+            PAct a = list[k];
+            Unit& un = u[a.unit];
+            // ---- legality rewrite (GameState.java:347-354); mutates the PlayerAction
+            if (!can_execute(a.unit, a)) {
+                int l = eta(un.type, a.type, a.param, a.utype >= 0 ? a.utype : 0);
+                a.type = T_NONE;
+                a.param = (int16_t)none_param(l);
+                a.utype = -1;
+            }
+            // (second check of GameState.java:384-400 -- target wall/occupied -- is implied by legality)
+            // ---- issue (GameState.java:249-328)
+            int8_t ctype = a.type;        // the local `p` that CANCEL_BOTH rebinds
+            int16_t cparam = a.param;
+            int8_t cutype = a.utype;
+            bool mutated = false;         // GameState.java:316 mutates the Pair itself
+            const int pos = usage_pos(un, a.type, a.param);
+            if (pos != -0x7fff) {
+                const int c = a.type == T_PRODUCE ? ut_cost(a.utype) : 0;
+                const int pl = un.player;
+                const int n = nunits();
+                // quick scan: any conflicting assignment at all?
+                bool any = false;
+                for (int j = 0; j < n && !any; j++) any = conflicts(j, pos, pl, c);
+                if (any) {
+                    // slow path, in issue order (LinkedHashMap iteration)
+                    uint32_t last = 0;
+                    bool first = true;
+                    for (;;) {
+                        int best = -1;
+                        uint32_t bs = 0xFFFFFFFFu;
+                        for (int j = 0; j < n; j++) {
+                            if (u[j].a_type < 0) continue;
+                            if (!first && u[j].a_seq <= last) continue;
+                            if (u[j].a_seq < bs) {
+                                bs = u[j].a_seq;
+                                best = j;
+                            }
+                        }
+                        if (best < 0) break;
+                        first = false;
+                        last = bs;
+                        if (!conflicts(best, pos, pl, c)) continue;
+                        Unit& ou = u[best];
+                        if (ou.a_time == time) {
+                            int d1 = eta(ou.type, ou.a_type, ou.a_param, ou.a_utype >= 0 ? ou.a_utype : 0);
+                            int d2 = eta(un.type, ctype, cparam, cutype >= 0 ? cutype : 0);
+                            int mn = d1 < d2 ? d1 : d2;
+                            ou.a_type = T_NONE;  // slot (a_seq) and a_time kept, GameState.java:292
+                            ou.a_param = (int16_t)none_param(mn);
+                            ou.a_utype = -1;
+                            for (int v = 0; v < 2; v++)
+                                if (ou.vtype[v] >= 0) ou.vtype[v] = T_NONE;  // views share the assignment object
+                            ctype = T_NONE;
+                            cparam = (int16_t)none_param(mn);
+                            cutype = -1;
+                        } else {
+                            ctype = T_NONE;  // new UnitAction(TYPE_NONE): parameter -1
+                            cparam = -1;
+                            cutype = -1;
+                            mutated = true;
+                        }
+                    }
+                }
+            }
+            if (mutated) {
+                a.type = T_NONE;
+                a.param = -1;
+                a.utype = -1;
+            }
+            reward_for_issued(a);  // rewards see the PlayerAction as left by issueSafe
+            un.a_type = ctype;
+            un.a_param = cparam;
+            un.a_utype = cutype;
+            un.a_x = (uint8_t)a.x;
+            un.a_y = (uint8_t)a.y;
+            un.a_time = time;
+            un.a_seq = hdr->next_seq++;
+        }
+    }
+    // !consistent(usage(assignment of unit j), ru) with ru = {pos, cost c of player pl}
+    MRTS_HD bool conflicts(int j, int pos, int pl, int c) const {
+        const Unit& ou = u[j];
+        if (ou.a_type != T_MOVE && ou.a_type != T_PRODUCE) return false;
+        if (usage_pos(ou, ou.a_type, ou.a_param) == pos) return true;
+        if (c != 0) {
+            int oc = (ou.a_type == T_PRODUCE && ou.player == pl) ? ut_cost(ou.a_utype) : 0;
+            int s = oc + c;
+            if (s > 0 && s > hdr->res[pl]) return true;
+        }
+        return false;
+    }
+
+    // ------------------------------------------------------------------ cycle
+    MRTS_HD void kill_unit(int o) {  // GameState.removeUnit: unit and its assignment leave the state
+        Unit& ou = u[o];
+        ou.flags |= UF_DEAD;  // the record (incl. a collected action) stays until compact()
+        grid[ou.x + ou.y * W] = G_NONE;
+    }
+    MRTS_HD void execute(int i, int type, int param, int ax, int ay, int prod) {
+        Unit& un = u[i];
+        const bool dead = un.flags & UF_DEAD;  // removed earlier this cycle: still executes (ready list is a snapshot)
+        switch (type) {
+            case T_MOVE: {
+                if (!dead) grid[un.x + un.y * W] = G_NONE;
+                un.x = (uint8_t)(un.x + dir_dx(param));
+                un.y = (uint8_t)(un.y + dir_dy(param));
+                if (!dead) grid[un.x + un.y * W] = (uint16_t)i;
+                break;
+            }
+            case T_ATTACK: {
+                int o = unit_at(ax, ay);
+                if (o >= 0) {
+                    u[o].hp = (int16_t)(u[o].hp - ut_damage(un.type));
+                    if (u[o].hp <= 0) kill_unit(o);
+                }
+                break;
+            }
+            case T_HARVEST: {
+                int o = (param >= 0 && param < 4) ? unit_at(un.x + dir_dx(param), un.y + dir_dy(param)) : -1;
+                if (o >= 0 && ut_is_resource(u[o].type) && ut_can_harvest(un.type) && un.res == 0) {
+                    u[o].res -= 1;  // harvestAmount
+                    if (u[o].res <= 0) kill_unit(o);
+                    un.res = 1;
+                }
+                break;
+            }
+            case T_RETURN: {
+                int o = (param >= 0 && param < 4) ? unit_at(un.x + dir_dx(param), un.y + dir_dy(param)) : -1;
+                if (o >= 0 && ut_is_stockpile(u[o].type) && un.res > 0) {  // owner NOT checked, UnitAction.java:430
+                    hdr->res[un.player] += un.res;
+                    un.res = 0;
+                }
+                break;
+            }
+            case T_PRODUCE: {
+                int tx = un.x + dir_dx(param), ty = un.y + dir_dy(param);
+                if (hdr->res[un.player] - ut_cost(prod) >= 0 && hdr->nunits < cap) {
+                    int k = hdr->nunits++;
+                    Unit& nu = u[k];
+                    nu.x = (uint8_t)tx;
+                    nu.y = (uint8_t)ty;
+                    nu.type = (uint8_t)prod;
+                    nu.player = un.player;
+                    nu.hp = (int16_t)ut_hp(prod);
+                    nu.res = 0;
+                    nu.a_type = -1;
+                    nu.a_param = -1;
+                    nu.a_utype = -1;
+                    nu.a_x = nu.a_y = 0;
+                    nu.a_time = 0;
+                    nu.a_seq = 0;
+                    nu.uid = hdr->next_uid++;
+                    nu.flags = 0;
+                    nu.vis = 0;  // born after the views were taken
+                    nu.vtype[0] = nu.vtype[1] = -1;
+                    nu.pad[0] = nu.pad[1] = 0;
+                    grid[tx + ty * W] = (uint16_t)k;
+                    hdr->res[un.player] -= ut_cost(prod);
+                }
+                break;
+            }
+        }
+    }
+
+    // GameState.cycle.  Dead units stay in the array (flagged) until compact().
+    MRTS_HD void cycle() {
+        hdr->time++;
+        const int time = hdr->time;
+        const int n = nunits();  // units born this cycle have no assignment
+        // ready non-NONE assignments, sorted by issue order; NONEs just vanish (no effect)
+        int nr = 0;
+        uint16_t* ready = (uint16_t*)pa;  // pa is free again
+        for (int i = 0; i < n; i++) {
+            Unit& un = u[i];
+            if (un.a_type < 0) continue;
+            int e = eta(un.type, un.a_type, un.a_param, un.a_utype >= 0 ? un.a_utype : 0);
+            if (e + un.a_time > time) continue;
+            if (un.a_type == T_NONE) {
+                un.a_type = -1;
+                continue;
+            }
+            int k = nr++;
+            while (k > 0 && u[ready[k - 1]].a_seq > un.a_seq) {
+                ready[k] = ready[k - 1];
+                k--;
+            }
+            ready[k] = (uint16_t)i;
+        }
+        for (int k = 0; k < nr; k++) {
+            const int i = ready[k];
+            Unit& un = u[i];
+            // a unit killed earlier this cycle lost its map entry but still executes the collected action
+            const int type = un.a_type, param = un.a_param, ax = un.a_x, ay = un.a_y, prod = un.a_utype;
+            un.a_type = -1;
+            execute(i, type, param, ax, ay, prod);
+        }
+    }
+
+    // stable compaction after cycle (PhysicalGameState.removeUnit keeps relative order) + grid fix-up
+    MRTS_HD void compact() {
+        const int n = nunits();
+        int k = 0;
+        for (int i = 0; i < n; i++) {
+            if (u[i].flags & UF_DEAD) continue;
+            if (k != i) {
+                u[k] = u[i];
+                grid[u[k].x + u[k].y * W] = (uint16_t)k;
+            }
+            k++;
+        }
+        hdr->nunits = k;
+    }
+
+    // PhysicalGameState.gameover / winner (PhysicalGameState.java:319-372) over live units
+    MRTS_HD void eval_gameover() {
+        int cnt[2] = {0, 0};
+        const int n = nunits();
+        for (int i = 0; i < n; i++)
+            if (alive(i) && u[i].player >= 0) cnt[u[i].player]++;
+        if (cnt[0] + cnt[1] == 0) {
+            gameover = 1;
+            winner = -1;
+        } else if (cnt[0] > 0 && cnt[1] > 0) {
+            gameover = 0;
+            winner = -1;
+        } else {
+            gameover = 1;
+            winner = cnt[0] > 0 ? 0 : 1;
+        }
+    }
+
+    // PartiallyObservableGameState(gs, p): membership + assignment copy, recorded per unit
+    MRTS_HD void make_view(int p) {
+        const int n = nunits();
+        for (int i = 0; i < n; i++) {
+            Unit& un = u[i];
+            bool in = un.player == p;
+            if (!in) {
+                for (int j = 0; j < n && !in; j++) {
+                    const Unit& w = u[j];
+                    if (w.player != p) continue;
+                    int dx = w.x - un.x, dy = w.y - un.y, r = ut_sight(w.type);
+                    in = dx * dx + dy * dy <= r * r;  // sqrt(d2) <= r, exact on integers
+                }
+            }
+            if (in) {
+                un.vis |= (uint8_t)(1 << p);
+                un.vtype[p] = un.a_type;
+            } else {
+                un.vis &= (uint8_t)~(1 << p);
+                un.vtype[p] = -1;
+            }
+        }
+    }
+
+    // ================================================================== scripted opponents
+    // AbstractionLayerAI table helpers (J/ai/abstraction/AbstractionLayerAI.java:36,115-141)
+    MRTS_HD int aa_find(uint16_t uid) const {
+        for (int k = 0; k < hdr->n_aa; k++)
+            if (aa[k].unit == uid) return k;
+        return -1;
+    }
+    MRTS_HD void aa_put(const AbstractAct& r) {  // LinkedHashMap.put: re-put keeps the slot
+        int k = aa_find(r.unit);
+        if (k < 0) {
+            if (hdr->n_aa >= cap) return;
+            k = hdr->n_aa++;
+        }
+        aa[k] = r;
+    }
+    MRTS_HD int find_uid(uint16_t uid, int vp) const {  // pgs.getUnits().contains(u) on the view
+        if (uid == NO_UID) return -1;
+        const int n = nunits();
+        for (int i = 0; i < n; i++)
+            if (u[i].uid == uid) return inview(i, vp) ? i : -1;
+        return -1;
+    }
+    MRTS_HD static int iabs(int v) { return v < 0 ? -v : v; }
+
+    // gs.free(x,y) on the bot's view, J/rts/GameState.java:191-207; bitsB = pending MOVE/PRODUCE targets
+    MRTS_HD bool free_cell(int x, int y, int vp) const {
+        const int pos = x + y * W;
+        uint16_t g = grid[pos];
+        if (g == G_WALL) return false;
+        if (g != G_NONE && inview(g, vp)) return false;
+        return !bit_get(bitsB, pos);
+    }
+    // GameState.isUnitActionAllowed, J/rts/GameState.java:434-457 (argument order of consistentWith kept)
+    MRTS_HD bool action_allowed(int i, int type, int param, int prod, int vp, const int* costB) const {
+        const Unit& un = u[i];
+        if (type == T_MOVE) {
+            int x2 = un.x + dir_dx(param), y2 = un.y + dir_dy(param);
+            if (x2 < 0 || y2 < 0 || x2 >= W || y2 >= H) return false;
+            if (wall_at(x2, y2) || unit_at_v(x2, y2, vp) >= 0) return false;
+        }
+        const int pos = usage_pos(un, type, param);
+        if (pos != -0x7fff && bit_get(bitsB, pos)) return false;
+        for (int p = 0; p < 2; p++) {
+            if (costB[p] == 0) continue;
+            int s = ((type == T_PRODUCE && un.player == p) ? ut_cost(prod) : 0) + costB[p];
+            if (s > 0 && s > hdr->res[p]) return false;
+        }
+        return true;
+    }
+
+    // ---- A*, J/ai/abstraction/pathfinding/AStarPathFinding.java:52-79,104-138,175-295
+    struct AStarBuf {
+        int16_t *open, *heur, *parents, *cost, *closed;
+        uint8_t* inoc;
+        int openinsert;
+    };
+    MRTS_HD AStarBuf astar_buf() const {
+        AStarBuf b;
+        b.open = astar;
+        b.heur = b.open + (HW + 1);
+        b.parents = b.heur + (HW + 1);
+        b.cost = b.parents + (HW + 1);
+        b.closed = b.cost + (HW + 1);
+        b.inoc = (uint8_t*)(b.closed + (HW + 1));
+        b.openinsert = 0;
+        return b;
+    }
+    MRTS_HD static void astar_add(AStarBuf& b, int newPos, int oldPos, int h) {
+        b.cost[newPos] = (int16_t)(b.cost[oldPos] + 1);
+        const int f = h + b.cost[newPos];
+        int i = b.openinsert - 1;
+        while (i >= 0 && b.heur[i] + b.cost[b.open[i]] < f) i--;  // first i from the tail with f_i >= f_new
+        for (int j = b.openinsert; j > i + 1; j--) {
+            b.open[j] = b.open[j - 1];
+            b.heur[j] = b.heur[j - 1];
+            b.parents[j] = b.parents[j - 1];
+        }
+        b.open[i + 1] = (int16_t)newPos;
+        b.heur[i + 1] = (int16_t)h;
+        b.parents[i + 1] = (int16_t)oldPos;
+        b.openinsert++;
+        b.inoc[newPos] = 1;
+    }
+    // findPathToPositionInRange: direction of the first move, or -1 (null)
+    MRTS_HD int astar_first_move(int i, int targetpos, int range, int vp) {
+        AStarBuf b = astar_buf();
+        const Unit& st = u[i];
+        for (int k = 0; k < HW; k++) {
+            b.closed[k] = -1;
+            b.inoc[k] = 0;
+        }
+        const int tx = targetpos % W, ty = targetpos / W;
+        const int sq = range * range;
+        const int startPos = st.y * W + st.x;
+        b.open[0] = (int16_t)startPos;
+        b.heur[0] = (int16_t)(iabs(st.x - tx) + iabs(st.y - ty));
+        b.parents[0] = (int16_t)startPos;
+        b.inoc[startPos] = 1;
+        b.cost[startPos] = 0;
+        b.openinsert = 1;
+        bool found = false;
+        int pos = 0, parent = 0;
+        while (b.openinsert > 0) {
+            b.openinsert--;
+            pos = b.open[b.openinsert];
+            parent = b.parents[b.openinsert];
+            if (b.closed[pos] != -1) continue;
+            b.closed[pos] = (int16_t)parent;
+            const int x = pos % W, y = pos / W;
+            if ((x - tx) * (x - tx) + (y - ty) * (y - ty) <= sq) {
+                found = true;
+                break;
+            }
+            // free(nbr) = gs.free() unless pre-seeded false by `ru` (bitsC); no need to cache: both are constant here
+            if (y > 0 && !b.inoc[pos - W] && free_cell(x, y - 1, vp) && !bit_get(bitsC, pos - W)) astar_add(b, pos - W, pos, iabs(x - tx) + iabs(y - 1 - ty));
+            if (x < W - 1 && !b.inoc[pos + 1] && free_cell(x + 1, y, vp) && !bit_get(bitsC, pos + 1)) astar_add(b, pos + 1, pos, iabs(x + 1 - tx) + iabs(y - ty));
+            if (y < H - 1 && !b.inoc[pos + W] && free_cell(x, y + 1, vp) && !bit_get(bitsC, pos + W)) astar_add(b, pos + W, pos, iabs(x - tx) + iabs(y + 1 - ty));
+            if (x > 0 && !b.inoc[pos - 1] && free_cell(x - 1, y, vp) && !bit_get(bitsC, pos - 1)) astar_add(b, pos - 1, pos, iabs(x - 1 - tx) + iabs(y - ty));
+        }
+        if (!found) return -1;
+        int last = pos;
+        while (parent != pos) {
+            last = pos;
+            pos = parent;
+            parent = b.closed[pos];
+        }
+        if (last == pos + W) return D_DOWN;
+        if (last == pos - 1) return D_LEFT;
+        if (last == pos - W) return D_UP;
+        if (last == pos + 1) return D_RIGHT;
+        return -1;
+    }
+
+    // Train.score, J/ai/abstraction/Train.java:98-127
+    MRTS_HD int train_score(int x, int y, int ut, int player, int vp) const {
+        int distance = 0;
+        bool first = true;
+        const int n = nunits();
+        const bool harv = ut_can_harvest(ut);
+        for (int i = 0; i < n; i++) {
+            if (!inview(i, vp)) continue;
+            const Unit& o = u[i];
+            bool cand = harv ? ut_is_resource(o.type) : (o.player >= 0 && o.player != player);
+            if (!cand) continue;
+            int d = iabs(o.x - x) + iabs(o.y - y);
+            if (first || d < distance) {
+                distance = d;
+                first = false;
+            }
+        }
+        return -distance;
+    }
+
+    // AbstractAction.execute: true + primitive action in `out`, or false (null)
+    MRTS_HD bool aa_execute(AbstractAct& r, int i, int vp, const int* costB, PAct& out) {
+        const Unit& un = u[i];
+        out.unit = (uint16_t)i;
+        out.utype = -1;
+        out.param = -1;
+        out.x = out.y = 0;
+        out.pad = 0;
+        switch (r.kind) {
+            case AA_TRAIN: {  // Train.java:48-96
+                const int x = un.x, y = un.y;
+                int best_dir = -1, best_score = -1;
+                for (int d = 0; d < 4; d++) {
+                    int nx = x + dir_dx(d), ny = y + dir_dy(d);
+                    if (nx < 0 || ny < 0 || nx >= W || ny >= H) continue;
+                    if (!free_cell(nx, ny, vp)) continue;
+                    int score = train_score(nx, ny, r.utype, un.player, vp);
+                    if (score > best_score || best_dir == -1) {
+                        best_score = score;
+                        best_dir = d;
+                    }
+                }
+                r.target = 1;  // completed = true
+                if (best_dir != -1 && action_allowed(i, T_PRODUCE, best_dir, r.utype, vp, costB)) {
+                    out.type = T_PRODUCE;
+                    out.param = (int16_t)best_dir;
+                    out.utype = r.utype;
+                    return true;
+                }
+                return false;
+            }
+            case AA_BUILD: {  // Build.java:56-78
+                int mv = astar_first_move(i, r.x + r.y * W, 1, vp);
+                if (mv >= 0) {
+                    if (action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
+                        out.type = T_MOVE;
+                        out.param = (int16_t)mv;
+                        return true;
+                    }
+                    return false;
+                }
+                int d = -1;
+                if (r.x == un.x && r.y == un.y - 1) d = D_UP;
+                if (r.x == un.x + 1 && r.y == un.y) d = D_RIGHT;
+                if (r.x == un.x && r.y == un.y + 1) d = D_DOWN;
+                if (r.x == un.x - 1 && r.y == un.y) d = D_LEFT;
+                if (d >= 0 && action_allowed(i, T_PRODUCE, d, r.utype, vp, costB)) {
+                    out.type = T_PRODUCE;
+                    out.param = (int16_t)d;
+                    out.utype = r.utype;
+                    return true;
+                }
+                return false;
+            }
+            case AA_HARVEST: {  // Harvest.java:71-114
+                const bool carrying = un.res != 0;
+                int ti = find_uid(carrying ? r.base : r.target, vp);
+                if (ti < 0) return false;
+                const Unit& tg = u[ti];
+                int mv = astar_first_move(i, tg.x + tg.y * W, 1, vp);
+                if (mv >= 0) {
+                    if (action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
+                        out.type = T_MOVE;
+                        out.param = (int16_t)mv;
+                        return true;
+                    }
+                    return false;
+                }
+                int d = -1;
+                if (tg.x == un.x && tg.y == un.y - 1) d = D_UP;
+                else if (tg.x == un.x + 1 && tg.y == un.y) d = D_RIGHT;
+                else if (tg.x == un.x && tg.y == un.y + 1) d = D_DOWN;
+                else if (tg.x == un.x - 1 && tg.y == un.y) d = D_LEFT;
+                if (d < 0) return false;
+                out.type = carrying ? T_RETURN : T_HARVEST;
+                out.param = (int16_t)d;
+                return true;
+            }
+            case AA_ATTACK: {  // Attack.java:50-65
+                int ti = find_uid(r.target, vp);
+                if (ti < 0) return false;
+                const Unit& tg = u[ti];
+                int dx = tg.x - un.x, dy = tg.y - un.y;
+                int rg = ut_range(un.type);
+                if (dx * dx + dy * dy <= rg * rg) {
+                    out.type = T_ATTACK;
+                    out.x = tg.x;
+                    out.y = tg.y;
+                    return true;
+                }
+                int mv = astar_first_move(i, tg.x + tg.y * W, rg, vp);
+                if (mv >= 0 && action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
+                    out.type = T_MOVE;
+                    out.param = (int16_t)mv;
+                    return true;
+                }
+                return false;
+            }
+        }
+        return false;
+    }
+
+    MRTS_HD bool aa_completed(const AbstractAct& r, int i, int vp) const {
+        switch (r.kind) {
+            case AA_TRAIN: return r.target != 0;                                   // Train.java:30-32
+            case AA_BUILD: return unit_at_v(r.x, r.y, vp) >= 0;                    // Build.java:33-37
+            case AA_HARVEST:                                                       // Harvest.java:42-48
+                if (u[i].res > 0) return find_uid(r.base, vp) < 0;
+                return find_uid(r.target, vp) < 0;
+            case AA_ATTACK: return find_uid(r.target, vp) < 0;                     // Attack.java:30-33
+        }
+        return true;
+    }
+
+    // AbstractionLayerAI.translateActions, AbstractionLayerAI.java:58-113 -> pa2
+    MRTS_HD void translate_actions(int player, int vp) {
+        int costB[2], costA[2], costC[2] = {0, 0};
+        pending_usage(bitsB, costB, vp);
+        bits_clear(bitsC);
+        npa2 = 0;
+        int na = hdr->n_aa, keep = 0;
+        for (int k = 0; k < na; k++) {
+            AbstractAct r = aa[k];
+            int i = find_uid(r.unit, vp);
+            bool del = false;
+            if (i < 0) del = true;
+            else if (aa_completed(r, i, vp)) del = true;
+            else if (u[i].a_type < 0) {
+                PAct out;
+                if (aa_execute(r, i, vp, costB, out)) {
+                    pa2[npa2++] = out;
+                    int pos = usage_pos(u[i], out.type, out.param);
+                    if (pos != -0x7fff) bit_set(bitsC, pos);
+                    if (out.type == T_PRODUCE) costC[u[i].player] += ut_cost(out.utype);
+                }
+            }
+            if (!del) aa[keep++] = r;  // r may carry Train's completed flag
+        }
+        hdr->n_aa = (uint16_t)keep;
+        (void)costC;
+        // accept desires first-come-first-served against the pending usage
+        for (int w = 0; w < nbits_words; w++) bitsA[w] = bitsB[w];
+        costA[0] = costB[0];
+        costA[1] = costB[1];
+        int kept = 0;
+        for (int k = 0; k < npa2; k++) {
+            PAct d = pa2[k];
+            const Unit& un = u[d.unit];
+            int pos = usage_pos(un, d.type, d.param);
+            int c = d.type == T_PRODUCE ? ut_cost(d.utype) : 0;
+            if (consistent_single(bitsA, costA, pos, un.player, c)) {
+                if (pos != -0x7fff) bit_set(bitsA, pos);
+                costA[un.player] += c;
+                pa2[kept++] = d;
+            }
+        }
+        npa2 = kept;
+        fill_with_nones(pa2, npa2, player, 10, vp);
+    }
+
+    // AbstractionLayerAI.findBuildingPosition, AbstractionLayerAI.java:143-228 (reserved list is empty for WorkerRush)
+    MRTS_HD int find_building_position(int dX, int dY, int vp) const {
+        const int mx = H > W ? H : W;
+        for (int l = 1; l < mx; l++) {
+            for (int side = 0; side < 4; side++) {
+                const bool horiz = (side == 0 || side == 2);
+                const int fixed = side == 0 ? dY - l : side == 1 ? dX + l : side == 2 ? dY + l : dX - l;
+                if (fixed < 0 || fixed >= (horiz ? H : W)) continue;
+                for (int dd = -l; dd <= l; dd++) {
+                    int x = horiz ? dX + dd : fixed;
+                    int y = horiz ? fixed : dY + dd;
+                    if (x < 0 || y < 0 || x >= W || y >= H) continue;
+                    if (!wall_at(x, y) && unit_at_v(x, y, vp) < 0) return x + y * W;
+                }
+            }
+        }
+        return -1;
+    }
+
+    MRTS_HD void bot_melee(int i, int player, int vp) {  // WorkerRush.meleeUnitBehavior, WorkerRush.java:106-122
+        int closest = -1, cd = 0;
+        const int n = nunits();
+        for (int j = 0; j < n; j++) {
+            if (!inview(j, vp)) continue;
+            const Unit& o = u[j];
+            if (o.player < 0 || o.player == player) continue;
+            int d = iabs(o.x - u[i].x) + iabs(o.y - u[i].y);
+            if (closest < 0 || d < cd) {
+                closest = j;
+                cd = d;
+            }
+        }
+        if (closest >= 0) {
+            AbstractAct r;
+            r.unit = u[i].uid;
+            r.kind = AA_ATTACK;
+            r.utype = -1;
+            r.x = r.y = 0;
+            r.target = u[closest].uid;
+            r.base = NO_UID;
+            aa_put(r);
+        }
+    }
+    MRTS_HD void aa_harvest(int i, int target, int base) {
+        AbstractAct r;
+        r.unit = u[i].uid;
+        r.kind = AA_HARVEST;
+        r.utype = -1;
+        r.x = r.y = 0;
+        r.target = target >= 0 ? u[target].uid : (uint16_t)NO_UID;
+        r.base = base >= 0 ? u[base].uid : (uint16_t)NO_UID;
+        aa_put(r);
+    }
+    // WorkerRush.workersBehavior tail, WorkerRush.java:148-197: true = the worker stays free
+    MRTS_HD bool bot_harvest(int w, int player, int vp) {
+        int cres = -1, cbase = -1, cd = 0;
+        const int n = nunits();
+        for (int j = 0; j < n; j++) {
+            if (!inview(j, vp) || !ut_is_resource(u[j].type)) continue;
+            int d = iabs(u[j].x - u[w].x) + iabs(u[j].y - u[w].y);
+            if (cres < 0 || d < cd) {
+                cres = j;
+                cd = d;
+            }
+        }
+        cd = 0;
+        for (int j = 0; j < n; j++) {
+            if (!inview(j, vp) || !ut_is_stockpile(u[j].type) || u[j].player != player) continue;
+            int d = iabs(u[j].x - u[w].x) + iabs(u[j].y - u[w].y);
+            if (cbase < 0 || d < cd) {
+                cbase = j;
+                cd = d;
+            }
+        }
+        const int k = aa_find(u[w].uid);
+        const bool isharv = k >= 0 && aa[k].kind == AA_HARVEST;
+        if (u[w].res > 0) {
+            if (cbase >= 0) {
+                if (!isharv || aa[k].base != u[cbase].uid) aa_harvest(w, -1, cbase);
+                return false;
+            }
+        } else {
+            if (cres >= 0 && cbase >= 0) {
+                if (!isharv || aa[k].target != u[cres].uid || aa[k].base != u[cbase].uid) aa_harvest(w, cres, cbase);
+                return false;
+            }
+        }
+        return true;
+    }
+
+    // WorkerRush.getAction, J/ai/abstraction/WorkerRush.java:63-104 -> pa2
+    MRTS_HD void worker_rush(int player, int vp) {
+        const int n = nunits();
+        const int pres = hdr->res[player];
+        for (int i = 0; i < n; i++) {
+            const Unit& un = u[i];
+            if (un.type == UT_BASE && un.player == player && un.a_type < 0 && pres >= ut_cost(UT_WORKER)) {
+                AbstractAct r;
+                r.unit = un.uid;
+                r.kind = AA_TRAIN;
+                r.utype = UT_WORKER;
+                r.x = r.y = 0;
+                r.target = 0;
+                r.base = NO_UID;
+                aa_put(r);
+            }
+        }
+        for (int i = 0; i < n; i++) {
+            const Unit& un = u[i];
+            if (ut_can_attack(un.type) && !ut_can_harvest(un.type) && un.player == player && un.a_type < 0) bot_melee(i, player, vp);
+        }
+        // workersBehavior, WorkerRush.java:124-204
+        int nbases = 0, nworkers = 0;
+        for (int i = 0; i < n; i++) {
+            if (u[i].player != player) continue;
+            if (u[i].type == UT_BASE) nbases++;
+            if (ut_can_harvest(u[i].type)) nworkers++;
+        }
+        if (nworkers > 0) {
+            int builder = -1, harvester = -1, seen = 0;
+            const bool want_base = nbases == 0 && pres >= ut_cost(UT_BASE);
+            for (int i = 0; i < n && (harvester < 0); i++) {
+                if (u[i].player != player || !ut_can_harvest(u[i].type)) continue;
+                if (seen == 0 && want_base) builder = i;
+                else harvester = i;
+                seen++;
+            }
+            if (builder >= 0) {  // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245
+                int k = aa_find(u[builder].uid);
+                if (k < 0 || aa[k].kind != AA_BUILD || aa[k].utype != UT_BASE) {
+                    int pos = find_building_position(u[builder].x, u[builder].y, vp);
+                    AbstractAct r;
+                    r.unit = u[builder].uid;
+                    r.kind = AA_BUILD;
+                    r.utype = UT_BASE;
+                    r.x = (int16_t)(pos % W);  // pos == -1 -> (-1, 0): Java % and / truncate like C++
+                    r.y = (int16_t)(pos / W);
+                    r.target = NO_UID;
+                    r.base = NO_UID;
+                    aa_put(r);
+                }
+            }
+            bool hfree = false;
+            if (harvester >= 0) hfree = bot_harvest(harvester, player, vp);
+            for (int i = 0; i < n; i++) {
+                if (u[i].player != player || !ut_can_harvest(u[i].type)) continue;
+                if (i == builder || i == harvester) continue;
+                bot_melee(i, player, vp);
+            }
+            if (hfree) bot_melee(harvester, player, vp);
+        }
+        translate_actions(player, vp);
+    }
+
+    // the scripted opponent's PlayerAction for `player` -> pa2
+    MRTS_HD void bot_action(int player, int vp) {
+        npa2 = 0;
+        if (ai == AI_WORKER_RUSH) worker_rush(player, vp);
+        else fill_with_nones(pa2, npa2, player, 10, vp);  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
+    }
+
+    // ================================================================== one environment step
+    // a0 / a1: the (HW,7) int32 action blocks of this game's player views (a1 unused for bot games).
+    // On return: rew[][] holds the six reward terms per view, gameover/winner are set, the unit
+    // array still contains units killed this cycle (flagged) so that stale partially observable
+    // views can be encoded; the caller then runs compact() or reloads the map template.
+    MRTS_HD bool step_game(const int32_t* a0, const int32_t* a1) {
+        for (int p = 0; p < 2; p++)
+            for (int k = 0; k < 6; k++) rew[p][k] = 0;
+        if (ai == AI_NONE) {
+            // JNIGridnetClientSelfPlay.gameStep, :159-189
+            for (int p = 0; p < 2; p++) {
+                int vp = -1;
+                if (partial) {
+                    make_view(p);
+                    vp = p;
+                }
+                decode_actions(p, p == 0 ? a0 : a1, vp);
+                issue_safe(pa, npa);
+            }
+        } else {
+            // JNIGridnetClient.gameStep, :163-196
+            int v0 = -1, v1 = -1;
+            if (partial) {
+                make_view(0);
+                make_view(1);
+                v0 = 0;
+                v1 = 1;
+            }
+            decode_actions(0, a0, v0);
+            bot_action(1, v1);
+            issue_safe(pa, npa);
+            issue_safe(pa2, npa2);
+        }
+        cycle();
+        eval_gameover();
+        if (gameover) {  // WinLossRewardFunction.java:16-24
+            rew[0][0] = winner == 0 ? 1 : -1;
+            rew[1][0] = winner == 1 ? 1 : -1;
+        }
+        hdr->steps++;
+        return gameover || hdr->steps >= max_steps;  // JNIGridnetVecClient.java:245-266 / :270-286
+    }
+};
+
+}  // namespace mrts
