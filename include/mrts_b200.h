@@ -1,0 +1,99 @@
+/* C ABI of the B200-native vectorised MicroRTS simulator (libmrts_b200.so).
+ *
+ * This is the boundary the reference crosses with JPype today: gym_microrts/envs/vec_env.py
+ * builds a Java `tests.JNIGridnetVecClient` (vec_env.py:256-276) and calls its reset / gameStep /
+ * getMasks / close methods.  Each entry point below names the Java method it replaces
+ * (J/ = gym_microrts/microrts/src/).  All tensor pointers are DEVICE pointers owned by the
+ * caller; all work is enqueued on the given CUDA stream (cudaStream_t passed as void*, NULL =
+ * legacy default stream) and nothing synchronises unless stated.  Every function returns 0 on
+ * success or a negative MRTS_E* code; mrts_last_error() gives the message for the calling thread.
+ *
+ * Layouts (C-contiguous):
+ *   obs      (N, H, W, P)   P = 29, or 31 with partial_obs; element = int32 (reference dtype) or uint8
+ *   mask     (N, H*W, 78)   same element type as obs; 78 = [6,4,4,4,4,7,49]
+ *   actions  (N, H*W, 7)    int32, MultiDiscrete [6,4,4,4,4,7,49] per cell
+ *   reward   (N, 6)         float64: WinLoss, ResourceGather, ProduceWorker, ProduceBuilding, Attack, ProduceCombatUnit
+ *   done     (N,)           uint8
+ * N = num_selfplay_envs + num_bot_envs; env order as in JNIGridnetVecClient.java:117-124.
+ */
+#ifndef MRTS_B200_H
+#define MRTS_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MRTS_OK 0
+#define MRTS_EINVAL (-1)
+#define MRTS_ECUDA (-2)
+#define MRTS_ENOMEM (-3)
+
+#define MRTS_AI_PASSIVE 0     /* ai.PassiveAI      (gym_microrts/microrts_ai.py:13-16) */
+#define MRTS_AI_WORKER_RUSH 1 /* ai.abstraction.WorkerRush (microrts_ai.py:19-22)      */
+
+/* One parsed map: what PhysicalGameState.load returns (J/rts/PhysicalGameState.java:54-65,685-711). */
+typedef struct mrts_map_template {
+    int32_t width, height;
+    const uint8_t* terrain;  /* width*height, row-major, 0 free / 1 wall (host pointer)            */
+    int32_t resources[2];    /* players' starting resources                                        */
+    int32_t n_units;
+    const int32_t* units7;   /* n_units rows: id, type, player, x, y, resources, hitpoints (host)  */
+} mrts_map_template;
+
+/* Constructor arguments of JNIGridnetVecClient (J/tests/JNIGridnetVecClient.java:106-142). */
+typedef struct mrts_config {
+    int32_t num_selfplay_envs; /* even                                                             */
+    int32_t num_bot_envs;
+    int32_t max_steps;
+    int32_t partial_obs;
+    int32_t none_mode;         /* 1 = this fork (every NONE has parameter -1, UnitAction.java:149-154), 0 = upstream */
+    int32_t device;            /* CUDA device ordinal                                              */
+    int32_t n_maps;
+    const mrts_map_template* maps;
+    const int32_t* env_map;    /* N entries: template index per env (self-play game g uses entry 2g) */
+    const int32_t* bot_ai;     /* num_bot_envs entries: MRTS_AI_*                                  */
+    int32_t elem_bytes;        /* 4 = int32 obs/mask (reference dtype), 1 = uint8                  */
+    int32_t threads_per_game;  /* 0 = choose from the map size                                     */
+} mrts_config;
+
+typedef struct mrts_env mrts_env;
+
+/* new JNIGridnetVecClient(...) */
+int mrts_create(const mrts_config* cfg, mrts_env** out);
+/* JNIGridnetVecClient.close (:318-329) */
+void mrts_destroy(mrts_env* env);
+
+/* JNIGridnetVecClient.reset (:179-211): every game restarts from its map; obs / mask may be NULL. */
+int mrts_reset(mrts_env* env, void* obs, void* mask, void* stream);
+/* JNIGridnetVecClient.gameStep (:213-297) fused with getMasks (:307-316) of the resulting state:
+ * any of obs / mask / reward / done may be NULL. */
+int mrts_step(mrts_env* env, const int32_t* actions, void* obs, void* mask, double* reward, uint8_t* done, void* stream);
+/* JNIGridnetVecClient.getMasks (:307-316) of the current state. */
+int mrts_get_masks(mrts_env* env, void* mask, void* stream);
+
+/* Introspection (synchronises the stream). */
+int mrts_num_envs(const mrts_env* env);
+int mrts_num_games(const mrts_env* env);
+int mrts_planes(const mrts_env* env);
+int mrts_unit_capacity(const mrts_env* env);
+int mrts_threads_per_game(const mrts_env* env);
+int mrts_smem_bytes(const mrts_env* env);
+/* State of one game for cross-checks against the oracle: hdr5 = time, res0, res1, steps, nunits;
+ * rows12 = per unit: type, player, x, y, res, hp, a_type (-1 idle), a_param, a_x, a_y, a_utype, a_time.
+ * Returns the number of units (or a negative error); host pointers. */
+int mrts_export_state(mrts_env* env, int game, int32_t* hdr5, int32_t* rows12, int cap_rows, void* stream);
+
+/* Raw engine access for replaying recorded games (J/test/microrts/TestTracesIntegrity.java:72-126):
+ * GameState.issueSafe of one player's actions on one game, rows7 = ux, uy, type, param, ax, ay, utype (host). */
+int mrts_debug_issue(mrts_env* env, int game, const int32_t* rows7, int n, void* stream);
+/* GameState.cycle on one game; *gameover (host, may be NULL) receives the result. */
+int mrts_debug_cycle(mrts_env* env, int game, int* gameover, void* stream);
+
+const char* mrts_last_error(void);
+const char* mrts_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,173 @@
+// Output phases of one environment step, run by the whole thread group that owns a game:
+// the one-hot observation (GameState.getVectorObservation, J/rts/GameState.java:922-969, +
+// MicroRTSGridModeVecEnv._encode_obs, gym_microrts/envs/vec_env.py:311-321) and the per-cell
+// action mask (JNIGridnetClient.getMasks, J/tests/JNIGridnetClient.java:203-216 +
+// vec_env.py:1091-1101), written with 128-bit stores straight into the caller's tensors.
+//
+// Every function takes (tid, nth): the calling thread's rank in its group and the group size.
+// The host build (tests/hostsim) calls them with (0, 1).
+#pragma once
+#include "mrts_core.h"
+
+namespace mrts {
+
+// observation bit layout inside one cell word (= channel index): hp 0-4, resources 5-9,
+// owner 10-12, unit type 13-20, action 21-26, terrain 27-28, visibility 29-30 (partial_obs)
+enum { OB_HP = 0, OB_RES = 5, OB_OWNER = 10, OB_TYPE = 13, OB_ACT = 21, OB_TERRAIN = 27, OB_VIS = 29 };
+MRTS_HD int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// word of a unit as seen by `viewer` (owner planes are relative: 1 = mine, 2 = opponent's)
+MRTS_HD uint32_t unit_obs_word(const Unit& un, int viewer, int act_type) {
+    uint32_t w = 1u << (OB_HP + clampi(un.hp, 0, 4));
+    w |= 1u << (OB_RES + clampi(un.res, 0, 4));
+    w |= 1u << (OB_OWNER + (un.player >= 0 ? ((un.player + viewer) & 1) + 1 : 0));
+    w |= 1u << (OB_TYPE + un.type + 1);
+    w |= 1u << (OB_ACT + clampi(act_type, 0, 5));
+    return w;
+}
+enum : uint32_t { OBS_EMPTY = (1u << OB_HP) | (1u << OB_RES) | (1u << OB_OWNER) | (1u << OB_TYPE) | (1u << OB_ACT) };
+
+// Phase A (cells): words[c] for every cell.  vp < 0: the true state; vp = p: player p's stale
+// partially observable view (membership + assignment copy recorded in Unit::vis / vtype).
+// grid0 = the map's wall grid (terrain plane).
+MRTS_HD void obs_words_cells(const Sim& s, int viewer, int vp, const uint16_t* grid0, uint32_t* words, int tid, int nth) {
+    const int n = s.hdr->nunits;
+    for (int c = tid; c < s.HW; c += nth) {
+        uint32_t w = OBS_EMPTY;
+        const uint16_t g = s.grid[c];
+        if (g < G_WALL && s.inview(g, vp)) {
+            const Unit& un = s.u[g];
+            w = unit_obs_word(un, viewer, vp < 0 ? un.a_type : un.vtype[vp]);
+        }
+        w |= 1u << (OB_TERRAIN + (grid0[c] == G_WALL ? 1 : 0));
+        if (s.partial) {
+            // README-literal visibility planes: is this cell within sight of any unit
+            // of the viewer's opponent in the TRUE post-step state
+            const int x = c % s.W, y = c / s.W;
+            bool seen = false;
+            for (int j = 0; j < n && !seen; j++) {
+                const Unit& o = s.u[j];
+                if ((o.flags & UF_DEAD) || o.player != 1 - viewer) continue;
+                int dx = o.x - x, dy = o.y - y, r = ut_sight(o.type);
+                seen = dx * dx + dy * dy <= r * r;
+            }
+            w |= 1u << (OB_VIS + (seen ? 1 : 0));
+        }
+        words[c] = w;
+    }
+}
+// Phase B (units, after a barrier; partial_obs only): units killed this cycle still belong to
+// the stale view (hp <= 0 clips to plane 0).
+MRTS_HD void obs_words_dead(const Sim& s, int viewer, int vp, uint32_t* words, int tid, int nth) {
+    if (vp < 0) return;
+    const int n = s.hdr->nunits;
+    for (int i = tid; i < n; i += nth) {
+        const Unit& un = s.u[i];
+        if (!(un.flags & UF_DEAD) || !s.inview(i, vp)) continue;
+        const int c = un.x + un.y * s.W;
+        const uint32_t keep = words[c] & ((3u << OB_TERRAIN) | (3u << OB_VIS));
+        words[c] = keep | unit_obs_word(un, viewer, un.vtype[vp]);
+    }
+}
+
+// ---- element expansion: 4 (int32) or 16 (uint8) consecutive one-hot elements per 16-byte store
+struct Vec16 {
+    uint32_t a, b, c, d;
+};
+MRTS_HD uint32_t spread4(uint32_t nibble) { return (nibble * 0x00204081u) & 0x01010101u; }  // bit k -> byte k
+
+#if defined(__CUDA_ARCH__)
+MRTS_HD void store16(void* p, Vec16 v) {
+    // streaming 128-bit store: the outputs are written once and never re-read by this kernel
+    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.a), "r"(v.b), "r"(v.c), "r"(v.d) : "memory");
+}
+#else
+MRTS_HD void store16(void* p, Vec16 v) { *(Vec16*)p = v; }
+#endif
+
+// Phase C: one env's observation.  ELEM = 4 (int32) or 1 (uint8).  P = planes per cell.
+template <int ELEM>
+MRTS_HD void store_obs(const uint32_t* words, int HW, int P, void* out, int tid, int nth) {
+    const bool vec = (((uintptr_t)out) & 15) == 0;  // odd map sizes: env rows are not 16-byte aligned -> scalar stores
+    const int total = HW * P;                 // elements
+    constexpr int EPC = 16 / ELEM;            // elements per 16-byte chunk
+    const int nchunks = vec ? total / EPC : 0;
+    uint8_t* base = (uint8_t*)out;
+    for (int j = tid; j < nchunks; j += nth) {
+        const int e0 = j * EPC;
+        const int q = e0 / P;
+        const int o = e0 - q * P;
+        const uint64_t lo = words[q];
+        const uint64_t hi = (q + 1 < HW) ? words[q + 1] : 0;
+        const uint32_t bits = (uint32_t)(((hi << P) | lo) >> o);
+        Vec16 v;
+        if (ELEM == 4) {
+            v.a = bits & 1u;
+            v.b = (bits >> 1) & 1u;
+            v.c = (bits >> 2) & 1u;
+            v.d = (bits >> 3) & 1u;
+        } else {
+            v.a = spread4(bits & 0xF);
+            v.b = spread4((bits >> 4) & 0xF);
+            v.c = spread4((bits >> 8) & 0xF);
+            v.d = spread4((bits >> 12) & 0xF);
+        }
+        store16(base + (size_t)j * 16, v);
+    }
+    // tail (total not a multiple of the chunk): scalar stores
+    for (int e = nchunks * EPC + tid; e < total; e += nth) {
+        const int q = e / P, o = e - q * P;
+        const uint32_t bit = (words[q] >> o) & 1u;
+        if (ELEM == 4) ((int32_t*)out)[e] = (int32_t)bit;
+        else ((uint8_t*)out)[e] = (uint8_t)bit;
+    }
+}
+
+// Phase C': zero one env's mask (>99% of it stays zero)
+template <int ELEM>
+MRTS_HD void zero_mask(int HW, void* out, int tid, int nth) {
+    const int total = HW * 78;
+    constexpr int EPC = 16 / ELEM;
+    const int nchunks = ((((uintptr_t)out) & 15) == 0) ? total / EPC : 0;
+    uint8_t* base = (uint8_t*)out;
+    Vec16 z;
+    z.a = z.b = z.c = z.d = 0;
+    for (int j = tid; j < nchunks; j += nth) store16(base + (size_t)j * 16, z);
+    for (int e = nchunks * EPC + tid; e < total; e += nth) {
+        if (ELEM == 4) ((int32_t*)out)[e] = 0;
+        else ((uint8_t*)out)[e] = 0;
+    }
+}
+
+// Phase M (units): legal-action sets of every idle owned unit (true state), into umask[3*i..]
+MRTS_HD void unit_masks(const Sim& s, uint32_t* umask, int tid, int nth) {
+    const int n = s.hdr->nunits;
+    for (int i = tid; i < n; i += nth) {
+        const Unit& un = s.u[i];
+        if (un.player < 0 || un.a_type >= 0 || (un.flags & UF_DEAD)) continue;
+        Mask78 m = s.unit_mask(i);
+        umask[3 * i] = m.w[0];
+        umask[3 * i + 1] = m.w[1];
+        umask[3 * i + 2] = m.w[2];
+    }
+}
+
+// Phase D (after a barrier): the 78 entries of every source unit of `player`
+template <int ELEM>
+MRTS_HD void patch_mask(const Sim& s, int player, const uint32_t* umask, void* out, int tid, int nth) {
+    const int n = s.hdr->nunits;
+    // item = (unit, entry) flattened over 96 slots per unit so that a warp stays on one unit
+    const int items = n * 96;
+    for (int it = tid; it < items; it += nth) {
+        const int i = it / 96, b = it - i * 96;
+        if (b >= 78) continue;
+        const Unit& un = s.u[i];
+        if (un.player != player || un.a_type >= 0 || (un.flags & UF_DEAD)) continue;
+        const uint32_t bit = (umask[3 * i + (b >> 5)] >> (b & 31)) & 1u;
+        const size_t e = (size_t)(un.x + un.y * s.W) * 78 + b;
+        if (ELEM == 4) ((int32_t*)out)[e] = (int32_t)bit;
+        else ((uint8_t*)out)[e] = (uint8_t)bit;
+    }
+}
+
+}  // namespace mrts

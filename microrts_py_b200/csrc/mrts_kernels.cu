@@ -1,0 +1,305 @@
+// CUDA kernels (sm_100a) and the C ABI of include/mrts_b200.h.
+//
+// Execution model: one thread block per game.  The block stages the game's state blob
+// (header + unit table [+ scripted-bot table]) and the map's wall grid in shared memory, thread 0
+// runs the lock-step rules (mrts_core.h), then all threads encode and stream out the
+// observation and mask tensors with 128-bit stores (mrts_encode.h) and write the blob back.
+// There is no tensor-core work on this path (no dense contraction); the bound is HBM write
+// bandwidth of the obs + mask tensors.  No CPU fallback exists: every entry point launches a kernel.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/mrts_b200.h"
+#include "mrts_setup.h"
+
+using namespace mrts;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(MRTS_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct BlockSync {
+    __device__ __forceinline__ void operator()() const { __syncthreads(); }
+};
+
+__global__ void mrts_pass_kernel(const EnvParams P) {
+    extern __shared__ uint4 smem_raw[];
+    const int g = blockIdx.x;
+    if (g >= P.n_games) return;
+    game_pass(P, g, (uint8_t*)smem_raw, (int)threadIdx.x, (int)blockDim.x, BlockSync());
+}
+
+// ---- raw engine access (trace replay): one block, one game
+struct DebugArgs {
+    int game;
+    int op;  // 0 = issue_safe(rows), 1 = cycle
+    const int32_t* rows7;
+    int n;
+    int* gameover;
+};
+__global__ void mrts_debug_kernel(const EnvParams P, const DebugArgs A) {
+    extern __shared__ uint4 smem_raw[];
+    uint8_t* mem = (uint8_t*)smem_raw;
+    const int tid = threadIdx.x, nth = blockDim.x;
+    const Layout L = make_layout(P.W, P.HW, P.cap, P.has_bot);
+    Sim s;
+    s.W = P.W;
+    s.H = P.H;
+    s.HW = P.HW;
+    s.cap = P.cap;
+    s.none_mode = P.none_mode;
+    s.partial = 0;
+    s.max_steps = P.max_steps;
+    s.ai = P.game_ai[A.game];
+    s.hdr = (GameHdr*)(mem + L.blob);
+    s.u = (Unit*)(mem + L.blob + 32);
+    s.aa = (AbstractAct*)(mem + L.blob + 32 + P.cap * 32);
+    s.grid = (uint16_t*)(mem + L.grid);
+    s.pa = (PAct*)(mem + L.pa);
+    s.pa2 = (PAct*)(mem + L.pa2);
+    s.npa = s.npa2 = 0;
+    s.nbits_words = L.nbits_words;
+    s.bitsA = (uint32_t*)(mem + L.bits);
+    s.bitsB = s.bitsA + L.nbits_words;
+    s.bitsC = s.bitsB + L.nbits_words;
+    s.astar = (int16_t*)(mem + L.astar);
+    const MapTpl tpl = P.maps[P.game_map[A.game]];
+    uint8_t* gblob = P.games + (size_t)A.game * P.game_stride;
+    copy16<Q16>(mem + L.blob, gblob, 32 + P.cap * 32, tid, nth);
+    copy16<uint32_t>(s.grid, P.grid_pool + tpl.grid_off, align16(P.HW * 2), tid, nth);
+    __syncthreads();
+    for (int i = tid; i < s.hdr->nunits; i += nth) s.grid[s.u[i].x + s.u[i].y * P.W] = (uint16_t)i;
+    __syncthreads();
+    if (tid == 0) {
+        for (int p = 0; p < 2; p++)
+            for (int k = 0; k < 6; k++) s.rew[p][k] = 0;
+        if (A.op == 0) {
+            int cnt = 0;
+            for (int k = 0; k < A.n && cnt < P.cap; k++) {
+                const int32_t* r = A.rows7 + 7 * k;
+                int i = s.unit_at(r[0], r[1]);
+                if (i < 0) continue;
+                PAct e;
+                e.unit = (uint16_t)i;
+                e.type = (int8_t)r[2];
+                e.param = (int16_t)r[3];
+                e.x = (int16_t)r[4];
+                e.y = (int16_t)r[5];
+                e.utype = (int8_t)r[6];
+                e.pad = 0;
+                // a re-issued unit replaces its assignment (LinkedHashMap.put keeps the slot): drop the old one first
+                s.pa[cnt++] = e;
+            }
+            s.issue_safe(s.pa, cnt);
+        } else {
+            s.cycle();
+            s.eval_gameover();
+            s.compact();
+            if (A.gameover) *A.gameover = s.gameover;
+        }
+    }
+    __syncthreads();
+    copy16<Q16>(gblob, mem + L.blob, 32 + P.cap * 32, tid, nth);
+}
+
+}  // namespace
+
+struct mrts_env {
+    EnvParams P;
+    int device = 0;
+    int threads = 64;
+    int smem = 0;
+    int N = 0;
+    std::vector<void*> allocs;
+    int* d_flag = nullptr;
+    int32_t* d_rows = nullptr;
+    int rows_cap = 0;
+};
+
+namespace {
+
+int choose_threads(int HW) {
+    if (HW <= 64) return 32;
+    if (HW <= 256) return 64;
+    if (HW <= 1024) return 128;
+    return 256;
+}
+
+template <class T>
+int upload(mrts_env* e, const std::vector<T>& h, const T** out) {
+    void* d = nullptr;
+    size_t bytes = (h.size() ? h.size() : 1) * sizeof(T);
+    CK(cudaMalloc(&d, bytes));
+    e->allocs.push_back(d);
+    if (!h.empty()) CK(cudaMemcpy(d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *out = (const T*)d;
+    return MRTS_OK;
+}
+
+int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask, double* reward, uint8_t* done, void* stream) {
+    if (!e) return fail(MRTS_EINVAL, "null env");
+    CK(cudaSetDevice(e->device));
+    EnvParams P = e->P;
+    P.mode = mode;
+    P.actions = actions;
+    P.obs = obs;
+    P.mask = mask;
+    P.reward = reward;
+    P.done = done;
+    mrts_pass_kernel<<<P.n_games, e->threads, e->smem, (cudaStream_t)stream>>>(P);
+    CK(cudaGetLastError());
+    return MRTS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* mrts_last_error(void) { return g_err.c_str(); }
+const char* mrts_version(void) { return "mrts-b200 0.1 (sm_100a)"; }
+
+int mrts_create(const mrts_config* cfg, mrts_env** out) {
+    if (!cfg || !out) return fail(MRTS_EINVAL, "null argument");
+    *out = nullptr;
+    HostSetup S;
+    std::string err;
+    int rc = build_setup(cfg, S, err);
+    if (rc) return fail(rc, err);
+    mrts_env* e = new mrts_env();
+    e->device = cfg->device;
+    e->N = S.N;
+    e->P = S.P;
+    EnvParams& P = e->P;
+    const int W = P.W, HW = P.HW, cap = P.cap;
+    cudaError_t ce = cudaSetDevice(cfg->device);
+    if (ce != cudaSuccess) {
+        delete e;
+        return fail(MRTS_ECUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(ce));
+    }
+    if ((rc = upload(e, S.tpls, &P.maps)) || (rc = upload(e, S.grids, &P.grid_pool)) || (rc = upload(e, S.units, &P.unit_pool)) ||
+        (rc = upload(e, S.game_map, &P.game_map)) || (rc = upload(e, S.game_ai, &P.game_ai))) {
+        mrts_destroy(e);
+        return rc;
+    }
+    void* d = nullptr;
+    ce = cudaMalloc(&d, (size_t)P.n_games * P.game_stride);
+    if (ce != cudaSuccess) {
+        mrts_destroy(e);
+        return fail(MRTS_ENOMEM, std::string("cudaMalloc(games): ") + cudaGetErrorString(ce));
+    }
+    e->allocs.push_back(d);
+    P.games = (uint8_t*)d;
+    cudaMemset(d, 0, (size_t)P.n_games * P.game_stride);
+    ce = cudaMalloc(&d, sizeof(int));
+    if (ce == cudaSuccess) {
+        e->allocs.push_back(d);
+        e->d_flag = (int*)d;
+    }
+
+    e->threads = cfg->threads_per_game > 0 ? cfg->threads_per_game : choose_threads(HW);
+    if (e->threads > 1024) e->threads = 1024;
+    e->smem = make_layout(W, HW, cap, P.has_bot).total;
+    int maxsm = 0;
+    cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device);
+    if (e->smem > maxsm) {
+        mrts_destroy(e);
+        return fail(MRTS_EINVAL, "map too large for shared-memory staging");
+    }
+    if (e->smem > 48 * 1024) {
+        cudaFuncSetAttribute(mrts_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+        cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+    }
+    // start every game from its template so that the state is defined before the first reset()
+    rc = launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+    if (rc) {
+        mrts_destroy(e);
+        return rc;
+    }
+    ce = cudaDeviceSynchronize();
+    if (ce != cudaSuccess) {
+        mrts_destroy(e);
+        return fail(MRTS_ECUDA, std::string("initial reset: ") + cudaGetErrorString(ce));
+    }
+    *out = e;
+    return MRTS_OK;
+}
+
+void mrts_destroy(mrts_env* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    for (void* p : e->allocs) cudaFree(p);
+    if (e->d_rows) cudaFree(e->d_rows);
+    delete e;
+}
+
+int mrts_reset(mrts_env* e, void* obs, void* mask, void* stream) { return launch(e, MODE_RESET, nullptr, obs, mask, nullptr, nullptr, stream); }
+
+int mrts_step(mrts_env* e, const int32_t* actions, void* obs, void* mask, double* reward, uint8_t* done, void* stream) {
+    if (!actions) return fail(MRTS_EINVAL, "actions is null");
+    return launch(e, MODE_STEP, actions, obs, mask, reward, done, stream);
+}
+
+int mrts_get_masks(mrts_env* e, void* mask, void* stream) {
+    if (!mask) return fail(MRTS_EINVAL, "mask is null");
+    return launch(e, MODE_OBSERVE, nullptr, nullptr, mask, nullptr, nullptr, stream);
+}
+
+int mrts_num_envs(const mrts_env* e) { return e ? e->N : MRTS_EINVAL; }
+int mrts_num_games(const mrts_env* e) { return e ? e->P.n_games : MRTS_EINVAL; }
+int mrts_planes(const mrts_env* e) { return e ? e->P.planes : MRTS_EINVAL; }
+int mrts_unit_capacity(const mrts_env* e) { return e ? e->P.cap : MRTS_EINVAL; }
+int mrts_threads_per_game(const mrts_env* e) { return e ? e->threads : MRTS_EINVAL; }
+int mrts_smem_bytes(const mrts_env* e) { return e ? e->smem : MRTS_EINVAL; }
+
+int mrts_export_state(mrts_env* e, int game, int32_t* hdr5, int32_t* rows12, int cap_rows, void* stream) {
+    if (!e || game < 0 || game >= e->P.n_games) return fail(MRTS_EINVAL, "bad game index");
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    std::vector<uint8_t> blob(e->P.game_stride);
+    CK(cudaMemcpy(blob.data(), e->P.games + (size_t)game * e->P.game_stride, blob.size(), cudaMemcpyDeviceToHost));
+    export_blob(blob.data(), hdr5, rows12, cap_rows);
+    return ((const GameHdr*)blob.data())->nunits;
+}
+
+static int debug_launch(mrts_env* e, int game, int op, const int32_t* rows7, int n, int* gameover, void* stream) {
+    if (!e || game < 0 || game >= e->P.n_games) return fail(MRTS_EINVAL, "bad game index");
+    CK(cudaSetDevice(e->device));
+    DebugArgs A;
+    A.game = game;
+    A.op = op;
+    A.rows7 = nullptr;
+    A.n = n;
+    A.gameover = e->d_flag;
+    if (op == 0 && n > 0) {
+        if (n > e->rows_cap) {
+            if (e->d_rows) cudaFree(e->d_rows);
+            e->d_rows = nullptr;
+            CK(cudaMalloc((void**)&e->d_rows, (size_t)n * 7 * sizeof(int32_t)));
+            e->rows_cap = n;
+        }
+        CK(cudaMemcpyAsync(e->d_rows, rows7, (size_t)n * 7 * sizeof(int32_t), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+        A.rows7 = e->d_rows;
+    }
+    mrts_debug_kernel<<<1, 64, e->smem, (cudaStream_t)stream>>>(e->P, A);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (op == 1 && gameover) CK(cudaMemcpy(gameover, e->d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    return MRTS_OK;
+}
+int mrts_debug_issue(mrts_env* e, int game, const int32_t* rows7, int n, void* stream) { return debug_launch(e, game, 0, rows7, n, nullptr, stream); }
+int mrts_debug_cycle(mrts_env* e, int game, int* gameover, void* stream) { return debug_launch(e, game, 1, nullptr, 0, gameover, stream); }
+
+}  // extern "C"

@@ -1,0 +1,233 @@
+// One game's pass through a launch: stage the state blob in (shared) memory, run the rules on
+// the group's leader, then have the whole group write observation / mask / reward / done and
+// put the blob back.  Shared by the CUDA kernel (mrts_kernels.cu) and the host debug build.
+//
+// Replaces JNIGridnetVecClient.reset / gameStep / getMasks (J/tests/JNIGridnetVecClient.java:
+// 179-211, 213-297, 307-316) for one client; env index layout as in :117-124 (self-play game g
+// = envs 2g and 2g+1, then the bot envs).
+#pragma once
+#include "mrts_encode.h"
+
+namespace mrts {
+
+enum { MODE_STEP = 0, MODE_RESET = 1, MODE_OBSERVE = 2 };
+
+struct EnvParams {
+    int32_t num_selfplay, num_bot;  // player views, as in the reference constructor
+    int32_t n_games;                // num_selfplay / 2 + num_bot
+    int32_t W, H, HW, cap, planes;
+    int32_t partial, none_mode, max_steps;
+    int32_t has_bot;                // any WorkerRush game: blob carries the abstract-action table
+    int32_t game_stride;            // bytes per game blob
+    uint8_t* games;                 // n_games blobs
+    const MapTpl* maps;
+    const uint16_t* grid_pool;      // wall grids of all templates
+    const Unit* unit_pool;          // initial unit lists of all templates
+    const int32_t* game_map;        // template id per game
+    const int8_t* game_ai;          // AI_* per game (AI_NONE = self-play)
+    // per-launch
+    int32_t mode;
+    int32_t elem;                   // bytes per obs/mask element: 4 (int32, reference dtype) or 1 (uint8)
+    const int32_t* actions;         // (N, HW, 7) int32
+    void* obs;                      // (N, H, W, planes) or null
+    void* mask;                     // (N, HW, 78) or null
+    double* reward;                 // (N, 6) or null
+    uint8_t* done;                  // (N,) or null
+};
+
+MRTS_HD int align16(int v) { return (v + 15) & ~15; }
+MRTS_HD int blob_bytes(int cap, int has_bot) { return 32 + cap * 32 + (has_bot ? align16(cap * 12) : 0); }
+
+struct Layout {
+    int blob, grid, words, umask, pa, pa2, bits, astar, misc, total, nbits_words;
+};
+MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot) {
+    Layout L;
+    int o = 0;
+    L.blob = o;
+    o += blob_bytes(cap, has_bot);
+    L.grid = o;
+    o += align16(HW * 2);
+    L.words = o;
+    o += align16(2 * HW * 4);
+    L.umask = o;
+    o += align16(cap * 12);
+    L.pa = o;
+    o += align16(cap * (int)sizeof(PAct));
+    L.pa2 = o;
+    o += has_bot ? align16(cap * (int)sizeof(PAct)) : 0;
+    L.nbits_words = (HW + 2 * W + 31) / 32;
+    L.bits = o;
+    o += align16(3 * L.nbits_words * 4);
+    L.astar = o;
+    o += has_bot ? align16(5 * (HW + 1) * 2 + HW) : 0;
+    L.misc = o;
+    o += 16;
+    L.total = o;
+    return L;
+}
+
+template <class T>
+MRTS_HD void copy16(void* dst, const void* src, int bytes, int tid, int nth) {  // bytes multiple of 16, both 16-aligned
+    const T* s = (const T*)src;
+    T* d = (T*)dst;
+    const int n = bytes / (int)sizeof(T);
+    for (int i = tid; i < n; i += nth) d[i] = s[i];
+}
+struct alignas(16) Q16 {
+    uint32_t a, b, c, d;
+};
+
+// SYNC: functor executing a barrier over the game's thread group.
+template <class SYNC>
+MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync) {
+    const Layout L = make_layout(P.W, P.HW, P.cap, P.has_bot);
+    Sim s;
+    s.W = P.W;
+    s.H = P.H;
+    s.HW = P.HW;
+    s.cap = P.cap;
+    s.none_mode = P.none_mode;
+    s.partial = P.partial;
+    s.max_steps = P.max_steps;
+    s.ai = P.game_ai[g];
+    s.hdr = (GameHdr*)(mem + L.blob);
+    s.u = (Unit*)(mem + L.blob + 32);
+    s.aa = (AbstractAct*)(mem + L.blob + 32 + P.cap * 32);
+    s.grid = (uint16_t*)(mem + L.grid);
+    s.pa = (PAct*)(mem + L.pa);
+    s.pa2 = (PAct*)(mem + L.pa2);
+    s.npa = s.npa2 = 0;
+    s.nbits_words = L.nbits_words;
+    s.bitsA = (uint32_t*)(mem + L.bits);
+    s.bitsB = s.bitsA + L.nbits_words;
+    s.bitsC = s.bitsB + L.nbits_words;
+    s.astar = (int16_t*)(mem + L.astar);
+    s.gameover = 0;
+    s.winner = -1;
+    uint32_t* words = (uint32_t*)(mem + L.words);
+    uint32_t* umask = (uint32_t*)(mem + L.umask);
+    volatile int32_t* misc = (volatile int32_t*)(mem + L.misc);
+
+    const MapTpl tpl = P.maps[P.game_map[g]];
+    const uint16_t* grid0 = P.grid_pool + tpl.grid_off;
+    uint8_t* gblob = P.games + (size_t)g * P.game_stride;
+    const bool selfplay = s.ai == AI_NONE;
+    const int nsp_games = P.num_selfplay / 2;
+    const int env0 = selfplay ? 2 * g : P.num_selfplay + (g - nsp_games);
+    const int nviews = selfplay ? 2 : 1;
+
+    // ---------------- load: template (reset) or the stored blob
+    auto load_template = [&]() {
+        if (tid == 0) {
+            GameHdr h;
+            h.nunits = tpl.nunits;
+            h.time = 0;
+            h.res[0] = tpl.res[0];
+            h.res[1] = tpl.res[1];
+            h.steps = 0;
+            h.next_seq = 0;
+            h.next_uid = (uint16_t)tpl.nunits;
+            h.n_aa = 0;
+            h.pad = 0;
+            *s.hdr = h;
+        }
+        copy16<Q16>(s.u, P.unit_pool + tpl.unit_off, tpl.nunits * 32, tid, nth);
+        copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
+    };
+    auto scatter_grid = [&]() {
+        const int n = s.hdr->nunits;
+        for (int i = tid; i < n; i += nth) s.grid[s.u[i].x + s.u[i].y * P.W] = (uint16_t)i;
+    };
+    if (P.mode == MODE_RESET) {
+        load_template();
+    } else {
+        const GameHdr* gh = (const GameHdr*)gblob;
+        const int n = gh->nunits, naa = gh->n_aa;
+        copy16<Q16>(mem + L.blob, gblob, 32 + n * 32, tid, nth);
+        if (P.has_bot && naa > 0) copy16<Q16>(s.aa, gblob + 32 + P.cap * 32, align16(naa * 12), tid, nth);
+        copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
+    }
+    sync();
+    scatter_grid();
+    sync();
+
+    // ---------------- rules (leader)
+    if (tid == 0) {
+        int reset = 0;
+        if (P.mode == MODE_STEP) {
+            const int32_t* a0 = P.actions + (size_t)env0 * P.HW * 7;
+            reset = s.step_game(a0, a0 + (size_t)P.HW * 7) ? 1 : 0;
+            for (int v = 0; v < nviews; v++) {
+                if (P.reward)
+                    for (int k = 0; k < 6; k++) P.reward[(size_t)(env0 + v) * 6 + k] = (double)s.rew[v][k];
+                // done[0] of WinLoss, forced true by the vec client on terminal / max_steps
+                if (P.done) P.done[env0 + v] = (uint8_t)reset;
+            }
+        } else if (P.partial) {
+            for (int v = 0; v < nviews; v++) s.make_view(v);
+        }
+        misc[0] = reset;
+    }
+    sync();
+    const int reset = misc[0];
+    if (reset) {  // JNIGridnetClient.reset: fresh game from the map, scripted opponent re-created
+        load_template();
+        sync();
+        scatter_grid();
+        sync();
+        if (P.partial) {
+            if (tid == 0)
+                for (int v = 0; v < nviews; v++) s.make_view(v);
+            sync();
+        }
+    }
+
+    // ---------------- observation words of every view (before compaction: stale views keep the dead)
+    if (P.obs) {
+        for (int v = 0; v < nviews; v++) obs_words_cells(s, v, P.partial ? v : -1, grid0, words + v * P.HW, tid, nth);
+        if (P.partial) {
+            sync();
+            for (int v = 0; v < nviews; v++) obs_words_dead(s, v, v, words + v * P.HW, tid, nth);
+        }
+    }
+    sync();
+    if (P.mode == MODE_STEP && !reset) {
+        if (tid == 0) s.compact();
+        sync();
+    }
+    if (P.mask) unit_masks(s, umask, tid, nth);
+
+    // ---------------- bulk stores
+    const size_t obs_env = (size_t)P.HW * P.planes * P.elem;
+    const size_t mask_env = (size_t)P.HW * 78 * P.elem;
+    for (int v = 0; v < nviews; v++) {
+        if (P.obs) {
+            void* o = (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env;
+            if (P.elem == 4) store_obs<4>(words + v * P.HW, P.HW, P.planes, o, tid, nth);
+            else store_obs<1>(words + v * P.HW, P.HW, P.planes, o, tid, nth);
+        }
+        if (P.mask) {
+            void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;
+            if (P.elem == 4) zero_mask<4>(P.HW, m, tid, nth);
+            else zero_mask<1>(P.HW, m, tid, nth);
+        }
+    }
+    sync();  // zero-fill before patches (and umask complete)
+    if (P.mask) {
+        for (int v = 0; v < nviews; v++) {
+            void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;
+            if (P.elem == 4) patch_mask<4>(s, v, umask, m, tid, nth);
+            else patch_mask<1>(s, v, umask, m, tid, nth);
+        }
+    }
+
+    // ---------------- put the blob back
+    if (P.mode != MODE_OBSERVE || P.partial) {
+        const int n = s.hdr->nunits, naa = s.hdr->n_aa;
+        copy16<Q16>(gblob, mem + L.blob, 32 + n * 32, tid, nth);
+        if (P.has_bot && naa > 0) copy16<Q16>(gblob + 32 + P.cap * 32, s.aa, align16(naa * 12), tid, nth);
+    }
+}
+
+}  // namespace mrts
