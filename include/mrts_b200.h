@@ -72,6 +72,25 @@ int mrts_step(mrts_env* env, const int32_t* actions, void* obs, void* mask, doub
 /* JNIGridnetVecClient.getMasks (:307-316) of the current state. */
 int mrts_get_masks(mrts_env* env, void* mask, void* stream);
 
+/* gameStep + getMasks + (optionally) a masked-uniform random policy for the resulting state,
+ * the sampling recipe of the reference's hello_world.py:27-67 moved onto the device so that a
+ * random-policy rollout never touches the host.  next_actions (N, H*W, 7) int32 receives, at the
+ * cell of every unit that may act next step, one action drawn uniformly per component from the
+ * unit's mask (0 where a component has no legal value); other cells are left as they are.
+ * next_actions may alias actions.  Reproducible from (seed, number of sampled launches so far). */
+typedef struct mrts_step_io {
+    const int32_t* actions; /* (N, H*W, 7) int32, required                                      */
+    void* obs;              /* nullable                                                         */
+    void* mask;             /* nullable                                                         */
+    double* reward;         /* (N, 6), nullable                                                 */
+    uint8_t* done;          /* (N,), nullable                                                   */
+    int32_t* next_actions;  /* nullable                                                         */
+    uint64_t seed;
+} mrts_step_io;
+int mrts_step_ex(mrts_env* env, const mrts_step_io* io, void* stream);
+/* The same sampler on the current state (e.g. after mrts_reset). */
+int mrts_sample_actions(mrts_env* env, int32_t* next_actions, uint64_t seed, void* stream);
+
 /* Introspection (synchronises the stream). */
 int mrts_num_envs(const mrts_env* env);
 int mrts_num_games(const mrts_env* env);

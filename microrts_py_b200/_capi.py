@@ -52,6 +52,18 @@ class ConfigC(C.Structure):
     ]
 
 
+class StepIOC(C.Structure):
+    _fields_ = [
+        ("actions", C.c_void_p),
+        ("obs", C.c_void_p),
+        ("mask", C.c_void_p),
+        ("reward", C.c_void_p),
+        ("done", C.c_void_p),
+        ("next_actions", C.c_void_p),
+        ("seed", C.c_uint64),
+    ]
+
+
 def make_config(
     num_selfplay_envs: int,
     num_bot_envs: int,
@@ -130,6 +142,8 @@ SYMBOLS = [
     "mrts_reset",
     "mrts_step",
     "mrts_get_masks",
+    "mrts_step_ex",
+    "mrts_sample_actions",
     "mrts_num_envs",
     "mrts_num_games",
     "mrts_planes",
@@ -161,6 +175,8 @@ def lib():
         L.mrts_reset.argtypes = [vp, vp, vp, vp]
         L.mrts_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.mrts_get_masks.argtypes = [vp, vp, vp]
+        L.mrts_step_ex.argtypes = [vp, C.POINTER(StepIOC), vp]
+        L.mrts_sample_actions.argtypes = [vp, vp, C.c_uint64, vp]
         for f in ("mrts_num_envs", "mrts_num_games", "mrts_planes", "mrts_unit_capacity", "mrts_threads_per_game", "mrts_smem_bytes"):
             getattr(L, f).argtypes = [vp]
         L.mrts_export_state.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]

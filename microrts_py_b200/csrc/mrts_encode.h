@@ -170,4 +170,62 @@ MRTS_HD void patch_mask(const Sim& s, int player, const uint32_t* umask, void* o
     }
 }
 
+// ---- masked-uniform action sampler (the recipe of the reference's hello_world.py:27-67: an
+// independent categorical per action component restricted to mask == 1; an all-zero group
+// yields 0), driven by a counter-based hash so a run is reproducible from (seed, launch counter).
+MRTS_HD uint64_t mix64(uint64_t z) {  // splitmix64 finaliser
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+MRTS_HD int popc64(uint64_t v) {
+#if defined(__CUDA_ARCH__)
+    return __popcll(v);
+#else
+    return __builtin_popcountll(v);
+#endif
+}
+// index of the (r mod popcount)-th set bit of `bits`, 0 if none is set
+MRTS_HD int pick_bit(uint64_t bits, uint32_t r) {
+    const int n = popc64(bits);
+    if (n == 0) return 0;
+    int k = (int)(r % (uint32_t)n);
+    for (int b = 0; b < 64; b++)
+        if ((bits >> b) & 1) {
+            if (k == 0) return b;
+            k--;
+        }
+    return 0;
+}
+MRTS_HD void sample_unit_action(const uint32_t* um, uint64_t key, int32_t* out7) {
+    const uint64_t lo = (uint64_t)um[0] | ((uint64_t)um[1] << 32);
+    const uint64_t att = (lo >> 29) | ((uint64_t)um[2] << 35);  // bits 29..77
+    const uint64_t r0 = mix64(key), r1 = mix64(key ^ 0xD1B54A32D192ED03ULL);
+    out7[0] = pick_bit(lo & 0x3F, (uint32_t)r0 & 0xFFFF);
+    out7[1] = pick_bit((lo >> 6) & 0xF, (uint32_t)(r0 >> 16) & 0xFFFF);
+    out7[2] = pick_bit((lo >> 10) & 0xF, (uint32_t)(r0 >> 32) & 0xFFFF);
+    out7[3] = pick_bit((lo >> 14) & 0xF, (uint32_t)(r0 >> 48) & 0xFFFF);
+    out7[4] = pick_bit((lo >> 18) & 0xF, (uint32_t)r1 & 0xFFFF);
+    out7[5] = pick_bit((lo >> 22) & 0x7F, (uint32_t)(r1 >> 16) & 0xFFFF);
+    out7[6] = pick_bit(att & 0x1FFFFFFFFFFFFULL, (uint32_t)(r1 >> 32));
+}
+// Phase S (units, after unit_masks + barrier): write the sampled action of every source unit of
+// view `player` at its cell of that view's (HW,7) block; other cells are left untouched (the
+// step only ever reads the cells of source units, PlayerAction.java:407).
+MRTS_HD void sample_actions(const Sim& s, int player, const uint32_t* umask, int32_t* out, uint64_t seed, uint32_t counter, uint32_t env,
+                            int tid, int nth) {
+    const int n = s.hdr->nunits;
+    for (int i = tid; i < n; i += nth) {
+        const Unit& un = s.u[i];
+        if (un.player != player || un.a_type >= 0 || (un.flags & UF_DEAD)) continue;
+        const int c = un.x + un.y * s.W;
+        const uint64_t key = mix64(seed ^ ((uint64_t)counter << 32 | env)) ^ (uint64_t)c * 0x9E3779B97F4A7C15ULL;
+        int32_t a[7];
+        sample_unit_action(umask + 3 * i, key, a);
+        int32_t* o = out + (size_t)c * 7;
+        for (int k = 0; k < 7; k++) o[k] = a[k];
+    }
+}
+
 }  // namespace mrts

@@ -127,6 +127,7 @@ struct mrts_env {
     int* d_flag = nullptr;
     int32_t* d_rows = nullptr;
     int rows_cap = 0;
+    uint32_t sample_counter = 0;
 };
 
 namespace {
@@ -149,7 +150,8 @@ int upload(mrts_env* e, const std::vector<T>& h, const T** out) {
     return MRTS_OK;
 }
 
-int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask, double* reward, uint8_t* done, void* stream) {
+int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask, double* reward, uint8_t* done, void* stream,
+           int32_t* next_actions = nullptr, uint64_t seed = 0) {
     if (!e) return fail(MRTS_EINVAL, "null env");
     CK(cudaSetDevice(e->device));
     EnvParams P = e->P;
@@ -159,6 +161,9 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     P.mask = mask;
     P.reward = reward;
     P.done = done;
+    P.next_actions = next_actions;
+    P.seed = seed;
+    P.counter = next_actions ? e->sample_counter++ : 0;
     mrts_pass_kernel<<<P.n_games, e->threads, e->smem, (cudaStream_t)stream>>>(P);
     CK(cudaGetLastError());
     return MRTS_OK;
@@ -255,6 +260,16 @@ int mrts_step(mrts_env* e, const int32_t* actions, void* obs, void* mask, double
 int mrts_get_masks(mrts_env* e, void* mask, void* stream) {
     if (!mask) return fail(MRTS_EINVAL, "mask is null");
     return launch(e, MODE_OBSERVE, nullptr, nullptr, mask, nullptr, nullptr, stream);
+}
+
+int mrts_step_ex(mrts_env* e, const mrts_step_io* io, void* stream) {
+    if (!io || !io->actions) return fail(MRTS_EINVAL, "actions is null");
+    return launch(e, MODE_STEP, io->actions, io->obs, io->mask, io->reward, io->done, stream, io->next_actions, io->seed);
+}
+
+int mrts_sample_actions(mrts_env* e, int32_t* next_actions, uint64_t seed, void* stream) {
+    if (!next_actions) return fail(MRTS_EINVAL, "next_actions is null");
+    return launch(e, MODE_OBSERVE, nullptr, nullptr, nullptr, nullptr, nullptr, stream, next_actions, seed);
 }
 
 int mrts_num_envs(const mrts_env* e) { return e ? e->N : MRTS_EINVAL; }

@@ -33,6 +33,9 @@ struct EnvParams {
     void* mask;                     // (N, HW, 78) or null
     double* reward;                 // (N, 6) or null
     uint8_t* done;                  // (N,) or null
+    int32_t* next_actions;          // (N, HW, 7) or null: masked-uniform sample for the resulting state
+    uint64_t seed;                  // sampler key
+    uint32_t counter;               // launch counter (sampler stream position)
 };
 
 MRTS_HD int align16(int v) { return (v + 15) & ~15; }
@@ -196,7 +199,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         if (tid == 0) s.compact();
         sync();
     }
-    if (P.mask) unit_masks(s, umask, tid, nth);
+    if (P.mask || P.next_actions) unit_masks(s, umask, tid, nth);
 
     // ---------------- bulk stores
     const size_t obs_env = (size_t)P.HW * P.planes * P.elem;
@@ -214,6 +217,9 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         }
     }
     sync();  // zero-fill before patches (and umask complete)
+    if (P.next_actions)
+        for (int v = 0; v < nviews; v++)
+            sample_actions(s, v, umask, P.next_actions + (size_t)(env0 + v) * P.HW * 7, P.seed, P.counter, (uint32_t)(env0 + v), tid, nth);
     if (P.mask) {
         for (int v = 0; v < nviews; v++) {
             void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;

@@ -1,0 +1,401 @@
+"""``MicroRTSGridModeVecEnv`` on B200: the reference's vectorised environment class
+(gym_microrts/envs/vec_env.py:38-1101) with the JVM/JPype backend replaced by libmrts_b200.so
+(include/mrts_b200.h), hand-written sm_100a CUDA kernels that run the whole step on the device.
+
+Same constructor arguments, attributes, method names, shapes and dtypes as the reference; see
+INTEGRATION.md for the call-by-call mapping.  PyTorch is used for device memory, streams and
+pinned host buffers only.  There is no CPU fallback: without the CUDA library or a CUDA device
+the constructor raises.
+
+Extra keyword-only arguments (all default to the reference's behaviour):
+
+  device        CUDA device ordinal or ``torch.device`` (default: the current device)
+  dtype         element type of observations and masks: ``np.int32`` (reference) or ``np.uint8``
+                (same values, a quarter of the HBM traffic)
+  return_torch  return device tensors instead of NumPy arrays (no host round trip)
+  zero_copy     NumPy mode only: return views of two alternating pinned host buffers instead of
+                fresh arrays (an array stays valid until the second next call of the same method)
+  fuse_mask     compute the action mask of the resulting state inside ``step`` (one launch,
+                the state is staged once); ``get_action_mask`` then only hands it out
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import _capi
+from ..maps import MapTemplate, load_map
+from ..microrts_ai import DeviceAI
+from ..spaces import Box, MultiDiscrete
+
+# ---------------------------------------------------------------------------------------------
+# UnitTypeTable() = VERSION_ORIGINAL + MOVE_CONFLICT_RESOLUTION_CANCEL_BOTH (J/rts/units/
+# UnitTypeTable.java:74-76,105-290), serialised the way UnitTypeTable.toJSON / UnitType.toJSON do
+# (UnitTypeTable.java:373-384, UnitType.java:305-350): this is the ``utt`` dict of the reference.
+# ---------------------------------------------------------------------------------------------
+_UTT_ROWS = [
+    # name, cost, hp, minD, maxD, range, produceT, moveT, attackT, harvestT, returnT, harvestAmt, sight, isRes, isStock, canHarv, canMove, canAtk, produces, producedBy
+    ("Resource", 1, 1, 1, 1, 1, 10, 10, 10, 10, 10, 1, 0, True, False, False, False, False, [], []),
+    ("Base", 10, 10, 1, 1, 1, 250, 10, 10, 10, 10, 1, 5, False, True, False, False, False, ["Worker"], ["Worker"]),
+    ("Barracks", 5, 4, 1, 1, 1, 200, 10, 10, 10, 10, 1, 3, False, False, False, False, False, ["Light", "Heavy", "Ranged"], ["Worker"]),
+    ("Worker", 1, 1, 1, 1, 1, 50, 10, 5, 20, 10, 1, 3, False, False, True, True, True, ["Base", "Barracks"], ["Base"]),
+    ("Light", 2, 4, 2, 2, 1, 80, 8, 5, 10, 10, 1, 2, False, False, False, True, True, [], ["Barracks"]),
+    ("Heavy", 2, 4, 4, 4, 1, 120, 12, 5, 10, 10, 1, 2, False, False, False, True, True, [], ["Barracks"]),
+    ("Ranged", 2, 1, 1, 1, 3, 100, 10, 5, 10, 10, 1, 3, False, False, False, True, True, [], ["Barracks"]),
+]
+_UTT_KEYS = [
+    "name", "cost", "hp", "minDamage", "maxDamage", "attackRange", "produceTime", "moveTime", "attackTime", "harvestTime",
+    "returnTime", "harvestAmount", "sightRadius", "isResource", "isStockpile", "canHarvest", "canMove", "canAttack", "produces", "producedBy",
+]  # fmt: skip
+
+
+def unit_type_table() -> dict:
+    types = []
+    for i, row in enumerate(_UTT_ROWS):
+        d = {"ID": i}
+        d.update(dict(zip(_UTT_KEYS, row)))
+        d["produces"] = list(d["produces"])
+        d["producedBy"] = list(d["producedBy"])
+        types.append(d)
+    return {"moveConflictResolutionStrategy": 1, "unitTypes": types}
+
+
+class RewardFunction:
+    """Stand-in for the Java reward objects in ``env.rfs``: callers only use ``str(rf)``, the Java
+    simple class name (J/ai/reward/RewardFunctionInterface.java:27-29; experiments/ppo_gridnet.py:151-153)."""
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __str__(self):
+        return self.name
+
+    __repr__ = __str__
+
+
+_RF_NAMES = [
+    "WinLossRewardFunction",
+    "ResourceGatherRewardFunction",
+    "ProduceWorkerRewardFunction",
+    "ProduceBuildingRewardFunction",
+    "AttackRewardFunction",
+    "ProduceCombatUnitRewardFunction",
+]  # order of vec_env.py:185-195
+
+_DEFAULT_MICRORTS_PATHS = [os.environ.get("MICRORTS_PATH", ""), "/root/reference/gym_microrts/microrts"]
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class MicroRTSGridModeVecEnv:
+    metadata = {"render.modes": ["human", "rgb_array"], "video.frames_per_second": 150}
+
+    def __init__(
+        self,
+        num_selfplay_envs,
+        num_bot_envs,
+        partial_obs=False,
+        max_steps=2000,
+        render_theme=2,
+        frame_skip=0,
+        ai2s=[],
+        map_paths=["maps/10x10/basesTwoWorkers10x10.xml"],
+        reward_shaping=True,
+        reward_weight=np.array([0.0, 1.0, 0.0, 0.0, 0.0, 5.0]),
+        cycle_maps=[],
+        autobuild=False,
+        jvm_args=[],
+        prior_mode="none",
+        reward_prior_weight=0.01,
+        prior_advice_freq=1,
+        seed=1,
+        runs_dir=".",
+        graph_ttl_file="graph.ttl",
+        graph_triples_file="triples.tsv",
+        *,
+        device=None,
+        dtype=np.int32,
+        return_torch=False,
+        zero_copy=False,
+        fuse_mask=True,
+        microrts_path=None,
+        threads_per_game=0,
+    ):
+        self.num_selfplay_envs = num_selfplay_envs
+        self.num_bot_envs = num_bot_envs
+        self.num_envs = num_selfplay_envs + num_bot_envs
+        assert self.num_bot_envs == len(ai2s), "for each environment, a microrts ai should be provided"
+        self.partial_obs = partial_obs
+        self.max_steps = max_steps
+        self.render_theme = render_theme
+        self.frame_skip = frame_skip
+        self.ai2s = ai2s
+        self.map_paths = list(map_paths)
+        if len(map_paths) == 1:
+            self.map_paths = [map_paths[0] for _ in range(self.num_envs)]
+        else:
+            assert len(map_paths) == self.num_envs, "if multiple maps are provided, they should be provided for each environment"
+        self.reward_shaping = reward_shaping
+        self.reward_weight = np.asarray(reward_weight, np.float64)
+        if str(prior_mode) != "none":
+            raise NotImplementedError("the knowledge-graph prior (prior_mode != 'none') is outside the device hot path")
+        if len(cycle_maps) > 0:
+            raise NotImplementedError("cycle_maps is not built yet (SURVEY 8f, next)")
+        self.cycle_maps = []
+        if num_selfplay_envs % 2:
+            raise ValueError("num_selfplay_envs must be even (two player views per self-play game)")
+        self.microrts_path = microrts_path or next((p for p in _DEFAULT_MICRORTS_PATHS if p and os.path.isdir(p)), "")
+
+        # ---- maps: parsed once, device-resident templates (the reference re-parses per reset)
+        cache = {}
+        templates: List[MapTemplate] = []
+        for p in self.map_paths:
+            if p not in cache:
+                cache[p] = load_map(p, self.microrts_path)
+            templates.append(cache[p])
+        self.height, self.width = templates[0].height, templates[0].width
+
+        # ---- scripted opponents -> device bot ids
+        ai_ids = []
+        for ai2 in ai2s:
+            a = ai2(None) if callable(ai2) else ai2
+            if not isinstance(a, DeviceAI):
+                raise NotImplementedError(f"ai2s entry {ai2!r} has no device implementation (use microrts_py_b200.microrts_ai)")
+            ai_ids.append(a.ai_id)
+
+        # ---- device
+        if not torch.cuda.is_available():
+            raise RuntimeError("microrts_py_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", dev_index)
+        self._np_dtype = np.dtype(dtype)
+        if self._np_dtype not in (np.dtype(np.int32), np.dtype(np.uint8)):
+            raise ValueError("dtype must be np.int32 (reference) or np.uint8")
+        self._t_dtype = torch.int32 if self._np_dtype == np.int32 else torch.uint8
+        self.return_torch = bool(return_torch)
+        self.zero_copy = bool(zero_copy)
+        self.fuse_mask = bool(fuse_mask)
+
+        self._lib = _capi.lib()
+        cfg, self._keep = _capi.make_config(
+            num_selfplay_envs, num_bot_envs, max_steps, partial_obs, templates, ai_ids,
+            none_mode=_capi.NONE_FORK, device=dev_index, elem_bytes=self._np_dtype.itemsize, threads_per_game=threads_per_game,
+        )  # fmt: skip
+        h = C.c_void_p()
+        _capi.check(self._lib.mrts_create(C.byref(cfg), C.byref(h)))
+        self._h = h
+
+        # ---- the reference's computed properties (vec_env.py:229-254)
+        self.real_utt = None
+        self.utt = unit_type_table()
+        self.rfs = [RewardFunction(n) for n in _RF_NAMES]
+        self.action_space_dims = [6, 4, 4, 4, 4, len(self.utt["unitTypes"]), 7 * 7]
+        self.num_planes = [5, 5, 3, len(self.utt["unitTypes"]) + 1, 6, 2]
+        if partial_obs:
+            self.num_planes = [5, 5, 3, len(self.utt["unitTypes"]) + 1, 6, 2, 2]
+        obs_length = sum(self.num_planes)
+        assert obs_length == self._lib.mrts_planes(self._h)
+        self.observation_space = Box(low=0.0, high=1.0, shape=(self.height, self.width, obs_length), dtype=np.int32)
+        self.num_planes_len = len(self.num_planes)
+        self.num_planes_prefix_sum = [0]
+        for num_plane in self.num_planes:
+            self.num_planes_prefix_sum.append(self.num_planes_prefix_sum[-1] + num_plane)
+        self.action_space = MultiDiscrete(np.array([self.action_space_dims] * self.height * self.width).flatten())
+        self.action_plane_space = MultiDiscrete(self.action_space_dims)
+        self.source_unit_idxs = np.tile(np.arange(self.height * self.width), (self.num_envs, 1))
+        self.source_unit_idxs = self.source_unit_idxs.reshape((self.source_unit_idxs.shape + (1,)))
+
+        # ---- buffers
+        N, HW, P = self.num_envs, self.height * self.width, obs_length
+        self._shape_obs = (N, self.height, self.width, P)
+        self._shape_mask = (N, HW, 78)
+        self._shape_act = (N, HW, 7)
+        self._d_actions = torch.zeros(self._shape_act, dtype=torch.int32, device=self.device)
+        self._d_mask: Optional[torch.Tensor] = None  # mask of the current state when valid
+        self._mask_valid = False
+        self._pending_actions: Optional[torch.Tensor] = None
+        self._h_actions = torch.zeros(self._shape_act, dtype=torch.int32).pin_memory()
+        self._rw_t = torch.as_tensor(self.reward_weight, dtype=torch.float64, device=self.device)
+        self._host_ring = {}  # name -> [pinned tensors], cursor
+        self.source_unit_mask = None
+        self._closed = False
+        self._sample_seed = int(seed)
+
+    # ------------------------------------------------------------------------------ helpers
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _new(self, shape, dtype):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def _to_host(self, name: str, t: torch.Tensor) -> np.ndarray:
+        """Device tensor -> NumPy through pinned memory.  zero_copy: a view of one of two
+        alternating pinned buffers; otherwise a fresh array (the reference's np.array copy)."""
+        ring = self._host_ring.get(name)
+        if ring is None:
+            k = 2 if self.zero_copy else 1
+            ring = [[torch.empty(t.shape, dtype=t.dtype).pin_memory() for _ in range(k)], 0]
+            self._host_ring[name] = ring
+        bufs, cur = ring
+        buf = bufs[cur % len(bufs)]
+        ring[1] = cur + 1
+        buf.copy_(t, non_blocking=True)
+        return buf
+
+    def _finish_host(self, *bufs):
+        torch.cuda.current_stream(self.device).synchronize()
+        out = []
+        for b in bufs:
+            a = b.numpy()
+            out.append(a if self.zero_copy else a.copy())
+        return out
+
+    def _check_open(self):
+        if self._closed:
+            raise RuntimeError("environment is closed")
+
+    # ------------------------------------------------------------------------------ API
+    def reset(self):
+        """JNIGridnetVecClient.reset + _encode_obs (vec_env.py:278-282): (N,H,W,P) observations."""
+        self._check_open()
+        obs = self._new(self._shape_obs, self._t_dtype)
+        mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.mrts_reset(self._h, _ptr(obs), _ptr(mask), self._stream()))
+        self._d_mask, self._mask_valid = mask, mask is not None
+        if self.return_torch:
+            return obs
+        (o,) = self._finish_host(self._to_host("obs", obs))
+        return o
+
+    def get_action_mask(self):
+        """vec_env.py:1091-1101: (N, H*W, 78) mask of the current state; also refreshes
+        ``source_unit_mask`` (N, H*W)."""
+        self._check_open()
+        if not self._mask_valid:
+            mask = self._new(self._shape_mask, self._t_dtype)
+            with torch.cuda.device(self.device):
+                _capi.check(self._lib.mrts_get_masks(self._h, _ptr(mask), self._stream()))
+            self._d_mask, self._mask_valid = mask, True
+        mask = self._d_mask
+        if self.return_torch:
+            # a unit that may act always has NOOP legal (Unit.java:519): entry 0 of its row == masks[y][x][0]
+            self.source_unit_mask = mask[:, :, 0]
+            return mask
+        (m,) = self._finish_host(self._to_host("mask", mask))
+        self.source_unit_mask = m[:, :, 0]
+        return m
+
+    def step_async(self, actions):
+        """vec_env.py:968-984.  ``actions``: anything reshapeable to (N, H*W, 7), NumPy or torch
+        (host or device), any integer dtype.  The reference forwards only the rows of cells whose
+        ``source_unit_mask`` is 1; the device decode applies the same rule to the current state
+        (PlayerAction.java:407), so the full grid is uploaded as is."""
+        self._check_open()
+        if isinstance(actions, torch.Tensor):
+            a = actions.reshape(self._shape_act)
+            if a.device.type == "cuda":
+                a = a.to(device=self.device, dtype=torch.int32).contiguous()
+            else:
+                self._h_actions.copy_(a)
+                self._d_actions.copy_(self._h_actions, non_blocking=True)
+                a = self._d_actions
+        else:
+            a = np.asarray(actions).reshape(self._shape_act)
+            np.copyto(self._h_actions.numpy(), a, casting="unsafe")
+            self._d_actions.copy_(self._h_actions, non_blocking=True)
+            a = self._d_actions
+        self._pending_actions = a
+
+    def step_wait(self):
+        """vec_env.py:1001-1057: (obs, reward @ reward_weight, done[:, 0], infos)."""
+        self._check_open()
+        if self._pending_actions is None:
+            raise RuntimeError("step_wait() without step_async()")
+        a = self._pending_actions
+        self._pending_actions = None
+        N = self.num_envs
+        obs = self._new(self._shape_obs, self._t_dtype)
+        mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
+        raw = self._new((N, 6), torch.float64)
+        done = self._new((N,), torch.uint8)
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.mrts_step(self._h, _ptr(a), _ptr(obs), _ptr(mask), _ptr(raw), _ptr(done), self._stream()))
+        self._d_mask, self._mask_valid = mask, mask is not None
+        if self.return_torch:
+            if not self.reward_shaping:
+                raw[:, 1:] = 0
+            return obs, raw @ self._rw_t, done.bool(), _LazyInfos(raw)
+        o, r, d = self._finish_host(self._to_host("obs", obs), self._to_host("raw", raw), self._to_host("done", done))
+        reward = r
+        if not self.reward_shaping:
+            reward[:, 1:] = 0
+        infos = [{"raw_rewards": item} for item in reward]
+        return o, reward @ self.reward_weight, d.astype(np.bool_), infos
+
+    def step(self, ac):
+        self.step_async(ac)
+        return self.step_wait()
+
+    def sample_actions(self, seed: Optional[int] = None) -> torch.Tensor:
+        """Device-side masked-uniform random policy for the current state (the sampling loop of the
+        reference's hello_world.py:27-67): returns the (N, H*W, 7) int32 device tensor."""
+        self._check_open()
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.mrts_sample_actions(self._h, _ptr(self._d_actions), C.c_uint64(self._sample_seed if seed is None else seed), self._stream()))
+        return self._d_actions
+
+    def getattr_depth_check(self, name, already_found):
+        if hasattr(self, name) and already_found:
+            return "{0}.{1}".format(type(self).__module__, type(self).__name__)
+        return None
+
+    def render(self, mode="human"):
+        """The reference renders with Java2D (J/tests/JNIGridnetClient.java:144-161); there is no
+        graphics stack on the target machines: unavailable."""
+        raise NotImplementedError("render() needs the reference's Java2D path: unavailable on this box")
+
+    def close(self):
+        if not self._closed and getattr(self, "_h", None):
+            self._lib.mrts_destroy(self._h)
+            self._h = None
+        self._closed = True
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    # ------------------------------------------------------------------------------ cross-checks
+    def export_state(self, game: int):
+        """(hdr5, rows12) of one game, see mrts_export_state in include/mrts_b200.h."""
+        cap = self._lib.mrts_unit_capacity(self._h)
+        hdr = np.zeros(5, np.int32)
+        rows = np.zeros((cap, 12), np.int32)
+        n = _capi.check(self._lib.mrts_export_state(self._h, game, hdr.ctypes.data_as(C.c_void_p), rows.ctypes.data_as(C.c_void_p), cap, self._stream()))
+        return hdr, rows[:n].copy()
+
+
+class _LazyInfos(Sequence):
+    """``infos`` of the torch mode: behaves like the reference's list of ``{"raw_rewards": (6,)}``
+    dicts but only materialises an entry (one device read) when a wrapper indexes it."""
+
+    def __init__(self, raw: torch.Tensor):
+        self.raw = raw
+
+    def __len__(self):
+        return self.raw.shape[0]
+
+    def __getitem__(self, i):
+        return {"raw_rewards": self.raw[i]}
