@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""Throughput of the vectorised MicroRTS environment step (BASELINE.json metric: env-steps/s
+including observation + mask + reward, and achieved HBM GB/s against the measured peak).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--envs E] [--dtype int32|uint8]
+  python bench.py --impl reference ...      # the CPU restatement of the reference path (oracle/) on host cores
+
+One "step" = one pass of the hot path over one slab of environments: mrts_step_ex =
+JNIGridnetVecClient.gameStep fused with getMasks, writing obs (N,H,W,P), mask (N,HW,78), raw
+rewards (N,6) and dones (N,) to HBM.  One env-step = one player view advanced one frame.
+`value` times that with actions already resident in HBM (drawn on the device by the fused
+masked-uniform sampler); `e2e` times the reference-facing class with HOST buffers: actions
+host->device, observation / mask / rewards / dones device->host every step.
+Multi-GPU: one process per GPU (torchrun), independent slabs, no collective in the step path
+(weak scaling); NCCL is used only for the start/stop barrier and the max-over-ranks time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from tests.common import MAP_8, MAP_16, MAP_32, MAP_64  # noqa: E402  (map names only)
+
+# name: (map, planes, envs per GPU, fraction self-play, bots, partial_obs, max_steps, description)
+WORKLOADS = {
+    "cfg2_rollout16": (MAP_16, 29, 24576, 0.0, ("passiveAI", "workerRushAI"), False, 2000,
+                       "ppo_gridnet rollout shape x1024: 16x16 basesWorkers16x16A, bot envs, half vs passiveAI half vs workerRushAI"),
+    "cfg1_selfplay16": (MAP_16, 29, 32768, 1.0, (), False, 2000, "16x16 basesWorkers16x16A self-play"),
+    "cfg3_selfplay8": (MAP_8, 29, 65536, 1.0, (), False, 2000, "8x8 basesWorkers8x8 self-play, 65,536 envs per GPU"),
+    "cfg4_partial32": (MAP_32, 31, 16384, 1.0, (), True, 2000, "32x32 BWDistantResources32x32 self-play, partial_obs, 16,384 envs per GPU"),
+    "cfg5_bloodbath64": (MAP_64, 29, 2048, 1.0, (), False, 2000, "64x64 (4)BloodBath.scmB self-play"),
+}
+DEFAULT_WORKLOAD = "cfg2_rollout16"
+
+
+def algorithmic_bytes(hw, planes, elem):
+    """B = obs + mask + actions_in + 6*8 + 1 per env-step, at the stored dtypes."""
+    return hw * planes * elem + hw * 78 * elem + hw * 7 * 4 + 49
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:  # noqa: BLE001
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:  # noqa: BLE001
+                self.proc.kill()
+        sm, mx, reasons = [], 0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload_setup(name, envs):
+    mp, planes, n_default, frac_sp, bots, partial, max_steps, desc = WORKLOADS[name]
+    n = envs or n_default
+    nsp = int(n * frac_sp) // 2 * 2
+    nbot = n - nsp
+    bot_names = [bots[i * len(bots) // nbot] for i in range(nbot)] if nbot else []
+    return dict(map=mp, planes=planes, n=n, nsp=nsp, nbot=nbot, bot_names=bot_names, partial=partial, max_steps=max_steps, desc=desc)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (oracle/, a C++ restatement of the reference's Java path -- the JVM/JPype
+# reference itself cannot run on this image) on the host cores.  The only place besides tests/ and
+# smoke() that executes oracle/ code, and only as the thing compared against, never shipped.
+# ------------------------------------------------------------------------------------------------
+def cpu_run(wl, n_envs, steps, warmup, budget_s, threads):
+    from oracle.oracle_py import OracleVecEnv
+    from tests.common import sample_actions, templates_for
+
+    nsp = int(n_envs * (wl["nsp"] / wl["n"])) // 2 * 2
+    nbot = n_envs - nsp
+    ids = [{"passiveAI": 0, "workerRushAI": 1}[wl["bot_names"][i * wl["nbot"] // nbot]] for i in range(nbot)] if nbot else []
+    env = OracleVecEnv(nsp, nbot, wl["max_steps"], wl["partial"], templates_for([wl["map"]] * n_envs), ids, threads=threads)
+    rng = np.random.default_rng(0)
+    obs = env.reset()
+    out = (obs, np.zeros((n_envs, 6)), np.zeros(n_envs, np.uint8))
+    spent, done_steps, per_step = 0.0, 0, []
+    for t in range(warmup + steps):
+        t0 = time.perf_counter()
+        m, _ = env.get_masks()
+        t1 = time.perf_counter()
+        a = sample_actions(m, rng)  # the policy stand-in: NOT timed
+        t2 = time.perf_counter()
+        env.step(a, out)
+        t3 = time.perf_counter()
+        if t >= warmup:
+            dt = (t1 - t0) + (t3 - t2)
+            spent += dt
+            per_step.append(dt)
+            done_steps += 1
+            if budget_s and spent > budget_s:
+                break
+    return n_envs * done_steps / spent, done_steps, spent
+
+
+def cpu_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:  # noqa: BLE001
+        return os.cpu_count() or 1
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = workload_setup(args.workload, args.envs)
+    cores = cpu_cores()
+    n_cpu = args.cpu_envs
+    v, k, spent = cpu_run(wl, n_cpu, args.steps, args.warmup, 150.0, cores)
+    hw = {MAP_8: 64, MAP_16: 256, MAP_32: 1024, MAP_64: 4096}[wl["map"]]
+    sample = f"{n_cpu} envs of the workload per step, {k} timed steps ({spent:.1f} s), get_masks + step timed, action sampling excluded"
+    line = {
+        "impl": "reference", "metric": "env-steps/sec incl. obs+mask+reward", "value": v, "unit": "env-steps/s", "n_gpus": args.gpus,
+        "steps": k, "warmup": args.warmup, "ms_per_step": 1e3 * spent / max(k, 1), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32", "data": "synthetic (real reference maps, seeded masked-uniform actions)",
+        "config": {"workload": args.workload, "description": wl["desc"], "map": wl["map"], "envs_per_step": n_cpu, "cells": hw},
+        "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample,
+                         "note": "C++ restatement of the reference's Java path (oracle/); the JVM/JPype reference is unavailable on this box"},
+        "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def gpu_arm(args):
+    import ctypes as C
+
+    import torch
+
+    from microrts_py_b200 import _capi, microrts_ai
+    from microrts_py_b200.envs import MicroRTSGridModeVecEnv
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    wl = workload_setup(args.workload, args.envs)
+    N, nsp, nbot = wl["n"], wl["nsp"], wl["nbot"]
+    np_dtype = np.int32 if args.dtype == "int32" else np.uint8
+    elem = np.dtype(np_dtype).itemsize
+    ai2s = [getattr(microrts_ai, b) for b in wl["bot_names"]]
+    env = MicroRTSGridModeVecEnv(nsp, nbot, partial_obs=wl["partial"], max_steps=wl["max_steps"], ai2s=ai2s, map_paths=[wl["map"]],
+                                 device=local, dtype=np_dtype, return_torch=True, seed=1000 + rank)
+    H, Wd, Pn = env.height, env.width, sum(env.num_planes)
+    HW = H * Wd
+    L = env._lib
+    dev = env.device
+    t_dtype = torch.int32 if elem == 4 else torch.uint8
+    obs = torch.empty((N, H, Wd, Pn), dtype=t_dtype, device=dev)
+    mask = torch.empty((N, HW, 78), dtype=t_dtype, device=dev)
+    rew = torch.empty((N, 6), dtype=torch.float64, device=dev)
+    done = torch.empty((N,), dtype=torch.uint8, device=dev)
+    actions = torch.zeros((N, HW, 7), dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev)
+    sp = C.c_void_p(stream.cuda_stream)
+
+    io = _capi.StepIOC()
+    io.actions, io.obs, io.mask, io.reward, io.done = actions.data_ptr(), obs.data_ptr(), mask.data_ptr(), rew.data_ptr(), done.data_ptr()
+    io.next_actions, io.seed = actions.data_ptr(), 1000 + rank
+
+    def step():
+        _capi.check(L.mrts_step_ex(env._h, C.byref(io), sp))
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    _capi.check(L.mrts_reset(env._h, obs.data_ptr(), mask.data_ptr(), sp))
+    _capi.check(L.mrts_sample_actions(env._h, actions.data_ptr(), C.c_uint64(1000 + rank), sp))
+    # spread the games over episode phases so that the timed steps see a mix of early / mid / late states
+    for _ in range(args.prewarm):
+        step()
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    dones = torch.zeros((), dtype=torch.int64, device=dev)
+    ev[0].record(stream)
+    for k in range(args.steps):
+        step()
+        ev[k + 1].record(stream)
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+    total_ms = ev[0].elapsed_time(ev[-1])
+    per_launch = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms_max = float(t.item())
+    units_mean = float(mask[:, :, 0].sum().item()) / N  # units that may act per view, end state
+
+    # ---------------- end to end: the reference-facing class with HOST buffers
+    e2e = e2e_run(args, env, wl, rank, dist, dev)
+
+    if rank == 0:
+        B = algorithmic_bytes(HW, Pn, elem)
+        peak, peak_src = measured_peak()
+        kern_ms = float(np.mean(per_launch))
+        achieved = B * N / (kern_ms * 1e-3) / 1e9
+        value = N * world * args.steps / (total_ms_max * 1e-3)
+        cores = cpu_cores()
+        cpu_v, cpu_k, cpu_spent = cpu_run(wl, args.cpu_envs, 10 ** 9, 1, args.cpu_budget, cores) if (world == 1 and args.cpu_budget > 0) else (None, 0, 0.0)
+        line = {
+            "metric": "env-steps/sec incl. obs+mask+reward", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.dtype, "data": "synthetic (real reference maps; actions drawn on the device by the fused masked-uniform sampler)",
+            "config": {"workload": args.workload, "description": wl["desc"], "map": wl["map"], "envs_per_gpu": N, "selfplay_views": nsp, "bot_envs": nbot,
+                       "partial_obs": wl["partial"], "max_steps": wl["max_steps"], "prewarm_steps": args.prewarm, "l2": "outputs per step (%.2f GB) exceed the 126 MB L2; no flush needed" % (B * N / 1e9),
+                       "mean_acting_units_per_view": units_mean, "threads_per_game": L.mrts_threads_per_game(env._h), "smem_per_game": L.mrts_smem_bytes(env._h)},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "mrts_pass_kernel", "bytes_per_env_step": B, "env_steps_per_launch": N, "kernel_ms": kern_ms, "peak_source": peak_src},
+            "e2e": e2e, "gpu_launches": args.steps, "clocks": clk,
+        }
+        if cpu_v is not None:
+            line["cpu_baseline"] = {"value": cpu_v, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                                    "sample": f"{args.cpu_envs} envs of the workload, {cpu_k} steps ({cpu_spent:.1f} s), get_masks + step timed, action sampling excluded"}
+        print(json.dumps(line), flush=True)
+    env.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def e2e_run(args, env_dev, wl, rank, dist, dev):
+    """The call a user of the reference makes (ppo_gridnet.py:459-480 loop shape): get_action_mask()
+    -> NumPy, policy output -> NumPy, step(actions) -> NumPy obs / reward / done.  Host buffers are
+    pinned; every step moves the actions host->device and obs + mask + raw rewards + dones (and the
+    device policy's sampled actions, as `action.cpu().numpy()` does) device->host."""
+    import torch
+
+    from microrts_py_b200 import microrts_ai
+    from microrts_py_b200.envs import MicroRTSGridModeVecEnv
+
+    n = min(wl["n"], args.e2e_envs)
+    nsp = int(n * (wl["nsp"] / wl["n"])) // 2 * 2
+    nbot = n - nsp
+    ai2s = [getattr(microrts_ai, wl["bot_names"][i * wl["nbot"] // nbot]) for i in range(nbot)] if nbot else []
+    np_dtype = np.int32 if args.dtype == "int32" else np.uint8
+    env = MicroRTSGridModeVecEnv(nsp, nbot, partial_obs=wl["partial"], max_steps=wl["max_steps"], ai2s=ai2s, map_paths=[wl["map"]],
+                                 device=dev.index, dtype=np_dtype, zero_copy=True, seed=77 + rank)
+    a_host = torch.zeros((n, env.height * env.width, 7), dtype=torch.int32).pin_memory()
+    env.reset()
+    mask = env.get_action_mask()
+    steps = max(3, args.steps // 4)
+
+    def one():
+        a_dev = env.sample_actions()           # policy stand-in, on the device
+        a_host.copy_(a_dev, non_blocking=True)  # action.cpu().numpy()
+        torch.cuda.current_stream(dev).synchronize()
+        obs, r, d, infos = env.step(a_host.numpy())
+        m = env.get_action_mask()
+        return obs, m, r, d
+
+    for _ in range(3):
+        one()
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        obs, m, r, d = one()
+    torch.cuda.synchronize(dev)
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    world = 1
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        world = dist.get_world_size()
+    dt = float(t.item())
+    h2d = a_host.numel() * 4
+    d2h = obs.nbytes + m.nbytes + n * 6 * 8 + n + a_host.numel() * 4
+    env.close()
+    return {"value": n * world * steps / dt, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "envs_per_gpu": n, "steps": steps,
+            "ms_per_step": 1e3 * dt / steps, "api": "MicroRTSGridModeVecEnv(zero_copy=True).step/get_action_mask with NumPy in/out (pinned host buffers)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's)")
+    ap.add_argument("--dtype", default="int32", choices=["int32", "uint8"])
+    ap.add_argument("--prewarm", type=int, default=300, help="untimed steps that spread the games over episode phases")
+    ap.add_argument("--cpu-envs", type=int, default=1024)
+    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg (0 = skip)")
+    ap.add_argument("--e2e-envs", type=int, default=8192)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps == 200 and args.warmup == 20:
+            args.steps, args.warmup = 30, 3
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

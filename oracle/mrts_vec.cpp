@@ -79,15 +79,32 @@ void VecEnv::reset(int32_t* obs) {
 
 void VecEnv::get_masks(int32_t* mask78, int32_t* source_unit_mask) {
     const int HW = H * W;
-    std::vector<int32_t> m79((size_t)HW * 79);
-    for (int e = 0; e < N; e++) {
-        const GameState& gs = e < num_selfplay ? selfplay[e / 2].gs : botgames[e - num_selfplay].gs;
-        int player = e < num_selfplay ? (e % 2) : 0;
-        build_masks(gs, player, m79.data());  // always the TRUE state (JNIGridnetClient.java:203-216)
-        for (int c = 0; c < HW; c++) {
-            source_mask[(size_t)e * HW + c] = m79[(size_t)c * 79];
-            if (mask78) std::memcpy(mask78 + ((size_t)e * HW + c) * 78, &m79[(size_t)c * 79 + 1], 78 * sizeof(int32_t));
+    auto run = [&](int e0, int e1) {
+        std::vector<int32_t> m79((size_t)HW * 79);
+        for (int e = e0; e < e1; e++) {
+            const GameState& gs = e < num_selfplay ? selfplay[e / 2].gs : botgames[e - num_selfplay].gs;
+            int player = e < num_selfplay ? (e % 2) : 0;
+            build_masks(gs, player, m79.data());  // always the TRUE state (JNIGridnetClient.java:203-216)
+            for (int c = 0; c < HW; c++) {
+                source_mask[(size_t)e * HW + c] = m79[(size_t)c * 79];
+                if (mask78) std::memcpy(mask78 + ((size_t)e * HW + c) * 78, &m79[(size_t)c * 79 + 1], 78 * sizeof(int32_t));
+            }
         }
+    };
+    if (threads <= 1 || N < 2 * threads) {
+        run(0, N);
+    } else {  // envs are independent: the CPU baseline spreads them over host threads
+        std::atomic<int> next(0);
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; t++)
+            pool.emplace_back([&]() {
+                for (;;) {
+                    int e0 = next.fetch_add(16);
+                    if (e0 >= N) break;
+                    run(e0, std::min(N, e0 + 16));
+                }
+            });
+        for (auto& th : pool) th.join();
     }
     if (source_unit_mask) std::memcpy(source_unit_mask, source_mask.data(), source_mask.size() * sizeof(int32_t));
     source_mask_valid = true;

@@ -19,3 +19,26 @@ def golden_traces():
 
     with gzip.open(os.path.join(ROOT, "tests", "golden", "traces.json.gz"), "rt") as f:
         return json.load(f)
+
+
+def _backend_params():
+    return [
+        pytest.param("oracle", id="oracle"),
+        pytest.param("hostsim", id="hostsim"),
+        pytest.param("cuda", id="cuda", marks=pytest.mark.gpu),
+    ]
+
+
+@pytest.fixture(params=_backend_params())
+def backend(request):
+    """Engine under test: the oracle and the host build of the device headers run on CPU; "cuda" is
+    the product (libmrts_b200.so through MicroRTSGridModeVecEnv) and needs the B200."""
+    return request.param
+
+
+@pytest.fixture(scope="session")
+def known_answers():
+    import json
+
+    with open(os.path.join(ROOT, "tests", "golden", "known_answers.json")) as f:
+        return json.load(f)

@@ -1,0 +1,145 @@
+"""GPU-only checks of the product surface beyond the reference-shaped NumPy path: torch
+(device-resident) mode, uint8 element mode, the device action sampler, un-fused masks, golden
+trace replay through the raw engine entry points, and full-size property checks."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from microrts_py_b200 import microrts_ai
+from tests.common import GROUPS, MAP_8, MAP_16, MAP_32, sample_actions, templates_for
+
+pytestmark = pytest.mark.gpu
+P, W = microrts_ai.passiveAI, microrts_ai.workerRushAI
+
+
+def _env(*a, **k):
+    from microrts_py_b200.envs import MicroRTSGridModeVecEnv
+
+    return MicroRTSGridModeVecEnv(*a, **k)
+
+
+def _oracle(nsp, ais, mp, partial=False, max_steps=2000):
+    from oracle.oracle_py import OracleVecEnv
+
+    n = nsp + len(ais)
+    return OracleVecEnv(nsp, len(ais), max_steps, partial, templates_for([mp] * n), [a(None).ai_id for a in ais])
+
+
+@pytest.mark.parametrize("mode", ["torch", "uint8", "unfused", "zero_copy"])
+def test_modes_match_oracle(mode):
+    import torch
+
+    kw = dict(torch=dict(return_torch=True), uint8=dict(dtype=np.uint8), unfused=dict(fuse_mask=False), zero_copy=dict(zero_copy=True))[mode]
+    ais = [P, W]
+    env = _env(4, 2, max_steps=150, ai2s=ais, map_paths=[MAP_16], **kw)
+    ref = _oracle(4, ais, MAP_16, max_steps=150)
+    rng = np.random.default_rng(7)
+
+    def host(x):
+        return x.cpu().numpy() if isinstance(x, torch.Tensor) else np.asarray(x)
+
+    np.testing.assert_array_equal(host(env.reset()).astype(np.int32), ref.reset())
+    for t in range(320):
+        m = host(env.get_action_mask())
+        m_ref, src_ref = ref.get_masks()
+        np.testing.assert_array_equal(m.astype(np.int32), m_ref, err_msg=f"mask {t}")
+        np.testing.assert_array_equal(host(env.source_unit_mask).astype(np.int32), src_ref)
+        a = sample_actions(m_ref, rng, 0.05)
+        act = torch.as_tensor(a.astype(np.int64)).cuda() if mode == "torch" else a.astype(np.int64)
+        o, r, d, infos = env.step(act)
+        o2, r2, d2 = ref.step(a)
+        np.testing.assert_array_equal(host(o).astype(np.int32), o2, err_msg=f"obs {t}")
+        np.testing.assert_array_equal(host(d).astype(np.uint8), d2)
+        np.testing.assert_array_equal(host(infos[3]["raw_rewards"]), r2[3])
+        np.testing.assert_allclose(host(r), r2 @ env.reward_weight, rtol=0, atol=1e-12)
+    env.close()
+
+
+def test_device_sampler_draws_from_the_mask_and_is_reproducible():
+    import torch
+
+    runs = []
+    for rep in range(2):
+        env = _env(64, 8, max_steps=100, ai2s=[P, W] * 4, map_paths=[MAP_8], return_torch=True, seed=5)
+        env.reset()
+        hist = []
+        for t in range(150):
+            m = env.get_action_mask()
+            a = env.sample_actions()
+            src = m[:, :, 0].bool()
+            assert src.any()
+            av, mv = a[src].long(), m[src]
+            for k, (lo, hi) in enumerate(GROUPS):
+                grp = mv[:, lo:hi]
+                chosen = torch.gather(grp, 1, av[:, k : k + 1]).squeeze(1)
+                empty = grp.sum(1) == 0
+                assert bool(((chosen == 1) | (empty & (av[:, k] == 0))).all()), f"component {k} step {t}"
+            o, r, d, _ = env.step(a)
+            hist.append((o.sum().item(), r.sum().item(), d.sum().item()))
+        runs.append(hist)
+        env.close()
+    assert runs[0] == runs[1]
+    assert any(h[2] > 0 for h in runs[0])
+
+
+def test_golden_trace_replay_on_device(golden_traces):
+    """TestTracesIntegrity.java:72-126 strengthened to state equality, through mrts_debug_issue /
+    mrts_debug_cycle on the GPU: a subset of the reference's 280 traces incl. the config maps."""
+    from microrts_py_b200 import _capi
+    from microrts_py_b200.maps import load_map
+
+    L = _capi.lib()
+    want = ("basesWorkers16x16A", "basesWorkers8x8", "BWDistantResources32x32", "BloodBath", "melee", "4x4")
+    picked = [t for t in golden_traces if any(w in t["map"] for w in want)]
+    assert len(picked) >= 8
+    for tr in picked[:24]:
+        tmpl = load_map(tr["map"])
+        cfg, keep = _capi.make_config(2, 0, 100000, False, [tmpl, tmpl], [], none_mode=_capi.NONE_UPSTREAM)
+        h = C.c_void_p()
+        _capi.check(L.mrts_create(C.byref(cfg), C.byref(h)))
+        cap = L.mrts_unit_capacity(h)
+        hdr, rows = np.zeros(5, np.int32), np.zeros((cap, 12), np.int32)
+        time = 0
+        for k, e in enumerate(tr["entries"]):
+            while time < e[0]:
+                _capi.check(L.mrts_debug_cycle(h, 0, None, None))
+                time += 1
+            n = _capi.check(L.mrts_export_state(h, 0, hdr.ctypes.data_as(C.c_void_p), rows.ctypes.data_as(C.c_void_p), cap, None))
+            units = np.asarray(e[3], np.int32).reshape(-1, 6)
+            assert (hdr[0], hdr[1], hdr[2]) == (e[0], e[1], e[2]), f"{tr['map']} entry {k}"
+            np.testing.assert_array_equal(rows[:n, :6], units, err_msg=f"{tr['map']} {tr['ai']} entry {k}")
+            acts = np.asarray(e[4], np.int32).reshape(-1, 6)
+            for p in (0, 1):
+                r7 = np.asarray([[units[a[0]][2], units[a[0]][3], a[1], a[2], a[3], a[4], a[5]] for a in acts if units[a[0]][1] == p], np.int32).reshape(-1, 7)
+                if len(r7):
+                    _capi.check(L.mrts_debug_issue(h, 0, r7.ctypes.data_as(C.c_void_p), len(r7), None))
+        L.mrts_destroy(h)
+
+
+@pytest.mark.parametrize("mp,nsp,partial", [(MAP_8, 65536, False), (MAP_32, 2048, True)])
+def test_full_size_properties(mp, nsp, partial):
+    """BASELINE-sized slabs: size-independent properties (one plane per group per cell, mask rows
+    only at source cells, NOOP always legal there, identical games stay identical under identical
+    actions) plus oracle equality on a subsample of envs fed the same actions."""
+    import torch
+
+    env = _env(nsp, 0, partial_obs=partial, max_steps=64, map_paths=[mp], return_torch=True, seed=3)
+    groups = 7 if partial else 6
+    obs = env.reset()
+    sub = 8
+    ref = _oracle(sub, [], mp, partial, max_steps=64)
+    np.testing.assert_array_equal(obs[:sub].cpu().numpy(), ref.reset())
+    for t in range(100):
+        m = env.get_action_mask()
+        assert bool((obs.sum(3) == groups).all())
+        src = m[:, :, 0] == 1
+        assert bool((m.sum(2)[~src] == 0).all())
+        a = env.sample_actions().clone()
+        a[sub:2 * sub] = a[:sub]  # a second group of games fed the first group's actions
+        o_ref, r_ref, d_ref = ref.step(a[:sub].cpu().numpy())
+        obs, r, d, infos = env.step(a)
+        np.testing.assert_array_equal(obs[:sub].cpu().numpy(), o_ref, err_msg=f"step {t}")
+        np.testing.assert_array_equal(infos.raw[:sub].cpu().numpy(), r_ref)
+        assert torch.equal(obs[:sub], obs[sub:2 * sub]) and torch.equal(d[:sub], d[sub:2 * sub])
+    env.close()
