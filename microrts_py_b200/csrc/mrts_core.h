@@ -42,6 +42,8 @@ enum { MB_TYPE = 0, MB_MOVE = 6, MB_HARVEST = 10, MB_RETURN = 14, MB_PDIR = 18, 
 MRTS_HD void mset(Mask78& m, int b) { m.w[b >> 5] |= 1u << (b & 31); }
 MRTS_HD bool mget(const Mask78& m, int b) { return (m.w[b >> 5] >> (b & 31)) & 1u; }
 
+MRTS_HD int astar_bytes(int W, int HW) { return ((3 * HW + (HW + W + (HW / W) + 2)) * 2 + HW * 2 + 15) & ~15; }
+
 struct Sim {
     // ---- configuration
     int W, H, HW, cap;
@@ -61,7 +63,8 @@ struct Sim {
     uint32_t* bitsB;
     uint32_t* bitsC;
     int nbits_words;
-    int16_t* astar;  // bot games: A* scratch, 5 arrays of (HW+1) int16 + HW bytes
+    int16_t* astar;  // bot games: A* scratch (astar_bytes)
+    int astar_gen;   // search counter (stamp generation)
     // ---- per-step results
     int rew[2][6];   // integer reward terms per player view (exact small integers)
     int gameover, winner;
@@ -667,80 +670,89 @@ struct Sim {
     }
 
     // ---- A*, J/ai/abstraction/pathfinding/AStarPathFinding.java:52-79,104-138,175-295
+    // The reference keeps the open list as an array sorted by f (largest first), pops from the
+    // tail and inserts a new node right after the last entry (scanning from the tail) whose f is
+    // >= the new one (addToOpen, :104-138).  That order is exactly "smallest f first, newest first
+    // among equal f", i.e. one LIFO stack per f value, and a position is pushed at most once
+    // (inOpenOrClosed, :60).  The stacks are intrusive lists threaded through `next`:
+    // push and pop are O(1) where the reference shifts the arrays.
     struct AStarBuf {
-        int16_t *open, *heur, *parents, *cost, *closed;
-        uint8_t* inoc;
-        int openinsert;
+        int16_t *cost, *parent, *next, *head;  // cost/parent/next per cell; head per f value (-1 = empty)
+        uint16_t* stamp;                       // == generation: cell was pushed during this search
     };
+    MRTS_HD int astar_nf() const { return HW + W + H + 2; }
     MRTS_HD AStarBuf astar_buf() const {
         AStarBuf b;
-        b.open = astar;
-        b.heur = b.open + (HW + 1);
-        b.parents = b.heur + (HW + 1);
-        b.cost = b.parents + (HW + 1);
-        b.closed = b.cost + (HW + 1);
-        b.inoc = (uint8_t*)(b.closed + (HW + 1));
-        b.openinsert = 0;
+        b.cost = astar;
+        b.parent = b.cost + HW;
+        b.next = b.parent + HW;
+        b.head = b.next + HW;
+        b.stamp = (uint16_t*)(b.head + astar_nf());
         return b;
     }
-    MRTS_HD static void astar_add(AStarBuf& b, int newPos, int oldPos, int h) {
-        b.cost[newPos] = (int16_t)(b.cost[oldPos] + 1);
-        const int f = h + b.cost[newPos];
-        int i = b.openinsert - 1;
-        while (i >= 0 && b.heur[i] + b.cost[b.open[i]] < f) i--;  // first i from the tail with f_i >= f_new
-        for (int j = b.openinsert; j > i + 1; j--) {
-            b.open[j] = b.open[j - 1];
-            b.heur[j] = b.heur[j - 1];
-            b.parents[j] = b.parents[j - 1];
-        }
-        b.open[i + 1] = (int16_t)newPos;
-        b.heur[i + 1] = (int16_t)h;
-        b.parents[i + 1] = (int16_t)oldPos;
-        b.openinsert++;
-        b.inoc[newPos] = 1;
+    // once per game pass, by the whole thread group, before the leader runs (the region is scratch)
+    MRTS_HD void astar_init(int tid, int nth) {
+        AStarBuf b = astar_buf();
+        for (int k = tid; k < astar_nf(); k += nth) b.head[k] = -1;
+        for (int k = tid; k < HW; k += nth) b.stamp[k] = 0;
+        astar_gen = 0;
     }
     // findPathToPositionInRange: direction of the first move, or -1 (null)
     MRTS_HD int astar_first_move(int i, int targetpos, int range, int vp) {
-        AStarBuf b = astar_buf();
+        const AStarBuf b = astar_buf();
         const Unit& st = u[i];
-        for (int k = 0; k < HW; k++) {
-            b.closed[k] = -1;
-            b.inoc[k] = 0;
-        }
+        const uint16_t gen = (uint16_t)++astar_gen;
         const int tx = targetpos % W, ty = targetpos / W;
         const int sq = range * range;
         const int startPos = st.y * W + st.x;
-        b.open[0] = (int16_t)startPos;
-        b.heur[0] = (int16_t)(iabs(st.x - tx) + iabs(st.y - ty));
-        b.parents[0] = (int16_t)startPos;
-        b.inoc[startPos] = 1;
+        const int h0 = iabs(st.x - tx) + iabs(st.y - ty);
+        b.parent[startPos] = (int16_t)startPos;
         b.cost[startPos] = 0;
-        b.openinsert = 1;
+        b.stamp[startPos] = gen;
+        b.next[startPos] = -1;
+        b.head[h0] = (int16_t)startPos;
+        int fmin = h0, fmax = h0, flo = h0, nopen = 1;
         bool found = false;
-        int pos = 0, parent = 0;
-        while (b.openinsert > 0) {
-            b.openinsert--;
-            pos = b.open[b.openinsert];
-            parent = b.parents[b.openinsert];
-            if (b.closed[pos] != -1) continue;
-            b.closed[pos] = (int16_t)parent;
+        int pos = startPos;
+        while (nopen > 0) {
+            while (b.head[fmin] < 0) fmin++;
+            pos = b.head[fmin];
+            b.head[fmin] = b.next[pos];
+            nopen--;
             const int x = pos % W, y = pos / W;
             if ((x - tx) * (x - tx) + (y - ty) * (y - ty) <= sq) {
                 found = true;
                 break;
             }
-            // free(nbr) = gs.free() unless pre-seeded false by `ru` (bitsC); no need to cache: both are constant here
-            if (y > 0 && !b.inoc[pos - W] && free_cell(x, y - 1, vp) && !bit_get(bitsC, pos - W)) astar_add(b, pos - W, pos, iabs(x - tx) + iabs(y - 1 - ty));
-            if (x < W - 1 && !b.inoc[pos + 1] && free_cell(x + 1, y, vp) && !bit_get(bitsC, pos + 1)) astar_add(b, pos + 1, pos, iabs(x + 1 - tx) + iabs(y - ty));
-            if (y < H - 1 && !b.inoc[pos + W] && free_cell(x, y + 1, vp) && !bit_get(bitsC, pos + W)) astar_add(b, pos + W, pos, iabs(x - tx) + iabs(y + 1 - ty));
-            if (x > 0 && !b.inoc[pos - 1] && free_cell(x - 1, y, vp) && !bit_get(bitsC, pos - 1)) astar_add(b, pos - 1, pos, iabs(x - 1 - tx) + iabs(y - ty));
+            const int g1 = b.cost[pos] + 1;
+            // neighbours in the reference's order: up, right, down, left (:236-262)
+#pragma unroll
+            for (int d = 0; d < 4; d++) {
+                const int nx = x + dir_dx(d), ny = y + dir_dy(d);
+                if (nx < 0 || ny < 0 || nx >= W || ny >= H) continue;
+                const int np = nx + ny * W;
+                if (b.stamp[np] == gen) continue;
+                // free(nbr) = gs.free() unless pre-seeded false by `ru` (bitsC); both are constant during a search
+                if (!free_cell(nx, ny, vp) || bit_get(bitsC, np)) continue;
+                const int f = iabs(nx - tx) + iabs(ny - ty) + g1;
+                b.cost[np] = (int16_t)g1;
+                b.parent[np] = (int16_t)pos;
+                b.stamp[np] = gen;
+                b.next[np] = b.head[f];
+                b.head[f] = (int16_t)np;
+                if (f < fmin) fmin = f;
+                if (f < flo) flo = f;
+                if (f > fmax) fmax = f;
+                nopen++;
+            }
         }
+        for (int f = flo; f <= fmax; f++) b.head[f] = -1;  // leave the stacks empty for the next search
         if (!found) return -1;
-        int last = pos;
+        int last = pos, parent = b.parent[pos];
         while (parent != pos) {
             last = pos;
             pos = parent;
-            parent = b.closed[pos];
+            parent = b.parent[pos];
         }
         if (last == pos + W) return D_DOWN;
         if (last == pos - 1) return D_LEFT;

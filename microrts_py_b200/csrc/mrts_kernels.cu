@@ -42,6 +42,21 @@ __global__ void mrts_pass_kernel(const EnvParams P) {
     game_pass(P, g, (uint8_t*)smem_raw, (int)threadIdx.x, (int)blockDim.x, BlockSync());
 }
 
+// One warp per game, GPB games per block: the group barrier is __syncwarp(), and a block's
+// shared memory is GPB independent per-game regions.  Small maps use this variant: it doubles
+// (vs 64-thread blocks) the number of games whose serial rules phase is in flight per SM.
+struct WarpSync {
+    __device__ __forceinline__ void operator()() const { __syncwarp(); }
+};
+constexpr int GPB = 4;
+__global__ void __launch_bounds__(32 * GPB) mrts_pass_warp_kernel(const EnvParams P, const int smem_per_game) {
+    extern __shared__ uint4 smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * GPB + warp;
+    if (g >= P.n_games) return;
+    game_pass(P, g, (uint8_t*)smem_raw + (size_t)warp * smem_per_game, lane, 32, WarpSync());
+}
+
 // ---- raw engine access (trace replay): one block, one game
 struct DebugArgs {
     int game;
@@ -54,28 +69,10 @@ __global__ void mrts_debug_kernel(const EnvParams P, const DebugArgs A) {
     extern __shared__ uint4 smem_raw[];
     uint8_t* mem = (uint8_t*)smem_raw;
     const int tid = threadIdx.x, nth = blockDim.x;
-    const Layout L = make_layout(P.W, P.HW, P.cap, P.has_bot);
+    const Layout L = layout_of(P);
     Sim s;
-    s.W = P.W;
-    s.H = P.H;
-    s.HW = P.HW;
-    s.cap = P.cap;
-    s.none_mode = P.none_mode;
+    bind_sim(s, P, L, mem, A.game);
     s.partial = 0;
-    s.max_steps = P.max_steps;
-    s.ai = P.game_ai[A.game];
-    s.hdr = (GameHdr*)(mem + L.blob);
-    s.u = (Unit*)(mem + L.blob + 32);
-    s.aa = (AbstractAct*)(mem + L.blob + 32 + P.cap * 32);
-    s.grid = (uint16_t*)(mem + L.grid);
-    s.pa = (PAct*)(mem + L.pa);
-    s.pa2 = (PAct*)(mem + L.pa2);
-    s.npa = s.npa2 = 0;
-    s.nbits_words = L.nbits_words;
-    s.bitsA = (uint32_t*)(mem + L.bits);
-    s.bitsB = s.bitsA + L.nbits_words;
-    s.bitsC = s.bitsB + L.nbits_words;
-    s.astar = (int16_t*)(mem + L.astar);
     const MapTpl tpl = P.maps[P.game_map[A.game]];
     uint8_t* gblob = P.games + (size_t)A.game * P.game_stride;
     copy16<Q16>(mem + L.blob, gblob, 32 + P.cap * 32, tid, nth);
@@ -132,10 +129,8 @@ struct mrts_env {
 
 namespace {
 
-int choose_threads(int HW) {
-    if (HW <= 64) return 32;
-    if (HW <= 256) return 64;
-    if (HW <= 1024) return 128;
+int choose_threads(int HW) {  // 32 = one warp per game (mrts_pass_warp_kernel), otherwise one block per game
+    if (HW <= 1024) return 32;
     return 256;
 }
 
@@ -164,7 +159,10 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     P.next_actions = next_actions;
     P.seed = seed;
     P.counter = next_actions ? e->sample_counter++ : 0;
-    mrts_pass_kernel<<<P.n_games, e->threads, e->smem, (cudaStream_t)stream>>>(P);
+    if (e->threads == 32)
+        mrts_pass_warp_kernel<<<(P.n_games + GPB - 1) / GPB, 32 * GPB, GPB * e->smem, (cudaStream_t)stream>>>(P, e->smem);
+    else
+        mrts_pass_kernel<<<P.n_games, e->threads, e->smem, (cudaStream_t)stream>>>(P);
     CK(cudaGetLastError());
     return MRTS_OK;
 }
@@ -216,13 +214,21 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
 
     e->threads = cfg->threads_per_game > 0 ? cfg->threads_per_game : choose_threads(HW);
     if (e->threads > 1024) e->threads = 1024;
-    e->smem = make_layout(W, HW, cap, P.has_bot).total;
+    if (e->threads < 32 || (e->threads & 31)) {
+        mrts_destroy(e);
+        return fail(MRTS_EINVAL, "threads_per_game must be a multiple of 32");
+    }
+    e->smem = layout_of(P).total;
     int maxsm = 0;
     cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device);
+    if (e->smem > maxsm || (e->threads == 32 && GPB * e->smem > maxsm)) {
+        if (e->threads == 32 && e->smem <= maxsm) e->threads = 64;  // too large for GPB games per block: one block per game
+    }
     if (e->smem > maxsm) {
         mrts_destroy(e);
         return fail(MRTS_EINVAL, "map too large for shared-memory staging");
     }
+    if (GPB * e->smem > 48 * 1024) cudaFuncSetAttribute(mrts_pass_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->threads == 32 ? GPB * e->smem : 48 * 1024);
     if (e->smem > 48 * 1024) {
         cudaFuncSetAttribute(mrts_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
         cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);

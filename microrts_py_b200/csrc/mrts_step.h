@@ -44,17 +44,20 @@ MRTS_HD int blob_bytes(int cap, int has_bot) { return 32 + cap * 32 + (has_bot ?
 struct Layout {
     int blob, grid, words, umask, pa, pa2, bits, astar, misc, total, nbits_words;
 };
-MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot) {
+// Shared-memory plan of one game.  The rules scratch (PlayerActions, reservation bitmaps, A*
+// arrays) is dead once the leader is done, the output scratch (observation words, per-unit
+// legal-action sets) is only written after that: the two share one region.
+MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int nviews = 2) {
     Layout L;
     int o = 0;
     L.blob = o;
     o += blob_bytes(cap, has_bot);
     L.grid = o;
     o += align16(HW * 2);
-    L.words = o;
-    o += align16(2 * HW * 4);
-    L.umask = o;
-    o += align16(cap * 12);
+    L.misc = o;
+    o += 16;
+    const int scratch = o;
+    // ---- rules scratch
     L.pa = o;
     o += align16(cap * (int)sizeof(PAct));
     L.pa2 = o;
@@ -63,29 +66,22 @@ MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot) {
     L.bits = o;
     o += align16(3 * L.nbits_words * 4);
     L.astar = o;
-    o += has_bot ? align16(5 * (HW + 1) * 2 + HW) : 0;
-    L.misc = o;
-    o += 16;
-    L.total = o;
+    o += has_bot ? astar_bytes(W, HW) : 0;
+    const int end_rules = o;
+    // ---- output scratch (aliases the rules scratch)
+    o = scratch;
+    L.words = o;
+    o += align16(nviews * HW * 4);
+    L.umask = o;
+    o += align16(cap * 12);
+    L.total = o > end_rules ? o : end_rules;
     return L;
 }
 
-template <class T>
-MRTS_HD void copy16(void* dst, const void* src, int bytes, int tid, int nth) {  // bytes multiple of 16, both 16-aligned
-    const T* s = (const T*)src;
-    T* d = (T*)dst;
-    const int n = bytes / (int)sizeof(T);
-    for (int i = tid; i < n; i += nth) d[i] = s[i];
-}
-struct alignas(16) Q16 {
-    uint32_t a, b, c, d;
-};
+MRTS_HD Layout layout_of(const EnvParams& P) { return make_layout(P.W, P.HW, P.cap, P.has_bot, P.num_selfplay > 0 ? 2 : 1); }
 
-// SYNC: functor executing a barrier over the game's thread group.
-template <class SYNC>
-MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync) {
-    const Layout L = make_layout(P.W, P.HW, P.cap, P.has_bot);
-    Sim s;
+// point a Sim at one game's shared-memory regions
+MRTS_HD void bind_sim(Sim& s, const EnvParams& P, const Layout& L, uint8_t* mem, int g) {
     s.W = P.W;
     s.H = P.H;
     s.HW = P.HW;
@@ -106,8 +102,28 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     s.bitsB = s.bitsA + L.nbits_words;
     s.bitsC = s.bitsB + L.nbits_words;
     s.astar = (int16_t*)(mem + L.astar);
+    s.astar_gen = 0;
     s.gameover = 0;
     s.winner = -1;
+}
+
+template <class T>
+MRTS_HD void copy16(void* dst, const void* src, int bytes, int tid, int nth) {  // bytes multiple of 16, both 16-aligned
+    const T* s = (const T*)src;
+    T* d = (T*)dst;
+    const int n = bytes / (int)sizeof(T);
+    for (int i = tid; i < n; i += nth) d[i] = s[i];
+}
+struct alignas(16) Q16 {
+    uint32_t a, b, c, d;
+};
+
+// SYNC: functor executing a barrier over the game's thread group.
+template <class SYNC>
+MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync) {
+    const Layout L = layout_of(P);
+    Sim s;
+    bind_sim(s, P, L, mem, g);
     uint32_t* words = (uint32_t*)(mem + L.words);
     uint32_t* umask = (uint32_t*)(mem + L.umask);
     volatile int32_t* misc = (volatile int32_t*)(mem + L.misc);
@@ -151,6 +167,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         if (P.has_bot && naa > 0) copy16<Q16>(s.aa, gblob + 32 + P.cap * 32, align16(naa * 12), tid, nth);
         copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
     }
+    if (P.mode == MODE_STEP && s.ai == AI_WORKER_RUSH) s.astar_init(tid, nth);
     sync();
     scatter_grid();
     sync();

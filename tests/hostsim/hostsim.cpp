@@ -52,7 +52,7 @@ int hs_create(const mrts_config* cfg, hs_env** out) {
     }
     const EnvParams& P = e->S.P;
     e->games.assign((size_t)P.n_games * P.game_stride + 64, 0);
-    e->mem.assign(make_layout(P.W, P.HW, P.cap, P.has_bot).total + 64, 0);
+    e->mem.assign(layout_of(P).total + 64, 0);
     pass(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr);
     *out = e;
     return 0;
