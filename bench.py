@@ -33,6 +33,8 @@ from tests.common import MAP_8, MAP_16, MAP_32, MAP_64  # noqa: E402  (map names
 WORKLOADS = {
     "cfg2_rollout16": (MAP_16, 29, 24576, 0.0, ("passiveAI", "workerRushAI"), False, 2000,
                        "ppo_gridnet rollout shape x1024: 16x16 basesWorkers16x16A, bot envs, half vs passiveAI half vs workerRushAI"),
+    "diag_passive16": (MAP_16, 29, 24576, 0.0, ("passiveAI",), False, 2000, "diagnostic: 16x16 bot envs, all vs passiveAI"),
+    "diag_wrush16": (MAP_16, 29, 24576, 0.0, ("workerRushAI",), False, 2000, "diagnostic: 16x16 bot envs, all vs workerRushAI"),
     "cfg1_selfplay16": (MAP_16, 29, 32768, 1.0, (), False, 2000, "16x16 basesWorkers16x16A self-play"),
     "cfg3_selfplay8": (MAP_8, 29, 65536, 1.0, (), False, 2000, "8x8 basesWorkers8x8 self-play, 65,536 envs per GPU"),
     "cfg4_partial32": (MAP_32, 31, 16384, 1.0, (), True, 2000, "32x32 BWDistantResources32x32 self-play, partial_obs, 16,384 envs per GPU"),
