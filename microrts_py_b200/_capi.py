@@ -18,7 +18,7 @@ from .maps import MapTemplate
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libmrts_b200.so")
+LIB_PATH = os.environ.get("MRTS_B200_LIB") or os.path.join(CSRC, "libmrts_b200.so")  # override: tuning builds only
 
 AI_PASSIVE, AI_WORKER_RUSH = 0, 1
 NONE_UPSTREAM, NONE_FORK = 0, 1

@@ -39,10 +39,42 @@ struct Mask78 {
     uint32_t w[3];
 };
 enum { MB_TYPE = 0, MB_MOVE = 6, MB_HARVEST = 10, MB_RETURN = 14, MB_PDIR = 18, MB_PTYPE = 22, MB_ATTACK = 29 };
-MRTS_HD void mset(Mask78& m, int b) { m.w[b >> 5] |= 1u << (b & 31); }
-MRTS_HD bool mget(const Mask78& m, int b) { return (m.w[b >> 5] >> (b & 31)) & 1u; }
+// no dynamic indexing of w[] (that would put the set in local memory); constant b folds away
+MRTS_HD void mset(Mask78& m, int b) {
+    const uint32_t bit = 1u << (b & 31);
+    const int k = b >> 5;
+    m.w[0] |= k == 0 ? bit : 0u;
+    m.w[1] |= k == 1 ? bit : 0u;
+    m.w[2] |= k == 2 ? bit : 0u;
+}
+MRTS_HD bool mget(const Mask78& m, int b) {
+    const int k = b >> 5;
+    const uint32_t w = k == 0 ? m.w[0] : (k == 1 ? m.w[1] : m.w[2]);
+    return (w >> (b & 31)) & 1u;
+}
 
 MRTS_HD int astar_bytes(int W, int HW) { return ((3 * HW + (HW + W + (HW / W) + 2)) * 2 + HW * 2 + 15) & ~15; }
+
+// Per-step scalars the rules mutate; they live in the game's shared-memory region so that the
+// immutable view below (Sim) can be copied freely into the registers of out-of-line functions.
+struct St {
+    int npa, npa2;   // lengths of pa / pa2
+    int astar_gen;   // search counter (stamp generation)
+    int gameover, winner;
+    int reset;
+    int rew[2][6];   // integer reward terms per player view (exact small integers)
+};
+
+struct Sim;
+// Out-of-line entry points of the big rule functions (one copy of each in the kernel image instead
+// of one per call site: the rules phase is instruction-fetch bound).  `sp` is the game's Sim in
+// shared memory; each copies it into registers first.
+MRTS_HDN int o_astar(const Sim* sp, int i, int targetpos, int range, int vp);
+MRTS_HDN void o_issue_safe(const Sim* sp, PAct* list, int cnt);
+MRTS_HDN void o_decode_actions(const Sim* sp, int player, int vp);
+MRTS_HDN void o_make_view(const Sim* sp, int p);
+MRTS_HDN void o_bot_melee(const Sim* sp, int i, int player, int vp);
+MRTS_HDN void o_fill_with_nones(const Sim* sp, PAct* list, int* cnt, int player, int duration, int vp);
 
 struct Sim {
     // ---- configuration
@@ -56,18 +88,14 @@ struct Sim {
     uint16_t* grid;  // HW cells: unit index, G_NONE or G_WALL
     // ---- leader scratch
     PAct* pa;        // cap entries: PlayerAction being issued
-    int npa;
     PAct* pa2;       // cap entries: the bot's PlayerAction
-    int npa2;
     uint32_t* bitsA; // reservation bitmaps over linear positions -W .. HW+W-1 (bit index pos+W)
     uint32_t* bitsB;
     uint32_t* bitsC;
     int nbits_words;
     int16_t* astar;  // bot games: A* scratch (astar_bytes)
-    int astar_gen;   // search counter (stamp generation)
-    // ---- per-step results
-    int rew[2][6];   // integer reward terms per player view (exact small integers)
-    int gameover, winner;
+    St* st;          // per-step mutable scalars
+    const Sim* self; // where this view is stored for the out-of-line entry points
 
     // ------------------------------------------------------------------ small helpers
     MRTS_HD int nunits() const { return hdr->nunits; }
@@ -206,21 +234,31 @@ struct Sim {
         return m;
     }
 
+    // Unit.canExecuteAction (Unit.java:531-534): is `a` in getUnitActions?  Evaluated directly for the
+    // one action instead of enumerating the whole set (unit_mask); tests/test_engine_units.py checks
+    // the two agree on every (unit, action) of sampled states.
     MRTS_HD bool can_execute(int i, const PAct& a) const {
         if (a.type == T_NONE) return true;  // NONE(noneDuration = ETA(a)) is always in the list
-        Mask78 m = unit_mask(i);
-        const int p = a.param;
+        const Unit& un = u[i];
+        const int t = un.type, pl = un.player, p = a.param;
+        if (a.type == T_ATTACK) {
+            if (!ut_can_attack(t)) return false;
+            const int dx = a.x - un.x, dy = a.y - un.y, r = ut_range(t);
+            if (dx * dx + dy * dy > r * r) return false;
+            const int o = unit_at(a.x, a.y);
+            return o >= 0 && u[o].player >= 0 && u[o].player != pl;
+        }
+        if (p < 0 || p > 3) return false;
+        const int nx = un.x + dir_dx(p), ny = un.y + dir_dy(p);
+        if (nx < 0 || ny < 0 || nx >= W || ny >= H) return false;
+        const uint16_t g = grid[nx + ny * W];
         switch (a.type) {
-            case T_MOVE: return p >= 0 && p < 4 && mget(m, MB_MOVE + p);
-            case T_HARVEST: return p >= 0 && p < 4 && mget(m, MB_HARVEST + p);
-            case T_RETURN: return p >= 0 && p < 4 && mget(m, MB_RETURN + p);
+            case T_MOVE: return ut_can_move(t) && g == G_NONE;
+            case T_HARVEST: return ut_can_harvest(t) && un.res == 0 && g < G_WALL && ut_is_resource(u[g].type);
+            case T_RETURN: return ut_can_harvest(t) && un.res > 0 && g < G_WALL && ut_is_stockpile(u[g].type) && u[g].player == pl;
             case T_PRODUCE:
-                return p >= 0 && p < 4 && a.utype >= 0 && a.utype < N_UTYPES && mget(m, MB_PDIR + p) && mget(m, MB_PTYPE + a.utype);
-            case T_ATTACK: {
-                int dx = a.x - u[i].x, dy = a.y - u[i].y;
-                if (dx < -3 || dx > 3 || dy < -3 || dy > 3) return false;
-                return mget(m, MB_ATTACK + (3 + dy) * 7 + 3 + dx);
-            }
+                return pl >= 0 && a.utype >= 0 && a.utype < N_UTYPES && ((ut_produces(t) >> a.utype) & 1) && hdr->res[pl] >= ut_cost(a.utype) &&
+                       g == G_NONE;
         }
         return false;
     }
@@ -230,106 +268,144 @@ struct Sim {
     // positions into `bits`, costs into cost[2]; vp selects the state the caller sees.
     MRTS_HD void pending_usage(uint32_t* bits, int* cost, int vp) const {
         bits_clear(bits);
-        cost[0] = cost[1] = 0;
+        int c0 = 0, c1 = 0;  // scalars: a dynamically indexed cost[] would live in local memory
         const int n = nunits();
         for (int i = 0; i < n; i++) {
             const Unit& un = u[i];
             if (un.a_type != T_MOVE && un.a_type != T_PRODUCE) continue;
             if (!inview(i, vp)) continue;
             bit_set(bits, usage_pos(un, un.a_type, un.a_param));
-            if (un.a_type == T_PRODUCE) cost[un.player] += ut_cost(un.a_utype);
+            if (un.a_type == T_PRODUCE) {
+                const int c = ut_cost(un.a_utype);
+                if (un.player == 0) c0 += c;
+                else c1 += c;
+            }
         }
+        cost[0] = c0;
+        cost[1] = c1;
     }
     // ResourceUsage.consistentWith(other) for a single-action `other` against an accumulated base
     // (ResourceUsage.java:31-50)
-    MRTS_HD bool consistent_single(const uint32_t* bits, const int* cost, int pos, int pl, int c) const {
+    MRTS_HD bool consistent_single(const uint32_t* bits, int used, int pos, int pl, int c) const {
         if (pos != -0x7fff && bit_get(bits, pos)) return false;
         if (c != 0) {
-            int s = cost[pl] + c;
-            if (s > 0 && s > hdr->res[pl]) return false;
+            int s = used + c;
+            if (s > 0 && s > (pl == 0 ? hdr->res[0] : hdr->res[1])) return false;
         }
         return true;
     }
 
     // ------------------------------------------------------------------ fromVectorAction + fillWithNones
-    // `actions` = this player view's (HW,7) block.  The reference visits the cells flagged by the
-    // previous get_action_mask in ascending index (vec_env.py:974) and Java keeps a cell iff it
-    // holds an idle unit of the player; both reduce to "own idle units in ascending cell order".
-    MRTS_HD void decode_actions(int player, const int32_t* actions, int vp) {
-        int cost[2];
-        pending_usage(bitsA, cost, vp);
-        npa = 0;
+    // UnitAction.fromVectorAction (UnitAction.java:681-715) of one (7,) action row, packed into 10
+    // bits: [0..2] type, [3..8] payload, [9] parameter out of range.  Payload: direction for
+    // MOVE/HARVEST/RETURN, direction | produced type << 2 for PRODUCE, the 7x7 offset index for
+    // ATTACK (63 = out of range -> off the window -> illegal).  Out-of-range values only matter
+    // through "the action is illegal" and "which cell / cost it reserves", both kept.
+    static MRTS_HD uint16_t pack_action(const int32_t* a) {
+        const int t = a[0];
+        if (t < T_MOVE || t > T_ATTACK) return T_NONE;  // NONE, or an out-of-range type: a no-op
+        int pay = 0, bad = 0;
+        if (t == T_PRODUCE) {
+            if (a[5] < 0 || a[5] >= N_UTYPES) return T_NONE;  // utt.getUnitType would throw: treated as a no-op
+            bad = a[4] < 0 || a[4] > 3;
+            pay = (bad ? 0 : a[4]) | (a[5] << 2);
+        } else if (t == T_ATTACK) {
+            pay = (a[6] < 0 || a[6] > 48) ? 63 : a[6];
+        } else {
+            const int d = a[t];  // a[1] move, a[2] harvest, a[3] return direction
+            bad = d < 0 || d > 3;
+            pay = bad ? 0 : d;
+        }
+        return (uint16_t)(t | (pay << 3) | (bad << 9));
+    }
+    // whole thread group, before the rules: every idle owned unit fetches its cell's row of its
+    // player view's (HW,7) block (self-play: view = player; bot game: only player 0 is driven)
+    MRTS_HD void prefetch_actions(const int32_t* a0, int tid, int nth) {
+        const int n = nunits();
+        for (int i = tid; i < n; i += nth) {
+            Unit& un = u[i];
+            if (un.player < 0 || un.a_type >= 0) continue;
+            if (ai != AI_NONE && un.player != 0) continue;
+            const int32_t* a = a0 + ((size_t)un.player * HW + (un.x + un.y * W)) * 7;
+            un.pre = pack_action(a);
+        }
+    }
+
+    // The reference visits the cells flagged by the previous get_action_mask in ascending index
+    // (vec_env.py:974) and Java keeps a cell iff it holds an idle unit of the player; both reduce to
+    // "own idle units in ascending cell order".
+    MRTS_HD void decode_actions(int player, int vp) {
+        int cost0, cost1;
+        {
+            int cost[2];
+            pending_usage(bitsA, cost, vp);
+            cost0 = cost[0];
+            cost1 = cost[1];
+        }
+        int cnt = 0;
         const int n = nunits();
         // own idle units sorted by cell index (insertion sort over the handful of candidates)
         for (int i = 0; i < n; i++) {
             const Unit& un = u[i];
             if (un.player != player || un.a_type >= 0 || !inview(i, vp)) continue;
             int pos = un.x + un.y * W;
-            int k = npa++;
+            int k = cnt++;
             while (k > 0 && (u[pa[k - 1].unit].x + u[pa[k - 1].unit].y * W) > pos) {
-                pa[k] = pa[k - 1];
+                pa[k].unit = pa[k - 1].unit;
                 k--;
             }
             pa[k].unit = (uint16_t)i;
         }
         int kept = 0;
-        for (int k = 0; k < npa; k++) {
+        const int have = player == 0 ? hdr->res[0] : hdr->res[1];
+        int used = player == 0 ? cost0 : cost1;
+        for (int k = 0; k < cnt; k++) {
             const int i = pa[k].unit;
             const Unit& un = u[i];
-            const int32_t* a = actions + (size_t)(un.x + un.y * W) * 7;
+            const int w = un.pre, pay = (w >> 3) & 63, bad = (w >> 9) & 1;
             PAct e;
             e.unit = (uint16_t)i;
-            e.type = (int8_t)a[0];
+            e.type = (int8_t)(w & 7);
             e.param = -1;  // DIRECTION_NONE, UnitAction.java:114
             e.utype = -1;
             e.x = e.y = 0;
             e.pad = 0;
-            switch (a[0]) {
-                case T_NONE: break;
-                case T_MOVE: e.param = (int16_t)a[1]; break;
-                case T_HARVEST: e.param = (int16_t)a[2]; break;
-                case T_RETURN: e.param = (int16_t)a[3]; break;
-                case T_PRODUCE:
-                    e.param = (int16_t)a[4];
-                    e.utype = (int8_t)a[5];
-                    break;
-                case T_ATTACK:
-                    e.x = (int16_t)(un.x + (a[6] % 7 - 3));
-                    e.y = (int16_t)(un.y + (a[6] / 7 - 3));
-                    break;
-                default: e.type = T_NONE; break;  // out-of-range type: treated as a no-op
-            }
-            if (e.type == T_PRODUCE && (e.utype < 0 || e.utype >= N_UTYPES)) {  // utt.getUnitType would throw
-                e.type = T_NONE;
-                e.param = -1;
-                e.utype = -1;
+            if (e.type == T_PRODUCE) {
+                e.param = (int16_t)(bad ? -1 : (pay & 3));
+                e.utype = (int8_t)(pay >> 2);
+            } else if (e.type == T_ATTACK) {
+                e.x = (int16_t)(un.x + (pay % 7 - 3));
+                e.y = (int16_t)(un.y + (pay / 7 - 3));
+            } else if (e.type != T_NONE) {
+                e.param = (int16_t)(bad ? -1 : pay);
             }
             const int pos = usage_pos(un, e.type, e.param);
             const int c = e.type == T_PRODUCE ? ut_cost(e.utype) : 0;
-            if (consistent_single(bitsA, cost, pos, player, c)) {
+            // ResourceUsage.consistentWith (ResourceUsage.java:31-50) against the accumulated base
+            bool ok = !(pos != -0x7fff && bit_get(bitsA, pos));
+            if (ok && c != 0 && used + c > 0 && used + c > have) ok = false;
+            if (ok) {
                 if (pos != -0x7fff) bit_set(bitsA, pos);
-                cost[player] += c;
+                used += c;
                 pa[kept++] = e;  // kept <= k: never overwrites an unread candidate
             }
         }
-        npa = kept;
-        fill_with_nones(pa, npa, player, 1, vp);
+        st->npa = kept;
+        o_fill_with_nones(self, pa, &st->npa, player, 1, vp);
     }
 
     // PlayerAction.fillWithNones: idle own units not yet in the action, in unit order
     MRTS_HD void fill_with_nones(PAct* list, int& cnt, int player, int duration, int vp) {
         const int n = nunits();
         const int have = cnt;
+        for (int k = 0; k < have; k++) u[list[k].unit].flags |= UF_LISTED;
         for (int i = 0; i < n; i++) {
-            const Unit& un = u[i];
+            Unit& un = u[i];
+            if (un.flags & UF_LISTED) {
+                un.flags &= (uint8_t)~UF_LISTED;
+                continue;
+            }
             if (un.player != player || un.a_type >= 0 || !inview(i, vp)) continue;
-            bool found = false;
-            for (int k = 0; k < have; k++)
-                if (list[k].unit == i) {
-                    found = true;
-                    break;
-                }
-            if (found) continue;
             PAct e;
             e.unit = (uint16_t)i;
             e.type = T_NONE;
@@ -346,23 +422,32 @@ struct Sim {
         const Unit& un = u[a.unit];
         const int p = un.player;
         if (p < 0) return;
-        if (a.type == T_HARVEST || a.type == T_RETURN) rew[p][1] += 1;  // ResourceGatherRewardFunction.java:22-31
+        if (a.type == T_HARVEST || a.type == T_RETURN) st->rew[p][1] += 1;  // ResourceGatherRewardFunction.java:22-31
         if (a.type == T_PRODUCE && a.utype >= 0) {
-            if (a.utype == UT_WORKER) rew[p][2] += 1;                                      // ProduceWorker :20-30
-            if (a.utype == UT_BASE || a.utype == UT_BARRACKS) rew[p][3] += 1;              // ProduceBuilding :20-30
-            if (a.utype == UT_LIGHT || a.utype == UT_HEAVY || a.utype == UT_RANGED) rew[p][5] += 1;  // ProduceCombatUnit
+            if (a.utype == UT_WORKER) st->rew[p][2] += 1;                                      // ProduceWorker :20-30
+            if (a.utype == UT_BASE || a.utype == UT_BARRACKS) st->rew[p][3] += 1;              // ProduceBuilding :20-30
+            if (a.utype == UT_LIGHT || a.utype == UT_HEAVY || a.utype == UT_RANGED) st->rew[p][5] += 1;  // ProduceCombatUnit
         }
         if (a.type == T_ATTACK) {  // AttackRewardFunction.java:20-36: occupant of the target cell in the pre-cycle snapshot
             int o = unit_at(a.x, a.y);
             if (o >= 0) {
-                if (u[o].player == 1 - p) rew[p][4] += 1;
-                else if (u[o].player == p) rew[p][4] -= 1;
+                if (u[o].player == 1 - p) st->rew[p][4] += 1;
+                else if (u[o].player == p) st->rew[p][4] -= 1;
             }
         }
     }
 
     MRTS_HD void issue_safe(PAct* list, int cnt) {
         const int time = hdr->time;
+        // target cells of every pending MOVE / PRODUCE (a superset is fine: it only gates the exact scan)
+        bits_clear(bitsB);
+        {
+            const int n = nunits();
+            for (int j = 0; j < n; j++) {
+                const Unit& ou = u[j];
+                if (ou.a_type == T_MOVE || ou.a_type == T_PRODUCE) bit_set(bitsB, usage_pos(ou, ou.a_type, ou.a_param));
+            }
+        }
         for (int k = 0; k < cnt; k++) {
             PAct a = list[k];
             Unit& un = u[a.unit];
@@ -384,9 +469,11 @@ struct Sim {
                 const int c = a.type == T_PRODUCE ? ut_cost(a.utype) : 0;
                 const int pl = un.player;
                 const int n = nunits();
-                // quick scan: any conflicting assignment at all?
-                bool any = false;
-                for (int j = 0; j < n && !any; j++) any = conflicts(j, pos, pl, c);
+                // quick test: any conflicting assignment at all?  A MOVE conflicts through its target cell
+                // only; a PRODUCE also through the players' resources, which needs the scan.
+                bool any = bit_get(bitsB, pos);
+                if (c != 0)
+                    for (int j = 0; j < n && !any; j++) any = conflicts(j, pos, pl, c);
                 if (any) {
                     // slow path, in issue order (LinkedHashMap iteration)
                     uint32_t last = 0;
@@ -441,6 +528,7 @@ struct Sim {
             un.a_y = (uint8_t)a.y;
             un.a_time = time;
             un.a_seq = hdr->next_seq++;
+            if (pos != -0x7fff) bit_set(bitsB, pos);
         }
     }
     // !consistent(usage(assignment of unit j), ru) with ru = {pos, cost c of player pl}
@@ -519,7 +607,7 @@ struct Sim {
                     nu.flags = 0;
                     nu.vis = 0;  // born after the views were taken
                     nu.vtype[0] = nu.vtype[1] = -1;
-                    nu.pad[0] = nu.pad[1] = 0;
+                    nu.pre = 0;
                     grid[tx + ty * W] = (uint16_t)k;
                     hdr->res[un.player] -= ut_cost(prod);
                 }
@@ -577,21 +665,24 @@ struct Sim {
         hdr->nunits = k;
     }
 
-    // PhysicalGameState.gameover / winner (PhysicalGameState.java:319-372) over live units
+    // PhysicalGameState.gameover / st->winner (PhysicalGameState.java:319-372) over live units
     MRTS_HD void eval_gameover() {
-        int cnt[2] = {0, 0};
+        int c0 = 0, c1 = 0;
         const int n = nunits();
         for (int i = 0; i < n; i++)
-            if (alive(i) && u[i].player >= 0) cnt[u[i].player]++;
-        if (cnt[0] + cnt[1] == 0) {
-            gameover = 1;
-            winner = -1;
-        } else if (cnt[0] > 0 && cnt[1] > 0) {
-            gameover = 0;
-            winner = -1;
+            if (alive(i)) {
+                c0 += u[i].player == 0;
+                c1 += u[i].player == 1;
+            }
+        if (c0 + c1 == 0) {
+            st->gameover = 1;
+            st->winner = -1;
+        } else if (c0 > 0 && c1 > 0) {
+            st->gameover = 0;
+            st->winner = -1;
         } else {
-            gameover = 1;
-            winner = cnt[0] > 0 ? 0 : 1;
+            st->gameover = 1;
+            st->winner = c0 > 0 ? 0 : 1;
         }
     }
 
@@ -634,11 +725,17 @@ struct Sim {
         }
         aa[k] = r;
     }
+    // The unit array is in creation order and uids are handed out in creation order (template
+    // index, then next_uid++), compaction is stable: the array is sorted by uid.
     MRTS_HD int find_uid(uint16_t uid, int vp) const {  // pgs.getUnits().contains(u) on the view
         if (uid == NO_UID) return -1;
-        const int n = nunits();
-        for (int i = 0; i < n; i++)
-            if (u[i].uid == uid) return inview(i, vp) ? i : -1;
+        int lo = 0, hi = nunits();
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (u[mid].uid < uid) lo = mid + 1;
+            else hi = mid;
+        }
+        if (lo < nunits() && u[lo].uid == uid) return inview(lo, vp) ? lo : -1;
         return -1;
     }
     MRTS_HD static int iabs(int v) { return v < 0 ? -v : v; }
@@ -661,6 +758,7 @@ struct Sim {
         }
         const int pos = usage_pos(un, type, param);
         if (pos != -0x7fff && bit_get(bitsB, pos)) return false;
+#pragma unroll
         for (int p = 0; p < 2; p++) {
             if (costB[p] == 0) continue;
             int s = ((type == T_PRODUCE && un.player == p) ? ut_cost(prod) : 0) + costB[p];
@@ -695,17 +793,17 @@ struct Sim {
         AStarBuf b = astar_buf();
         for (int k = tid; k < astar_nf(); k += nth) b.head[k] = -1;
         for (int k = tid; k < HW; k += nth) b.stamp[k] = 0;
-        astar_gen = 0;
+        st->astar_gen = 0;
     }
     // findPathToPositionInRange: direction of the first move, or -1 (null)
     MRTS_HD int astar_first_move(int i, int targetpos, int range, int vp) {
         const AStarBuf b = astar_buf();
-        const Unit& st = u[i];
-        const uint16_t gen = (uint16_t)++astar_gen;
+        const Unit& su = u[i];
+        const uint16_t gen = (uint16_t)++st->astar_gen;
         const int tx = targetpos % W, ty = targetpos / W;
         const int sq = range * range;
-        const int startPos = st.y * W + st.x;
-        const int h0 = iabs(st.x - tx) + iabs(st.y - ty);
+        const int startPos = su.y * W + su.x;
+        const int h0 = iabs(su.x - tx) + iabs(su.y - ty);
         b.parent[startPos] = (int16_t)startPos;
         b.cost[startPos] = 0;
         b.stamp[startPos] = gen;
@@ -813,7 +911,7 @@ struct Sim {
                 return false;
             }
             case AA_BUILD: {  // Build.java:56-78
-                int mv = astar_first_move(i, r.x + r.y * W, 1, vp);
+                int mv = o_astar(self, i, r.x + r.y * W, 1, vp);
                 if (mv >= 0) {
                     if (action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
                         out.type = T_MOVE;
@@ -840,7 +938,7 @@ struct Sim {
                 int ti = find_uid(carrying ? r.base : r.target, vp);
                 if (ti < 0) return false;
                 const Unit& tg = u[ti];
-                int mv = astar_first_move(i, tg.x + tg.y * W, 1, vp);
+                int mv = o_astar(self, i, tg.x + tg.y * W, 1, vp);
                 if (mv >= 0) {
                     if (action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
                         out.type = T_MOVE;
@@ -871,7 +969,7 @@ struct Sim {
                     out.y = tg.y;
                     return true;
                 }
-                int mv = astar_first_move(i, tg.x + tg.y * W, rg, vp);
+                int mv = o_astar(self, i, tg.x + tg.y * W, rg, vp);
                 if (mv >= 0 && action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
                     out.type = T_MOVE;
                     out.param = (int16_t)mv;
@@ -897,10 +995,10 @@ struct Sim {
 
     // AbstractionLayerAI.translateActions, AbstractionLayerAI.java:58-113 -> pa2
     MRTS_HD void translate_actions(int player, int vp) {
-        int costB[2], costA[2], costC[2] = {0, 0};
+        int costB[2];
         pending_usage(bitsB, costB, vp);
         bits_clear(bitsC);
-        npa2 = 0;
+        st->npa2 = 0;
         int na = hdr->n_aa, keep = 0;
         for (int k = 0; k < na; k++) {
             AbstractAct r = aa[k];
@@ -911,34 +1009,32 @@ struct Sim {
             else if (u[i].a_type < 0) {
                 PAct out;
                 if (aa_execute(r, i, vp, costB, out)) {
-                    pa2[npa2++] = out;
+                    pa2[st->npa2++] = out;
                     int pos = usage_pos(u[i], out.type, out.param);
                     if (pos != -0x7fff) bit_set(bitsC, pos);
-                    if (out.type == T_PRODUCE) costC[u[i].player] += ut_cost(out.utype);
                 }
             }
             if (!del) aa[keep++] = r;  // r may carry Train's completed flag
         }
         hdr->n_aa = (uint16_t)keep;
-        (void)costC;
         // accept desires first-come-first-served against the pending usage
         for (int w = 0; w < nbits_words; w++) bitsA[w] = bitsB[w];
-        costA[0] = costB[0];
-        costA[1] = costB[1];
+        int used0 = costB[0], used1 = costB[1];
         int kept = 0;
-        for (int k = 0; k < npa2; k++) {
+        for (int k = 0; k < st->npa2; k++) {
             PAct d = pa2[k];
             const Unit& un = u[d.unit];
             int pos = usage_pos(un, d.type, d.param);
             int c = d.type == T_PRODUCE ? ut_cost(d.utype) : 0;
-            if (consistent_single(bitsA, costA, pos, un.player, c)) {
+            if (consistent_single(bitsA, un.player == 0 ? used0 : used1, pos, un.player, c)) {
                 if (pos != -0x7fff) bit_set(bitsA, pos);
-                costA[un.player] += c;
+                if (un.player == 0) used0 += c;
+                else used1 += c;
                 pa2[kept++] = d;
             }
         }
-        npa2 = kept;
-        fill_with_nones(pa2, npa2, player, 10, vp);
+        st->npa2 = kept;
+        o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);
     }
 
     // AbstractionLayerAI.findBuildingPosition, AbstractionLayerAI.java:143-228 (reserved list is empty for WorkerRush)
@@ -1050,7 +1146,7 @@ struct Sim {
         }
         for (int i = 0; i < n; i++) {
             const Unit& un = u[i];
-            if (ut_can_attack(un.type) && !ut_can_harvest(un.type) && un.player == player && un.a_type < 0) bot_melee(i, player, vp);
+            if (ut_can_attack(un.type) && !ut_can_harvest(un.type) && un.player == player && un.a_type < 0) o_bot_melee(self, i, player, vp);
         }
         // workersBehavior, WorkerRush.java:124-204
         int nbases = 0, nworkers = 0;
@@ -1088,62 +1184,90 @@ struct Sim {
             for (int i = 0; i < n; i++) {
                 if (u[i].player != player || !ut_can_harvest(u[i].type)) continue;
                 if (i == builder || i == harvester) continue;
-                bot_melee(i, player, vp);
+                o_bot_melee(self, i, player, vp);
             }
-            if (hfree) bot_melee(harvester, player, vp);
+            if (hfree) o_bot_melee(self, harvester, player, vp);
         }
         translate_actions(player, vp);
     }
 
     // the scripted opponent's PlayerAction for `player` -> pa2
     MRTS_HD void bot_action(int player, int vp) {
-        npa2 = 0;
+        st->npa2 = 0;
         if (ai == AI_WORKER_RUSH) worker_rush(player, vp);
-        else fill_with_nones(pa2, npa2, player, 10, vp);  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
+        else o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
     }
 
     // ================================================================== one environment step
-    // a0 / a1: the (HW,7) int32 action blocks of this game's player views (a1 unused for bot games).
-    // On return: rew[][] holds the six reward terms per view, gameover/winner are set, the unit
+    // The agents' actions were staged per unit by prefetch_actions.
+    // On return: st->rew[][] holds the six reward terms per view, st->gameover/st->winner are set, the unit
     // array still contains units killed this cycle (flagged) so that stale partially observable
     // views can be encoded; the caller then runs compact() or reloads the map template.
-    MRTS_HD bool step_game(const int32_t* a0, const int32_t* a1) {
+    MRTS_HD bool step_game() {
         for (int p = 0; p < 2; p++)
-            for (int k = 0; k < 6; k++) rew[p][k] = 0;
+            for (int k = 0; k < 6; k++) st->rew[p][k] = 0;
         if (ai == AI_NONE) {
             // JNIGridnetClientSelfPlay.gameStep, :159-189
             for (int p = 0; p < 2; p++) {
                 int vp = -1;
                 if (partial) {
-                    make_view(p);
+                    o_make_view(self, p);
                     vp = p;
                 }
-                decode_actions(p, p == 0 ? a0 : a1, vp);
-                issue_safe(pa, npa);
+                o_decode_actions(self, p, vp);
+                o_issue_safe(self, pa, st->npa);
             }
         } else {
             // JNIGridnetClient.gameStep, :163-196
             int v0 = -1, v1 = -1;
             if (partial) {
-                make_view(0);
-                make_view(1);
+                o_make_view(self, 0);
+                o_make_view(self, 1);
                 v0 = 0;
                 v1 = 1;
             }
-            decode_actions(0, a0, v0);
+            o_decode_actions(self, 0, v0);
             bot_action(1, v1);
-            issue_safe(pa, npa);
-            issue_safe(pa2, npa2);
+            o_issue_safe(self, pa, st->npa);
+            o_issue_safe(self, pa2, st->npa2);
         }
         cycle();
         eval_gameover();
-        if (gameover) {  // WinLossRewardFunction.java:16-24
-            rew[0][0] = winner == 0 ? 1 : -1;
-            rew[1][0] = winner == 1 ? 1 : -1;
+        if (st->gameover) {  // WinLossRewardFunction.java:16-24
+            st->rew[0][0] = st->winner == 0 ? 1 : -1;
+            st->rew[1][0] = st->winner == 1 ? 1 : -1;
         }
         hdr->steps++;
-        return gameover || hdr->steps >= max_steps;  // JNIGridnetVecClient.java:245-266 / :270-286
+        return st->gameover || hdr->steps >= max_steps;  // JNIGridnetVecClient.java:245-266 / :270-286
     }
 };
+
+// ---- out-of-line entry points (see the declarations above Sim)
+MRTS_HDN int o_astar(const Sim* sp, int i, int targetpos, int range, int vp) {
+    Sim s = *sp;
+    return s.astar_first_move(i, targetpos, range, vp);
+}
+MRTS_HDN void o_issue_safe(const Sim* sp, PAct* list, int cnt) {
+    Sim s = *sp;
+    s.issue_safe(list, cnt);
+}
+MRTS_HDN void o_decode_actions(const Sim* sp, int player, int vp) {
+    Sim s = *sp;
+    s.decode_actions(player, vp);
+}
+MRTS_HDN void o_make_view(const Sim* sp, int p) {
+    Sim s = *sp;
+    s.make_view(p);
+}
+MRTS_HDN void o_bot_melee(const Sim* sp, int i, int player, int vp) {
+    Sim s = *sp;
+    s.bot_melee(i, player, vp);
+}
+MRTS_HDN void o_fill_with_nones(const Sim* sp, PAct* list, int* cnt, int player, int duration, int vp) {
+    Sim s = *sp;
+    int c = *cnt;
+    s.fill_with_nones(list, c, player, duration, vp);
+    *cnt = c;
+}
 
 }  // namespace mrts

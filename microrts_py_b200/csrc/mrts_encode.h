@@ -86,8 +86,8 @@ MRTS_HD void store16(void* p, Vec16 v) { *(Vec16*)p = v; }
 #endif
 
 // Phase C: one env's observation.  ELEM = 4 (int32) or 1 (uint8).  P = planes per cell.
-template <int ELEM>
-MRTS_HD void store_obs(const uint32_t* words, int HW, int P, void* out, int tid, int nth) {
+template <int ELEM, int P>
+MRTS_HD void store_obs(const uint32_t* words, int HW, void* out, int tid, int nth) {
     const bool vec = (((uintptr_t)out) & 15) == 0;  // odd map sizes: env rows are not 16-byte aligned -> scalar stores
     const int total = HW * P;                 // elements
     constexpr int EPC = 16 / ELEM;            // elements per 16-byte chunk
@@ -191,12 +191,18 @@ MRTS_HD int pick_bit(uint64_t bits, uint32_t r) {
     const int n = popc64(bits);
     if (n == 0) return 0;
     int k = (int)(r % (uint32_t)n);
+#if defined(__CUDA_ARCH__)
+    const uint32_t lo = (uint32_t)bits, hi = (uint32_t)(bits >> 32);
+    const int nlo = __popc(lo);
+    return k < nlo ? (int)__fns(lo, 0, k + 1) : 32 + (int)__fns(hi, 0, k - nlo + 1);
+#else
     for (int b = 0; b < 64; b++)
         if ((bits >> b) & 1) {
             if (k == 0) return b;
             k--;
         }
     return 0;
+#endif
 }
 MRTS_HD void sample_unit_action(const uint32_t* um, uint64_t key, int32_t* out7) {
     const uint64_t lo = (uint64_t)um[0] | ((uint64_t)um[1] << 32);

@@ -35,11 +35,12 @@ struct BlockSync {
     __device__ __forceinline__ void operator()() const { __syncthreads(); }
 };
 
+template <int ELEM, int PLANES>
 __global__ void mrts_pass_kernel(const EnvParams P) {
     extern __shared__ uint4 smem_raw[];
     const int g = blockIdx.x;
     if (g >= P.n_games) return;
-    game_pass(P, g, (uint8_t*)smem_raw, (int)threadIdx.x, (int)blockDim.x, BlockSync());
+    game_pass<ELEM, PLANES>(P, g, (uint8_t*)smem_raw, (int)threadIdx.x, (int)blockDim.x, BlockSync());
 }
 
 // One warp per game, GPB games per block: the group barrier is __syncwarp(), and a block's
@@ -49,12 +50,16 @@ struct WarpSync {
     __device__ __forceinline__ void operator()() const { __syncwarp(); }
 };
 constexpr int GPB = 4;
-__global__ void __launch_bounds__(32 * GPB) mrts_pass_warp_kernel(const EnvParams P, const int smem_per_game) {
+#ifndef MRTS_WARP_MIN_BLOCKS
+#define MRTS_WARP_MIN_BLOCKS 5
+#endif
+template <int ELEM, int PLANES>
+__global__ void __launch_bounds__(32 * GPB, MRTS_WARP_MIN_BLOCKS) mrts_pass_warp_kernel(const EnvParams P, const int smem_per_game) {
     extern __shared__ uint4 smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = blockIdx.x * GPB + warp;
     if (g >= P.n_games) return;
-    game_pass(P, g, (uint8_t*)smem_raw + (size_t)warp * smem_per_game, lane, 32, WarpSync());
+    game_pass<ELEM, PLANES>(P, g, (uint8_t*)smem_raw + (size_t)warp * smem_per_game, lane, 32, WarpSync());
 }
 
 // ---- raw engine access (trace replay): one block, one game
@@ -81,8 +86,13 @@ __global__ void mrts_debug_kernel(const EnvParams P, const DebugArgs A) {
     for (int i = tid; i < s.hdr->nunits; i += nth) s.grid[s.u[i].x + s.u[i].y * P.W] = (uint16_t)i;
     __syncthreads();
     if (tid == 0) {
+        *(Sim*)(mem + L.sim) = s;
+        St z;
+        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = 0;
+        z.winner = -1;
         for (int p = 0; p < 2; p++)
-            for (int k = 0; k < 6; k++) s.rew[p][k] = 0;
+            for (int k = 0; k < 6; k++) z.rew[p][k] = 0;
+        *s.st = z;
         if (A.op == 0) {
             int cnt = 0;
             for (int k = 0; k < A.n && cnt < P.cap; k++) {
@@ -105,7 +115,7 @@ __global__ void mrts_debug_kernel(const EnvParams P, const DebugArgs A) {
             s.cycle();
             s.eval_gameover();
             s.compact();
-            if (A.gameover) *A.gameover = s.gameover;
+            if (A.gameover) *A.gameover = s.st->gameover;
         }
     }
     __syncthreads();
@@ -159,10 +169,18 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     P.next_actions = next_actions;
     P.seed = seed;
     P.counter = next_actions ? e->sample_counter++ : 0;
-    if (e->threads == 32)
-        mrts_pass_warp_kernel<<<(P.n_games + GPB - 1) / GPB, 32 * GPB, GPB * e->smem, (cudaStream_t)stream>>>(P, e->smem);
-    else
-        mrts_pass_kernel<<<P.n_games, e->threads, e->smem, (cudaStream_t)stream>>>(P);
+    const dim3 wgrid((P.n_games + GPB - 1) / GPB), bgrid(P.n_games);
+    const cudaStream_t st = (cudaStream_t)stream;
+#define MRTS_LAUNCH(E, PL)                                                                       \
+    do {                                                                                         \
+        if (e->threads == 32) mrts_pass_warp_kernel<E, PL><<<wgrid, 32 * GPB, GPB * e->smem, st>>>(P, e->smem); \
+        else mrts_pass_kernel<E, PL><<<bgrid, e->threads, e->smem, st>>>(P);                     \
+    } while (0)
+    if (P.elem == 4 && P.planes == 29) MRTS_LAUNCH(4, 29);
+    else if (P.elem == 4) MRTS_LAUNCH(4, 31);
+    else if (P.planes == 29) MRTS_LAUNCH(1, 29);
+    else MRTS_LAUNCH(1, 31);
+#undef MRTS_LAUNCH
     CK(cudaGetLastError());
     return MRTS_OK;
 }
@@ -228,10 +246,21 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         mrts_destroy(e);
         return fail(MRTS_EINVAL, "map too large for shared-memory staging");
     }
-    if (GPB * e->smem > 48 * 1024) cudaFuncSetAttribute(mrts_pass_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->threads == 32 ? GPB * e->smem : 48 * 1024);
-    if (e->smem > 48 * 1024) {
-        cudaFuncSetAttribute(mrts_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
-        cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+    {
+        const int wbytes = e->threads == 32 ? GPB * e->smem : 48 * 1024;
+        if (GPB * e->smem > 48 * 1024) {
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+        }
+        if (e->smem > 48 * 1024) {
+            cudaFuncSetAttribute(mrts_pass_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+            cudaFuncSetAttribute(mrts_pass_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+            cudaFuncSetAttribute(mrts_pass_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+            cudaFuncSetAttribute(mrts_pass_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+            cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+        }
     }
     // start every game from its template so that the state is defined before the first reset()
     rc = launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);

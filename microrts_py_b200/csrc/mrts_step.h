@@ -42,7 +42,7 @@ MRTS_HD int align16(int v) { return (v + 15) & ~15; }
 MRTS_HD int blob_bytes(int cap, int has_bot) { return 32 + cap * 32 + (has_bot ? align16(cap * 12) : 0); }
 
 struct Layout {
-    int blob, grid, words, umask, pa, pa2, bits, astar, misc, total, nbits_words;
+    int blob, grid, words, umask, pa, pa2, bits, astar, misc, sim, total, nbits_words;
 };
 // Shared-memory plan of one game.  The rules scratch (PlayerActions, reservation bitmaps, A*
 // arrays) is dead once the leader is done, the output scratch (observation words, per-unit
@@ -54,8 +54,10 @@ MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int nviews = 2) 
     o += blob_bytes(cap, has_bot);
     L.grid = o;
     o += align16(HW * 2);
-    L.misc = o;
-    o += 16;
+    L.misc = o;  // St
+    o += align16((int)sizeof(St));
+    L.sim = o;   // the game's Sim view, read by the out-of-line rule functions
+    o += align16((int)sizeof(Sim));
     const int scratch = o;
     // ---- rules scratch
     L.pa = o;
@@ -96,15 +98,13 @@ MRTS_HD void bind_sim(Sim& s, const EnvParams& P, const Layout& L, uint8_t* mem,
     s.grid = (uint16_t*)(mem + L.grid);
     s.pa = (PAct*)(mem + L.pa);
     s.pa2 = (PAct*)(mem + L.pa2);
-    s.npa = s.npa2 = 0;
     s.nbits_words = L.nbits_words;
     s.bitsA = (uint32_t*)(mem + L.bits);
     s.bitsB = s.bitsA + L.nbits_words;
     s.bitsC = s.bitsB + L.nbits_words;
     s.astar = (int16_t*)(mem + L.astar);
-    s.astar_gen = 0;
-    s.gameover = 0;
-    s.winner = -1;
+    s.st = (St*)(mem + L.misc);
+    s.self = (const Sim*)(mem + L.sim);
 }
 
 template <class T>
@@ -112,6 +112,7 @@ MRTS_HD void copy16(void* dst, const void* src, int bytes, int tid, int nth) {  
     const T* s = (const T*)src;
     T* d = (T*)dst;
     const int n = bytes / (int)sizeof(T);
+#pragma unroll 1
     for (int i = tid; i < n; i += nth) d[i] = s[i];
 }
 struct alignas(16) Q16 {
@@ -119,14 +120,13 @@ struct alignas(16) Q16 {
 };
 
 // SYNC: functor executing a barrier over the game's thread group.
-template <class SYNC>
+template <int ELEM, int PLANES, class SYNC>
 MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync) {
     const Layout L = layout_of(P);
     Sim s;
     bind_sim(s, P, L, mem, g);
     uint32_t* words = (uint32_t*)(mem + L.words);
     uint32_t* umask = (uint32_t*)(mem + L.umask);
-    volatile int32_t* misc = (volatile int32_t*)(mem + L.misc);
 
     const MapTpl tpl = P.maps[P.game_map[g]];
     const uint16_t* grid0 = P.grid_pool + tpl.grid_off;
@@ -168,29 +168,39 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
     }
     if (P.mode == MODE_STEP && s.ai == AI_WORKER_RUSH) s.astar_init(tid, nth);
+    if (tid == 0) {
+        *(Sim*)(mem + L.sim) = s;
+        St z;
+        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = 0;
+        z.winner = -1;
+        for (int p = 0; p < 2; p++)
+            for (int k = 0; k < 6; k++) z.rew[p][k] = 0;
+        *s.st = z;
+    }
     sync();
     scatter_grid();
+    // the agents' action rows of the units that may act, fetched by the whole group (the leader never waits on HBM)
+    if (P.mode == MODE_STEP) s.prefetch_actions(P.actions + (size_t)env0 * P.HW * 7, tid, nth);
     sync();
 
     // ---------------- rules (leader)
     if (tid == 0) {
-        int reset = 0;
         if (P.mode == MODE_STEP) {
-            const int32_t* a0 = P.actions + (size_t)env0 * P.HW * 7;
-            reset = s.step_game(a0, a0 + (size_t)P.HW * 7) ? 1 : 0;
-            for (int v = 0; v < nviews; v++) {
-                if (P.reward)
-                    for (int k = 0; k < 6; k++) P.reward[(size_t)(env0 + v) * 6 + k] = (double)s.rew[v][k];
-                // done[0] of WinLoss, forced true by the vec client on terminal / max_steps
-                if (P.done) P.done[env0 + v] = (uint8_t)reset;
-            }
+            s.st->reset = s.step_game() ? 1 : 0;
         } else if (P.partial) {
-            for (int v = 0; v < nviews; v++) s.make_view(v);
+            for (int v = 0; v < nviews; v++) o_make_view(s.self, v);
         }
-        misc[0] = reset;
     }
     sync();
-    const int reset = misc[0];
+    const int reset = ((volatile St*)s.st)->reset;
+    if (P.mode == MODE_STEP) {
+        // six reward terms per view (exact small integers) and done[0] of WinLoss, forced true by the
+        // vec client on terminal / max_steps: 12 + 2 scalars, one per lane
+        for (int k = tid; k < nviews * 6; k += nth)
+            if (P.reward) P.reward[(size_t)env0 * 6 + k] = (double)s.st->rew[k / 6][k % 6];
+        for (int v = tid; v < nviews; v += nth)
+            if (P.done) P.done[env0 + v] = (uint8_t)reset;
+    }
     if (reset) {  // JNIGridnetClient.reset: fresh game from the map, scripted opponent re-created
         load_template();
         sync();
@@ -198,7 +208,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         sync();
         if (P.partial) {
             if (tid == 0)
-                for (int v = 0; v < nviews; v++) s.make_view(v);
+                for (int v = 0; v < nviews; v++) o_make_view(s.self, v);
             sync();
         }
     }
@@ -219,18 +229,16 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (P.mask || P.next_actions) unit_masks(s, umask, tid, nth);
 
     // ---------------- bulk stores
-    const size_t obs_env = (size_t)P.HW * P.planes * P.elem;
-    const size_t mask_env = (size_t)P.HW * 78 * P.elem;
+    const size_t obs_env = (size_t)P.HW * PLANES * ELEM;
+    const size_t mask_env = (size_t)P.HW * 78 * ELEM;
     for (int v = 0; v < nviews; v++) {
         if (P.obs) {
             void* o = (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env;
-            if (P.elem == 4) store_obs<4>(words + v * P.HW, P.HW, P.planes, o, tid, nth);
-            else store_obs<1>(words + v * P.HW, P.HW, P.planes, o, tid, nth);
+            store_obs<ELEM, PLANES>(words + v * P.HW, P.HW, o, tid, nth);
         }
         if (P.mask) {
             void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;
-            if (P.elem == 4) zero_mask<4>(P.HW, m, tid, nth);
-            else zero_mask<1>(P.HW, m, tid, nth);
+            zero_mask<ELEM>(P.HW, m, tid, nth);
         }
     }
     sync();  // zero-fill before patches (and umask complete)
@@ -240,8 +248,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (P.mask) {
         for (int v = 0; v < nviews; v++) {
             void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;
-            if (P.elem == 4) patch_mask<4>(s, v, umask, m, tid, nth);
-            else patch_mask<1>(s, v, umask, m, tid, nth);
+            patch_mask<ELEM>(s, v, umask, m, tid, nth);
         }
     }
 

@@ -74,10 +74,10 @@ struct Unit {  // 32 bytes
     uint8_t flags;    // UF_*
     uint8_t vis;      // bit p: unit is in player p's partially observable view (taken this step)
     int8_t vtype[2];  // action type recorded in view p's assignment copy, -1 none
-    uint8_t pad[2];
+    uint16_t pre;     // this step's decoded agent action for the unit (pack_action), staged by the whole group before the rules run
 };
 static_assert(sizeof(Unit) == 32, "Unit must be 32 bytes");
-enum { UF_DEAD = 1, UF_THIS_STEP = 2 };
+enum { UF_DEAD = 1, UF_THIS_STEP = 2, UF_LISTED = 4 /* scratch mark of fill_with_nones, always cleared again */ };
 
 // abstract action of the scripted bots (J/ai/abstraction/{Train,Build,Harvest,Attack}.java)
 enum { AA_TRAIN = 0, AA_BUILD = 1, AA_HARVEST = 2, AA_ATTACK = 3 };

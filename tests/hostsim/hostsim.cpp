@@ -38,7 +38,12 @@ static void pass(hs_env* e, int mode, const int32_t* actions, void* obs, void* m
     P.mask = mask;
     P.reward = reward;
     P.done = done;
-    for (int g = 0; g < P.n_games; g++) game_pass(P, g, e->mem.data(), 0, 1, NoSync());
+    for (int g = 0; g < P.n_games; g++) {
+        if (P.elem == 4 && P.planes == 29) game_pass<4, 29>(P, g, e->mem.data(), 0, 1, NoSync());
+        else if (P.elem == 4) game_pass<4, 31>(P, g, e->mem.data(), 0, 1, NoSync());
+        else if (P.planes == 29) game_pass<1, 29>(P, g, e->mem.data(), 0, 1, NoSync());
+        else game_pass<1, 31>(P, g, e->mem.data(), 0, 1, NoSync());
+    }
 }
 
 extern "C" {

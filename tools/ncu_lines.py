@@ -14,7 +14,9 @@ import tempfile
 from collections import defaultdict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB = os.path.join(ROOT, "microrts_py_b200", "csrc", "libmrts_b200.so")
+LIB = os.environ.get("NCU_LINES_LIB") or os.path.join(ROOT, "microrts_py_b200", "csrc", "libmrts_b200.so")
+SRC = os.environ.get("NCU_LINES_SRC") or os.path.join(ROOT, "microrts_py_b200", "csrc")
+COL = os.environ.get("NCU_LINES_COL") or "# Samples"  # e.g. stall_long_sb, stall_no_inst
 
 
 def line_table(kernel):
@@ -46,7 +48,7 @@ def main():
     rows = list(csv.reader(open(path)))
     h = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[h]
-    ia, isamp, iinst = hdr.index("Address"), hdr.index("# Samples"), hdr.index("Instructions Executed")
+    ia, isamp, iinst = hdr.index("Address"), hdr.index(COL), hdr.index("Instructions Executed")
     body = [r for r in rows[h + 1 :] if len(r) > iinst and r[ia].startswith("0x")]
     base = int(body[0][ia], 16)
     per = defaultdict(lambda: [0, 0])
@@ -59,7 +61,7 @@ def main():
         per[key][1] += n
         tot[0] += s
         tot[1] += n
-    print(f"total samples {tot[0]}  warp instructions {tot[1]}")
+    print(f"column {COL}: total {tot[0]}  warp instructions {tot[1]}")
     byfile = defaultdict(lambda: [0, 0])
     for (f, l), (s, n) in per.items():
         byfile[f][0] += s
@@ -69,7 +71,7 @@ def main():
     src = {}
     for (f, l), (s, n) in sorted(per.items(), key=lambda kv: -kv[1][0])[:top]:
         if f not in src:
-            p = os.path.join(ROOT, "microrts_py_b200", "csrc", f)
+            p = os.path.join(SRC, f)
             src[f] = open(p).read().splitlines() if os.path.exists(p) else []
         text = src[f][l - 1].strip() if 0 < l <= len(src[f]) else ""
         print(f"{100*s/max(tot[0],1):5.1f}% {100*n/max(tot[1],1):5.1f}%  {f}:{l}  {text[:110]}")
