@@ -54,7 +54,7 @@ typedef struct mrts_config {
     const int32_t* env_map;    /* N entries: template index per env (self-play game g uses entry 2g) */
     const int32_t* bot_ai;     /* num_bot_envs entries: MRTS_AI_*                                  */
     int32_t elem_bytes;        /* 4 = int32 obs/mask (reference dtype), 1 = uint8                  */
-    int32_t threads_per_game;  /* 0 = choose from the map size                                     */
+    int32_t threads_per_game;  /* 0 = choose from the map size; n > 0 = n threads per game; n < 0 = one warp per game, -n games per block */
 } mrts_config;
 
 typedef struct mrts_env mrts_env;

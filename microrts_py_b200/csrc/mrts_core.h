@@ -138,6 +138,7 @@ struct Sim {
         return pos;
     }
     MRTS_HD void bits_clear(uint32_t* b) const {
+#pragma unroll 1
         for (int i = 0; i < nbits_words; i++) b[i] = 0;
     }
     MRTS_HD bool bit_get(const uint32_t* b, int pos) const {
@@ -182,7 +183,9 @@ struct Sim {
                     }
             } else {
                 const int r = ut_range(t), sq = r * r;
+#pragma unroll 1
                 for (int dy = -r; dy <= r; dy++)
+#pragma unroll 1
                     for (int dx = -r; dx <= r; dx++) {
                         if (dx * dx + dy * dy > sq) continue;
                         int o = unit_at(x + dx, y + dy);
@@ -210,6 +213,7 @@ struct Sim {
         const int prod = ut_produces(t);
         if (prod && pl >= 0) {
             int afford = 0;
+#pragma unroll 1
             for (int k = 1; k < N_UTYPES; k++)
                 if (((prod >> k) & 1) && hdr->res[pl] >= ut_cost(k)) afford |= 1 << k;
             int dirs = 0;
@@ -270,6 +274,7 @@ struct Sim {
         bits_clear(bits);
         int c0 = 0, c1 = 0;  // scalars: a dynamically indexed cost[] would live in local memory
         const int n = nunits();
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             const Unit& un = u[i];
             if (un.a_type != T_MOVE && un.a_type != T_PRODUCE) continue;
@@ -322,6 +327,7 @@ struct Sim {
     // player view's (HW,7) block (self-play: view = player; bot game: only player 0 is driven)
     MRTS_HD void prefetch_actions(const int32_t* a0, int tid, int nth) {
         const int n = nunits();
+#pragma unroll 1
         for (int i = tid; i < n; i += nth) {
             Unit& un = u[i];
             if (un.player < 0 || un.a_type >= 0) continue;
@@ -345,11 +351,13 @@ struct Sim {
         int cnt = 0;
         const int n = nunits();
         // own idle units sorted by cell index (insertion sort over the handful of candidates)
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             const Unit& un = u[i];
             if (un.player != player || un.a_type >= 0 || !inview(i, vp)) continue;
             int pos = un.x + un.y * W;
             int k = cnt++;
+#pragma unroll 1
             while (k > 0 && (u[pa[k - 1].unit].x + u[pa[k - 1].unit].y * W) > pos) {
                 pa[k].unit = pa[k - 1].unit;
                 k--;
@@ -359,6 +367,7 @@ struct Sim {
         int kept = 0;
         const int have = player == 0 ? hdr->res[0] : hdr->res[1];
         int used = player == 0 ? cost0 : cost1;
+#pragma unroll 1
         for (int k = 0; k < cnt; k++) {
             const int i = pa[k].unit;
             const Unit& un = u[i];
@@ -398,7 +407,9 @@ struct Sim {
     MRTS_HD void fill_with_nones(PAct* list, int& cnt, int player, int duration, int vp) {
         const int n = nunits();
         const int have = cnt;
+#pragma unroll 1
         for (int k = 0; k < have; k++) u[list[k].unit].flags |= UF_LISTED;
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             Unit& un = u[i];
             if (un.flags & UF_LISTED) {
@@ -443,11 +454,13 @@ struct Sim {
         bits_clear(bitsB);
         {
             const int n = nunits();
+#pragma unroll 1
             for (int j = 0; j < n; j++) {
                 const Unit& ou = u[j];
                 if (ou.a_type == T_MOVE || ou.a_type == T_PRODUCE) bit_set(bitsB, usage_pos(ou, ou.a_type, ou.a_param));
             }
         }
+#pragma unroll 1
         for (int k = 0; k < cnt; k++) {
             PAct a = list[k];
             Unit& un = u[a.unit];
@@ -473,14 +486,17 @@ struct Sim {
                 // only; a PRODUCE also through the players' resources, which needs the scan.
                 bool any = bit_get(bitsB, pos);
                 if (c != 0)
+#pragma unroll 1
                     for (int j = 0; j < n && !any; j++) any = conflicts(j, pos, pl, c);
                 if (any) {
                     // slow path, in issue order (LinkedHashMap iteration)
                     uint32_t last = 0;
                     bool first = true;
+#pragma unroll 1
                     for (;;) {
                         int best = -1;
                         uint32_t bs = 0xFFFFFFFFu;
+#pragma unroll 1
                         for (int j = 0; j < n; j++) {
                             if (u[j].a_type < 0) continue;
                             if (!first && u[j].a_seq <= last) continue;
@@ -624,6 +640,7 @@ struct Sim {
         // ready non-NONE assignments, sorted by issue order; NONEs just vanish (no effect)
         int nr = 0;
         uint16_t* ready = (uint16_t*)pa;  // pa is free again
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             Unit& un = u[i];
             if (un.a_type < 0) continue;
@@ -634,12 +651,14 @@ struct Sim {
                 continue;
             }
             int k = nr++;
+#pragma unroll 1
             while (k > 0 && u[ready[k - 1]].a_seq > un.a_seq) {
                 ready[k] = ready[k - 1];
                 k--;
             }
             ready[k] = (uint16_t)i;
         }
+#pragma unroll 1
         for (int k = 0; k < nr; k++) {
             const int i = ready[k];
             Unit& un = u[i];
@@ -654,6 +673,7 @@ struct Sim {
     MRTS_HD void compact() {
         const int n = nunits();
         int k = 0;
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             if (u[i].flags & UF_DEAD) continue;
             if (k != i) {
@@ -669,6 +689,7 @@ struct Sim {
     MRTS_HD void eval_gameover() {
         int c0 = 0, c1 = 0;
         const int n = nunits();
+#pragma unroll 1
         for (int i = 0; i < n; i++)
             if (alive(i)) {
                 c0 += u[i].player == 0;
@@ -689,10 +710,12 @@ struct Sim {
     // PartiallyObservableGameState(gs, p): membership + assignment copy, recorded per unit
     MRTS_HD void make_view(int p) {
         const int n = nunits();
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             Unit& un = u[i];
             bool in = un.player == p;
             if (!in) {
+#pragma unroll 1
                 for (int j = 0; j < n && !in; j++) {
                     const Unit& w = u[j];
                     if (w.player != p) continue;
@@ -713,23 +736,28 @@ struct Sim {
     // ================================================================== scripted opponents
     // AbstractionLayerAI table helpers (J/ai/abstraction/AbstractionLayerAI.java:36,115-141)
     MRTS_HD int aa_find(uint16_t uid) const {
+#pragma unroll 1
         for (int k = 0; k < hdr->n_aa; k++)
             if (aa[k].unit == uid) return k;
         return -1;
     }
-    MRTS_HD void aa_put(const AbstractAct& r) {  // LinkedHashMap.put: re-put keeps the slot
+    MRTS_HD void aa_put(const AbstractAct& r, int i) {  // LinkedHashMap.put: re-put keeps the slot; i = the unit's index
         int k = aa_find(r.unit);
         if (k < 0) {
             if (hdr->n_aa >= cap) return;
             k = hdr->n_aa++;
         }
         aa[k] = r;
+        // UF_AA_ATTACK mirrors "this unit's table entry is an Attack" (see worker_rush)
+        if (r.kind == AA_ATTACK) u[i].flags |= UF_AA_ATTACK;
+        else u[i].flags &= (uint8_t)~UF_AA_ATTACK;
     }
     // The unit array is in creation order and uids are handed out in creation order (template
     // index, then next_uid++), compaction is stable: the array is sorted by uid.
     MRTS_HD int find_uid(uint16_t uid, int vp) const {  // pgs.getUnits().contains(u) on the view
         if (uid == NO_UID) return -1;
         int lo = 0, hi = nunits();
+#pragma unroll 1
         while (lo < hi) {
             const int mid = (lo + hi) >> 1;
             if (u[mid].uid < uid) lo = mid + 1;
@@ -791,7 +819,9 @@ struct Sim {
     // once per game pass, by the whole thread group, before the leader runs (the region is scratch)
     MRTS_HD void astar_init(int tid, int nth) {
         AStarBuf b = astar_buf();
+#pragma unroll 1
         for (int k = tid; k < astar_nf(); k += nth) b.head[k] = -1;
+#pragma unroll 1
         for (int k = tid; k < HW; k += nth) b.stamp[k] = 0;
         st->astar_gen = 0;
     }
@@ -812,6 +842,7 @@ struct Sim {
         int fmin = h0, fmax = h0, flo = h0, nopen = 1;
         bool found = false;
         int pos = startPos;
+#pragma unroll 1
         while (nopen > 0) {
             while (b.head[fmin] < 0) fmin++;
             pos = b.head[fmin];
@@ -844,9 +875,11 @@ struct Sim {
                 nopen++;
             }
         }
+#pragma unroll 1
         for (int f = flo; f <= fmax; f++) b.head[f] = -1;  // leave the stacks empty for the next search
         if (!found) return -1;
         int last = pos, parent = b.parent[pos];
+#pragma unroll 1
         while (parent != pos) {
             last = pos;
             pos = parent;
@@ -865,6 +898,7 @@ struct Sim {
         bool first = true;
         const int n = nunits();
         const bool harv = ut_can_harvest(ut);
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             if (!inview(i, vp)) continue;
             const Unit& o = u[i];
@@ -994,18 +1028,21 @@ struct Sim {
     }
 
     // AbstractionLayerAI.translateActions, AbstractionLayerAI.java:58-113 -> pa2
-    MRTS_HD void translate_actions(int player, int vp) {
+    MRTS_HD void translate_actions(int player, int vp, bool enemy_seen) {
         int costB[2];
         pending_usage(bitsB, costB, vp);
         bits_clear(bitsC);
         st->npa2 = 0;
         int na = hdr->n_aa, keep = 0;
+#pragma unroll 1
         for (int k = 0; k < na; k++) {
             AbstractAct r = aa[k];
             int i = find_uid(r.unit, vp);
             bool del = false;
             if (i < 0) del = true;
-            else if (aa_completed(r, i, vp)) del = true;
+            else if (enemy_seen && u[i].a_type >= 0 && (u[i].flags & UF_AA_ATTACK) && ut_can_harvest(u[i].type)) {
+                // busy worker with an Attack entry: the reference's per-frame re-put keeps it alive (see worker_rush)
+            } else if (aa_completed(r, i, vp)) del = true;
             else if (u[i].a_type < 0) {
                 PAct out;
                 if (aa_execute(r, i, vp, costB, out)) {
@@ -1015,12 +1052,15 @@ struct Sim {
                 }
             }
             if (!del) aa[keep++] = r;  // r may carry Train's completed flag
+            else if (i >= 0) u[i].flags &= (uint8_t)~UF_AA_ATTACK;
         }
         hdr->n_aa = (uint16_t)keep;
         // accept desires first-come-first-served against the pending usage
+#pragma unroll 1
         for (int w = 0; w < nbits_words; w++) bitsA[w] = bitsB[w];
         int used0 = costB[0], used1 = costB[1];
         int kept = 0;
+#pragma unroll 1
         for (int k = 0; k < st->npa2; k++) {
             PAct d = pa2[k];
             const Unit& un = u[d.unit];
@@ -1040,11 +1080,13 @@ struct Sim {
     // AbstractionLayerAI.findBuildingPosition, AbstractionLayerAI.java:143-228 (reserved list is empty for WorkerRush)
     MRTS_HD int find_building_position(int dX, int dY, int vp) const {
         const int mx = H > W ? H : W;
+#pragma unroll 1
         for (int l = 1; l < mx; l++) {
             for (int side = 0; side < 4; side++) {
                 const bool horiz = (side == 0 || side == 2);
                 const int fixed = side == 0 ? dY - l : side == 1 ? dX + l : side == 2 ? dY + l : dX - l;
                 if (fixed < 0 || fixed >= (horiz ? H : W)) continue;
+#pragma unroll 1
                 for (int dd = -l; dd <= l; dd++) {
                     int x = horiz ? dX + dd : fixed;
                     int y = horiz ? fixed : dY + dd;
@@ -1059,6 +1101,7 @@ struct Sim {
     MRTS_HD void bot_melee(int i, int player, int vp) {  // WorkerRush.meleeUnitBehavior, WorkerRush.java:106-122
         int closest = -1, cd = 0;
         const int n = nunits();
+#pragma unroll 1
         for (int j = 0; j < n; j++) {
             if (!inview(j, vp)) continue;
             const Unit& o = u[j];
@@ -1077,7 +1120,7 @@ struct Sim {
             r.x = r.y = 0;
             r.target = u[closest].uid;
             r.base = NO_UID;
-            aa_put(r);
+            aa_put(r, i);
         }
     }
     MRTS_HD void aa_harvest(int i, int target, int base) {
@@ -1088,12 +1131,13 @@ struct Sim {
         r.x = r.y = 0;
         r.target = target >= 0 ? u[target].uid : (uint16_t)NO_UID;
         r.base = base >= 0 ? u[base].uid : (uint16_t)NO_UID;
-        aa_put(r);
+        aa_put(r, i);
     }
     // WorkerRush.workersBehavior tail, WorkerRush.java:148-197: true = the worker stays free
     MRTS_HD bool bot_harvest(int w, int player, int vp) {
         int cres = -1, cbase = -1, cd = 0;
         const int n = nunits();
+#pragma unroll 1
         for (int j = 0; j < n; j++) {
             if (!inview(j, vp) || !ut_is_resource(u[j].type)) continue;
             int d = iabs(u[j].x - u[w].x) + iabs(u[j].y - u[w].y);
@@ -1103,6 +1147,7 @@ struct Sim {
             }
         }
         cd = 0;
+#pragma unroll 1
         for (int j = 0; j < n; j++) {
             if (!inview(j, vp) || !ut_is_stockpile(u[j].type) || u[j].player != player) continue;
             int d = iabs(u[j].x - u[w].x) + iabs(u[j].y - u[w].y);
@@ -1128,9 +1173,35 @@ struct Sim {
     }
 
     // WorkerRush.getAction, J/ai/abstraction/WorkerRush.java:63-104 -> pa2
+    //
+    // The reference re-puts Attack(closest enemy) for EVERY free worker on every frame, busy or not
+    // (workersBehavior, :198-203).  For a worker that is busy and whose table entry already is an
+    // Attack the re-put is unobservable: the slot is kept (LinkedHashMap.put), the target is only read
+    // when the worker is idle (that frame's put is executed here as well), and because the fresh
+    // target is a unit of this frame's view the entry is never "completed" in translateActions.  So
+    // such workers are skipped and translate_actions keeps their entry -- provided an enemy is in
+    // view at all (otherwise the reference puts nothing and the stale entry is checked as usual).
     MRTS_HD void worker_rush(int player, int vp) {
         const int n = nunits();
         const int pres = hdr->res[player];
+        // one pass: census (:124-137) + is any enemy in view
+        int nbases = 0, nworkers = 0, w0 = -1, w1 = -1;
+        bool enemy_seen = false;
+#pragma unroll 1
+        for (int i = 0; i < n; i++) {
+            const Unit& un = u[i];
+            if (un.player == player) {
+                if (un.type == UT_BASE) nbases++;
+                if (ut_can_harvest(un.type)) {
+                    if (nworkers == 0) w0 = i;
+                    else if (nworkers == 1) w1 = i;
+                    nworkers++;
+                }
+            } else if (un.player >= 0 && inview(i, vp)) {
+                enemy_seen = true;
+            }
+        }
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             const Unit& un = u[i];
             if (un.type == UT_BASE && un.player == player && un.a_type < 0 && pres >= ut_cost(UT_WORKER)) {
@@ -1141,29 +1212,19 @@ struct Sim {
                 r.x = r.y = 0;
                 r.target = 0;
                 r.base = NO_UID;
-                aa_put(r);
+                aa_put(r, i);
             }
         }
+#pragma unroll 1
         for (int i = 0; i < n; i++) {
             const Unit& un = u[i];
             if (ut_can_attack(un.type) && !ut_can_harvest(un.type) && un.player == player && un.a_type < 0) o_bot_melee(self, i, player, vp);
         }
         // workersBehavior, WorkerRush.java:124-204
-        int nbases = 0, nworkers = 0;
-        for (int i = 0; i < n; i++) {
-            if (u[i].player != player) continue;
-            if (u[i].type == UT_BASE) nbases++;
-            if (ut_can_harvest(u[i].type)) nworkers++;
-        }
         if (nworkers > 0) {
-            int builder = -1, harvester = -1, seen = 0;
             const bool want_base = nbases == 0 && pres >= ut_cost(UT_BASE);
-            for (int i = 0; i < n && (harvester < 0); i++) {
-                if (u[i].player != player || !ut_can_harvest(u[i].type)) continue;
-                if (seen == 0 && want_base) builder = i;
-                else harvester = i;
-                seen++;
-            }
+            const int builder = want_base ? w0 : -1;
+            const int harvester = want_base ? w1 : w0;
             if (builder >= 0) {  // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245
                 int k = aa_find(u[builder].uid);
                 if (k < 0 || aa[k].kind != AA_BUILD || aa[k].utype != UT_BASE) {
@@ -1176,19 +1237,22 @@ struct Sim {
                     r.y = (int16_t)(pos / W);
                     r.target = NO_UID;
                     r.base = NO_UID;
-                    aa_put(r);
+                    aa_put(r, builder);
                 }
             }
             bool hfree = false;
             if (harvester >= 0) hfree = bot_harvest(harvester, player, vp);
+#pragma unroll 1
             for (int i = 0; i < n; i++) {
-                if (u[i].player != player || !ut_can_harvest(u[i].type)) continue;
+                const Unit& un = u[i];
+                if (un.player != player || !ut_can_harvest(un.type)) continue;
                 if (i == builder || i == harvester) continue;
+                if (enemy_seen && un.a_type >= 0 && (un.flags & UF_AA_ATTACK)) continue;  // unobservable re-put, see above
                 o_bot_melee(self, i, player, vp);
             }
             if (hfree) o_bot_melee(self, harvester, player, vp);
         }
-        translate_actions(player, vp);
+        translate_actions(player, vp, enemy_seen);
     }
 
     // the scripted opponent's PlayerAction for `player` -> pa2

@@ -49,15 +49,15 @@ __global__ void mrts_pass_kernel(const EnvParams P) {
 struct WarpSync {
     __device__ __forceinline__ void operator()() const { __syncwarp(); }
 };
-constexpr int GPB = 4;
+constexpr int GPB_MAX = 4;  // games per block is chosen per environment (mrts_env::gpb), see choose_gpb
 #ifndef MRTS_WARP_MIN_BLOCKS
 #define MRTS_WARP_MIN_BLOCKS 5
 #endif
 template <int ELEM, int PLANES>
-__global__ void __launch_bounds__(32 * GPB, MRTS_WARP_MIN_BLOCKS) mrts_pass_warp_kernel(const EnvParams P, const int smem_per_game) {
+__global__ void __launch_bounds__(32 * GPB_MAX, MRTS_WARP_MIN_BLOCKS) mrts_pass_warp_kernel(const EnvParams P, const int smem_per_game) {
     extern __shared__ uint4 smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int g = blockIdx.x * GPB + warp;
+    const int g = blockIdx.x * (blockDim.x >> 5) + warp;
     if (g >= P.n_games) return;
     game_pass<ELEM, PLANES>(P, g, (uint8_t*)smem_raw + (size_t)warp * smem_per_game, lane, 32, WarpSync());
 }
@@ -128,6 +128,7 @@ struct mrts_env {
     EnvParams P;
     int device = 0;
     int threads = 64;
+    int gpb = 1;  // warp kernel: games (warps) per block
     int smem = 0;
     int N = 0;
     std::vector<void*> allocs;
@@ -169,6 +170,7 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     P.next_actions = next_actions;
     P.seed = seed;
     P.counter = next_actions ? e->sample_counter++ : 0;
+    const int GPB = e->gpb;
     const dim3 wgrid((P.n_games + GPB - 1) / GPB), bgrid(P.n_games);
     const cudaStream_t st = (cudaStream_t)stream;
 #define MRTS_LAUNCH(E, PL)                                                                       \
@@ -230,37 +232,51 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         e->d_flag = (int*)d;
     }
 
-    e->threads = cfg->threads_per_game > 0 ? cfg->threads_per_game : choose_threads(HW);
+    // threads_per_game: 0 = choose; n > 0 = n threads per game; n < 0 = warp kernel with -n games per block (tuning)
+    e->threads = cfg->threads_per_game > 0 ? cfg->threads_per_game : (cfg->threads_per_game < 0 ? 32 : choose_threads(HW));
     if (e->threads > 1024) e->threads = 1024;
     if (e->threads < 32 || (e->threads & 31)) {
         mrts_destroy(e);
         return fail(MRTS_EINVAL, "threads_per_game must be a multiple of 32");
     }
     e->smem = layout_of(P).total;
-    int maxsm = 0;
+    int maxsm = 0, smem_sm = 0, max_blocks = 32;
     cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device);
-    if (e->smem > maxsm || (e->threads == 32 && GPB * e->smem > maxsm)) {
-        if (e->threads == 32 && e->smem <= maxsm) e->threads = 64;  // too large for GPB games per block: one block per game
-    }
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, cfg->device);
+    cudaDeviceGetAttribute(&max_blocks, cudaDevAttrMaxBlocksPerMultiprocessor, cfg->device);
     if (e->smem > maxsm) {
         mrts_destroy(e);
         return fail(MRTS_EINVAL, "map too large for shared-memory staging");
     }
-    {
-        const int wbytes = e->threads == 32 ? GPB * e->smem : 48 * 1024;
-        if (GPB * e->smem > 48 * 1024) {
+    if (e->threads == 32) {
+        // Games per block: a block's shared memory and warp slots are only released when its slowest
+        // game is done and game times vary widely (scripted-bot path finding), so take the smallest
+        // count that still reaches the most resident games per SM.
+        int best = 1, best_w = 0;
+        for (int g = 1; g <= GPB_MAX; g *= 2) {
+            if (g * e->smem > maxsm) break;
+            int blocks = smem_sm / (g * e->smem + 1024);  // 1 KB per-block reservation
+            if (blocks > max_blocks) blocks = max_blocks;
+            int w = blocks * g;
+            if (w > 64) w = 64;
+            if (w > best_w) best_w = w, best = g;
+        }
+        e->gpb = cfg->threads_per_game < 0 ? -cfg->threads_per_game : best;
+        if (e->gpb > GPB_MAX) e->gpb = GPB_MAX;
+        const int wbytes = e->gpb * e->smem;
+        if (wbytes > 48 * 1024) {
             cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
             cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
             cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
             cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
         }
-        if (e->smem > 48 * 1024) {
-            cudaFuncSetAttribute(mrts_pass_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
-            cudaFuncSetAttribute(mrts_pass_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
-            cudaFuncSetAttribute(mrts_pass_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
-            cudaFuncSetAttribute(mrts_pass_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
-            cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
-        }
+    }
+    if (e->smem > 48 * 1024) {
+        cudaFuncSetAttribute(mrts_pass_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+        cudaFuncSetAttribute(mrts_pass_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+        cudaFuncSetAttribute(mrts_pass_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+        cudaFuncSetAttribute(mrts_pass_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
+        cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
     }
     // start every game from its template so that the state is defined before the first reset()
     rc = launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);

@@ -77,7 +77,8 @@ struct Unit {  // 32 bytes
     uint16_t pre;     // this step's decoded agent action for the unit (pack_action), staged by the whole group before the rules run
 };
 static_assert(sizeof(Unit) == 32, "Unit must be 32 bytes");
-enum { UF_DEAD = 1, UF_THIS_STEP = 2, UF_LISTED = 4 /* scratch mark of fill_with_nones, always cleared again */ };
+enum { UF_DEAD = 1, UF_THIS_STEP = 2, UF_LISTED = 4 /* scratch mark of fill_with_nones, always cleared again */,
+       UF_AA_ATTACK = 8 /* scripted bot: the unit's abstract-action entry is an Attack */ };
 
 // abstract action of the scripted bots (J/ai/abstraction/{Train,Build,Harvest,Attack}.java)
 enum { AA_TRAIN = 0, AA_BUILD = 1, AA_HARVEST = 2, AA_ATTACK = 3 };
