@@ -55,6 +55,8 @@ typedef struct mrts_config {
     const int32_t* bot_ai;     /* num_bot_envs entries: MRTS_AI_*                                  */
     int32_t elem_bytes;        /* 4 = int32 obs/mask (reference dtype), 1 = uint8                  */
     int32_t threads_per_game;  /* 0 = choose from the map size; n > 0 = n threads per game; n < 0 = one warp per game, -n games per block */
+    int32_t staged_units;      /* 0 = choose; units per game staged in shared memory by the warp kernel (games that may
+                                  outgrow it take the full-capacity launch); tuning / tests                          */
 } mrts_config;
 
 typedef struct mrts_env mrts_env;

@@ -49,6 +49,7 @@ class ConfigC(C.Structure):
         ("bot_ai", C.c_void_p),
         ("elem_bytes", C.c_int32),
         ("threads_per_game", C.c_int32),
+        ("staged_units", C.c_int32),
     ]
 
 
@@ -75,6 +76,7 @@ def make_config(
     device: int = 0,
     elem_bytes: int = 4,
     threads_per_game: int = 0,
+    staged_units: int = 0,
 ):
     """Build an ``mrts_config``.  ``templates`` has one entry per env (as ``map_paths`` after
     broadcasting); identical templates are de-duplicated by object identity / name.
@@ -121,6 +123,7 @@ def make_config(
     cfg.bot_ai = ai.ctypes.data if len(ai) else None
     cfg.elem_bytes = elem_bytes
     cfg.threads_per_game = threads_per_game
+    cfg.staged_units = staged_units
     return cfg, keep
 
 

@@ -62,6 +62,7 @@ struct St {
     int astar_gen;   // search counter (stamp generation)
     int gameover, winner;
     int reset;
+    int nprod;       // pending PRODUCE assignments at load (capacity check)
     int rew[2][6];   // integer reward terms per player view (exact small integers)
 };
 

@@ -62,6 +62,19 @@ __global__ void __launch_bounds__(32 * GPB_MAX, MRTS_WARP_MIN_BLOCKS) mrts_pass_
     game_pass<ELEM, PLANES>(P, g, (uint8_t*)smem_raw + (size_t)warp * smem_per_game, lane, 32, WarpSync());
 }
 
+// Games the warp kernel deferred because their unit table may outgrow the staged capacity
+// (EnvParams::scap): same pass, one block per game, shared memory sized for the full capacity.
+// P.ovf is null here (nothing can be deferred again); `list` = [count, game indices...].
+template <int ELEM, int PLANES>
+__global__ void __launch_bounds__(128) mrts_overflow_kernel(const EnvParams P, const int32_t* list) {
+    extern __shared__ uint4 smem_raw[];
+    const int count = list[0];
+    for (int k = blockIdx.x; k < count; k += gridDim.x) {
+        game_pass<ELEM, PLANES>(P, list[1 + k], (uint8_t*)smem_raw, (int)threadIdx.x, (int)blockDim.x, BlockSync());
+        __syncthreads();
+    }
+}
+
 // ---- raw engine access (trace replay): one block, one game
 struct DebugArgs {
     int game;
@@ -129,7 +142,9 @@ struct mrts_env {
     int device = 0;
     int threads = 64;
     int gpb = 1;  // warp kernel: games (warps) per block
-    int smem = 0;
+    int smem = 0;       // bytes per game at the staged capacity (P.scap)
+    int smem_full = 0;  // bytes per game at the full capacity (overflow / debug launches)
+    int32_t* d_ovf = nullptr;
     int N = 0;
     std::vector<void*> allocs;
     int* d_flag = nullptr;
@@ -173,10 +188,22 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     const int GPB = e->gpb;
     const dim3 wgrid((P.n_games + GPB - 1) / GPB), bgrid(P.n_games);
     const cudaStream_t st = (cudaStream_t)stream;
+    const bool defer = e->threads == 32 && P.scap < P.cap;
+    EnvParams F = P;  // full-capacity parameters of the overflow launch
+    F.scap = P.cap;
+    F.ovf = nullptr;
+    if (defer) {
+        P.ovf = e->d_ovf;
+        CK(cudaMemsetAsync(e->d_ovf, 0, sizeof(int32_t), st));
+    } else {
+        P.ovf = nullptr;
+    }
+    const int ogrid = P.n_games < 296 ? P.n_games : 296;
 #define MRTS_LAUNCH(E, PL)                                                                       \
     do {                                                                                         \
         if (e->threads == 32) mrts_pass_warp_kernel<E, PL><<<wgrid, 32 * GPB, GPB * e->smem, st>>>(P, e->smem); \
         else mrts_pass_kernel<E, PL><<<bgrid, e->threads, e->smem, st>>>(P);                     \
+        if (defer) mrts_overflow_kernel<E, PL><<<ogrid, 128, e->smem_full, st>>>(F, e->d_ovf);   \
     } while (0)
     if (P.elem == 4 && P.planes == 29) MRTS_LAUNCH(4, 29);
     else if (P.elem == 4) MRTS_LAUNCH(4, 31);
@@ -239,12 +266,39 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         mrts_destroy(e);
         return fail(MRTS_EINVAL, "threads_per_game must be a multiple of 32");
     }
+    {
+        EnvParams F = P;
+        F.scap = P.cap;
+        e->smem_full = layout_of(F).total;
+    }
+    // Staged unit capacity of the warp kernel: the blob in HBM holds `cap` units (the proven bound:
+    // initial units + every resource on the map), shared memory only `scap`; a game that could
+    // outgrow it during a step is deferred to mrts_overflow_kernel.  cfg->staged_units overrides.
+    P.scap = P.cap;
+    if (e->threads == 32 && (P.cap > 64 || cfg->staged_units > 0)) {
+        int most = 0;
+        for (const MapTpl& t : S.tpls) most = t.nunits > most ? t.nunits : most;
+        int want = cfg->staged_units > 0 ? cfg->staged_units : (HW <= 256 ? 48 : 64);
+        if (cfg->staged_units <= 0 && want < most + 16) want = most + 16;
+        if (want < most) want = most;  // a reset must always fit
+        if (want < P.cap) P.scap = want;
+    }
     e->smem = layout_of(P).total;
+    if (P.scap < P.cap) {
+        void* o = nullptr;
+        ce = cudaMalloc(&o, sizeof(int32_t) * (size_t)(P.n_games + 1));
+        if (ce != cudaSuccess) {
+            mrts_destroy(e);
+            return fail(MRTS_ENOMEM, std::string("cudaMalloc(overflow list): ") + cudaGetErrorString(ce));
+        }
+        e->allocs.push_back(o);
+        e->d_ovf = (int32_t*)o;
+    }
     int maxsm = 0, smem_sm = 0, max_blocks = 32;
     cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device);
     cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, cfg->device);
     cudaDeviceGetAttribute(&max_blocks, cudaDevAttrMaxBlocksPerMultiprocessor, cfg->device);
-    if (e->smem > maxsm) {
+    if (e->smem > maxsm || e->smem_full > maxsm) {
         mrts_destroy(e);
         return fail(MRTS_EINVAL, "map too large for shared-memory staging");
     }
@@ -271,12 +325,18 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
             cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
         }
     }
+    if (e->smem_full > 48 * 1024) {
+        cudaFuncSetAttribute(mrts_overflow_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_full);
+        cudaFuncSetAttribute(mrts_overflow_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_full);
+        cudaFuncSetAttribute(mrts_overflow_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_full);
+        cudaFuncSetAttribute(mrts_overflow_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_full);
+        cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_full);
+    }
     if (e->smem > 48 * 1024) {
         cudaFuncSetAttribute(mrts_pass_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
         cudaFuncSetAttribute(mrts_pass_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
         cudaFuncSetAttribute(mrts_pass_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
         cudaFuncSetAttribute(mrts_pass_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
-        cudaFuncSetAttribute(mrts_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem);
     }
     // start every game from its template so that the state is defined before the first reset()
     rc = launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
@@ -359,7 +419,10 @@ static int debug_launch(mrts_env* e, int game, int op, const int32_t* rows7, int
         CK(cudaMemcpyAsync(e->d_rows, rows7, (size_t)n * 7 * sizeof(int32_t), cudaMemcpyHostToDevice, (cudaStream_t)stream));
         A.rows7 = e->d_rows;
     }
-    mrts_debug_kernel<<<1, 64, e->smem, (cudaStream_t)stream>>>(e->P, A);
+    EnvParams F = e->P;
+    F.scap = F.cap;
+    F.ovf = nullptr;
+    mrts_debug_kernel<<<1, 64, e->smem_full, (cudaStream_t)stream>>>(F, A);
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize((cudaStream_t)stream));
     if (op == 1 && gameover) CK(cudaMemcpy(gameover, e->d_flag, sizeof(int), cudaMemcpyDeviceToHost));

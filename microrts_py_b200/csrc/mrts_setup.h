@@ -108,6 +108,8 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
     P.H = H;
     P.HW = HW;
     P.cap = cap;
+    P.scap = cap;  // the CUDA library may stage fewer (mrts_create)
+    P.ovf = nullptr;
     P.partial = cfg->partial_obs ? 1 : 0;
     P.planes = P.partial ? 31 : 29;
     P.none_mode = cfg->none_mode ? NONE_FORK : NONE_UPSTREAM;

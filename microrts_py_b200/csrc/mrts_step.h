@@ -15,7 +15,9 @@ enum { MODE_STEP = 0, MODE_RESET = 1, MODE_OBSERVE = 2 };
 struct EnvParams {
     int32_t num_selfplay, num_bot;  // player views, as in the reference constructor
     int32_t n_games;                // num_selfplay / 2 + num_bot
-    int32_t W, H, HW, cap, planes;
+    int32_t W, H, HW, cap, planes;  // cap = unit capacity of a game blob in HBM
+    int32_t scap;                   // unit capacity staged in shared memory by this launch (<= cap); games that may exceed it go to `ovf`
+    int32_t* ovf;                   // [0] = count, [1..] = game indices deferred to the full-capacity launch; null = no deferral
     int32_t partial, none_mode, max_steps;
     int32_t has_bot;                // any WorkerRush game: blob carries the abstract-action table
     int32_t game_stride;            // bytes per game blob
@@ -47,7 +49,7 @@ struct Layout {
 // Shared-memory plan of one game.  The rules scratch (PlayerActions, reservation bitmaps, A*
 // arrays) is dead once the leader is done, the output scratch (observation words, per-unit
 // legal-action sets) is only written after that: the two share one region.
-MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int nviews = 2) {
+MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot) {
     Layout L;
     int o = 0;
     L.blob = o;
@@ -73,28 +75,28 @@ MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int nviews = 2) 
     // ---- output scratch (aliases the rules scratch)
     o = scratch;
     L.words = o;
-    o += align16(nviews * HW * 4);
+    o += align16(HW * 4);  // one view at a time
     L.umask = o;
     o += align16(cap * 12);
     L.total = o > end_rules ? o : end_rules;
     return L;
 }
 
-MRTS_HD Layout layout_of(const EnvParams& P) { return make_layout(P.W, P.HW, P.cap, P.has_bot, P.num_selfplay > 0 ? 2 : 1); }
+MRTS_HD Layout layout_of(const EnvParams& P) { return make_layout(P.W, P.HW, P.scap, P.has_bot); }
 
 // point a Sim at one game's shared-memory regions
 MRTS_HD void bind_sim(Sim& s, const EnvParams& P, const Layout& L, uint8_t* mem, int g) {
     s.W = P.W;
     s.H = P.H;
     s.HW = P.HW;
-    s.cap = P.cap;
+    s.cap = P.scap;
     s.none_mode = P.none_mode;
     s.partial = P.partial;
     s.max_steps = P.max_steps;
     s.ai = P.game_ai[g];
     s.hdr = (GameHdr*)(mem + L.blob);
     s.u = (Unit*)(mem + L.blob + 32);
-    s.aa = (AbstractAct*)(mem + L.blob + 32 + P.cap * 32);
+    s.aa = (AbstractAct*)(mem + L.blob + 32 + P.scap * 32);
     s.grid = (uint16_t*)(mem + L.grid);
     s.pa = (PAct*)(mem + L.pa);
     s.pa2 = (PAct*)(mem + L.pa2);
@@ -118,6 +120,24 @@ MRTS_HD void copy16(void* dst, const void* src, int bytes, int tid, int nth) {  
 struct alignas(16) Q16 {
     uint32_t a, b, c, d;
 };
+
+MRTS_HD void group_add(int* p, int v) {
+#if defined(__CUDA_ARCH__)
+    atomicAdd(p, v);
+#else
+    *p += v;
+#endif
+}
+// queue game g for the full-capacity launch (mrts_kernels.cu: mrts_overflow_kernel)
+MRTS_HD void defer_game(const EnvParams& P, int g) {
+#if defined(__CUDA_ARCH__)
+    const int k = atomicAdd(P.ovf, 1);
+    P.ovf[1 + k] = g;
+#else
+    (void)P;
+    (void)g;
+#endif
+}
 
 // SYNC: functor executing a barrier over the game's thread group.
 template <int ELEM, int PLANES, class SYNC>
@@ -163,6 +183,10 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     } else {
         const GameHdr* gh = (const GameHdr*)gblob;
         const int n = gh->nunits, naa = gh->n_aa;
+        if (n > P.scap) {  // does not fit the staged capacity: leave the game untouched for the full-capacity launch
+            if (tid == 0) defer_game(P, g);
+            return;
+        }
         copy16<Q16>(mem + L.blob, gblob, 32 + n * 32, tid, nth);
         if (P.has_bot && naa > 0) copy16<Q16>(s.aa, gblob + 32 + P.cap * 32, align16(naa * 12), tid, nth);
         copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
@@ -171,13 +195,26 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (tid == 0) {
         *(Sim*)(mem + L.sim) = s;
         St z;
-        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = 0;
+        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = 0;
         z.winner = -1;
         for (int p = 0; p < 2; p++)
             for (int k = 0; k < 6; k++) z.rew[p][k] = 0;
         *s.st = z;
     }
     sync();
+    if (P.mode == MODE_STEP && P.scap < P.cap) {
+        // units can only be born from PRODUCE assignments pending at load (one issued now cannot complete
+        // in this cycle: produce times are >= 50): if they might not fit, defer before anything is written
+        const int n = s.hdr->nunits;
+        int mine = 0;
+        for (int i = tid; i < n; i += nth) mine += s.u[i].a_type == T_PRODUCE;
+        if (mine) group_add(&s.st->nprod, mine);
+        sync();
+        if (n + ((volatile St*)s.st)->nprod > P.scap) {
+            if (tid == 0) defer_game(P, g);
+            return;
+        }
+    }
     scatter_grid();
     // the agents' action rows of the units that may act, fetched by the whole group (the leader never waits on HBM)
     if (P.mode == MODE_STEP) s.prefetch_actions(P.actions + (size_t)env0 * P.HW * 7, tid, nth);
@@ -213,34 +250,30 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         }
     }
 
-    // ---------------- observation words of every view (before compaction: stale views keep the dead)
+    // ---------------- observations, one view at a time (before compaction: stale views keep the dead)
+    const size_t obs_env = (size_t)P.HW * PLANES * ELEM;
+    const size_t mask_env = (size_t)P.HW * 78 * ELEM;
     if (P.obs) {
-        for (int v = 0; v < nviews; v++) obs_words_cells(s, v, P.partial ? v : -1, grid0, words + v * P.HW, tid, nth);
-        if (P.partial) {
+        for (int v = 0; v < nviews; v++) {
+            obs_words_cells(s, v, P.partial ? v : -1, grid0, words, tid, nth);
+            if (P.partial) {
+                sync();
+                obs_words_dead(s, v, v, words, tid, nth);
+            }
             sync();
-            for (int v = 0; v < nviews; v++) obs_words_dead(s, v, v, words + v * P.HW, tid, nth);
+            store_obs<ELEM, PLANES>(words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, tid, nth);
+            sync();
         }
     }
-    sync();
     if (P.mode == MODE_STEP && !reset) {
         if (tid == 0) s.compact();
         sync();
     }
     if (P.mask || P.next_actions) unit_masks(s, umask, tid, nth);
 
-    // ---------------- bulk stores
-    const size_t obs_env = (size_t)P.HW * PLANES * ELEM;
-    const size_t mask_env = (size_t)P.HW * 78 * ELEM;
-    for (int v = 0; v < nviews; v++) {
-        if (P.obs) {
-            void* o = (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env;
-            store_obs<ELEM, PLANES>(words + v * P.HW, P.HW, o, tid, nth);
-        }
-        if (P.mask) {
-            void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;
-            zero_mask<ELEM>(P.HW, m, tid, nth);
-        }
-    }
+    // ---------------- mask: zero fill, then the 78 entries of every source unit
+    if (P.mask)
+        for (int v = 0; v < nviews; v++) zero_mask<ELEM>(P.HW, (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env, tid, nth);
     sync();  // zero-fill before patches (and umask complete)
     if (P.next_actions)
         for (int v = 0; v < nviews; v++)

@@ -127,6 +127,7 @@ class MicroRTSGridModeVecEnv:
         fuse_mask=True,
         microrts_path=None,
         threads_per_game=0,
+        staged_units=0,
     ):
         self.num_selfplay_envs = num_selfplay_envs
         self.num_bot_envs = num_bot_envs
@@ -189,7 +190,7 @@ class MicroRTSGridModeVecEnv:
         self._lib = _capi.lib()
         cfg, self._keep = _capi.make_config(
             num_selfplay_envs, num_bot_envs, max_steps, partial_obs, templates, ai_ids,
-            none_mode=_capi.NONE_FORK, device=dev_index, elem_bytes=self._np_dtype.itemsize, threads_per_game=threads_per_game,
+            none_mode=_capi.NONE_FORK, device=dev_index, elem_bytes=self._np_dtype.itemsize, threads_per_game=threads_per_game, staged_units=staged_units,
         )  # fmt: skip
         h = C.c_void_p()
         _capi.check(self._lib.mrts_create(C.byref(cfg), C.byref(h)))

@@ -143,3 +143,31 @@ def test_full_size_properties(mp, nsp, partial):
         np.testing.assert_array_equal(infos.raw[:sub].cpu().numpy(), r_ref)
         assert torch.equal(obs[:sub], obs[sub:2 * sub]) and torch.equal(d[:sub], d[sub:2 * sub])
     env.close()
+
+
+@pytest.mark.parametrize("staged", [8, 12])
+def test_games_outgrowing_the_staged_capacity_take_the_full_capacity_launch(staged):
+    """The warp kernel stages only `staged_units` units per game in shared memory; games that may
+    outgrow it are deferred to mrts_overflow_kernel (full blob capacity).  With a tiny staged
+    capacity most WorkerRush games cross over (and come back after resets): every step must still
+    equal the oracle bit for bit."""
+    ais = [W, P, W, W]
+    env = _env(4, 4, max_steps=400, ai2s=ais, map_paths=[MAP_16], staged_units=staged)
+    ref = _oracle(4, ais, MAP_16, max_steps=400)
+    rng = np.random.default_rng(21)
+    np.testing.assert_array_equal(env.reset(), ref.reset())
+    most = 0
+    for t in range(900):
+        m = env.get_action_mask()
+        m_ref, _ = ref.get_masks()
+        np.testing.assert_array_equal(m, m_ref, err_msg=f"mask {t}")
+        a = sample_actions(m_ref, rng, 0.03)
+        o, r, d, infos = env.step(a)
+        o2, r2, d2 = ref.step(a)
+        np.testing.assert_array_equal(o, o2, err_msg=f"obs {t}")
+        np.testing.assert_array_equal(np.stack([i["raw_rewards"] for i in infos]), r2, err_msg=f"reward {t}")
+        np.testing.assert_array_equal(d.astype(np.uint8), d2)
+        if t % 50 == 0:
+            most = max(most, max(len(env.export_state(g)[1]) for g in range(6)))
+    assert most > max(staged, 8), "the case was meant to exceed the staged capacity"
+    env.close()
