@@ -156,6 +156,7 @@ SYMBOLS = [
     "mrts_export_state",
     "mrts_debug_issue",
     "mrts_debug_cycle",
+    "mrts_debug_timing",
     "mrts_last_error",
     "mrts_version",
 ]
@@ -185,6 +186,7 @@ def lib():
         L.mrts_export_state.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
         L.mrts_debug_issue.argtypes = [vp, C.c_int, vp, C.c_int, vp]
         L.mrts_debug_cycle.argtypes = [vp, C.c_int, C.POINTER(C.c_int), vp]
+        L.mrts_debug_timing.argtypes = [vp, vp]
         L.mrts_last_error.restype = C.c_char_p
         L.mrts_version.restype = C.c_char_p
         _lib = L

@@ -38,6 +38,15 @@ struct PAct {  // one entry of a PlayerAction (unit, UnitAction)
 struct Mask78 {
     uint32_t w[3];
 };
+#if defined(MRTS_STATS) && !defined(__CUDA_ARCH__)
+#include <cstdio>
+struct MrtsStats { long searches = 0, pre_fail = 0, guard = 0, guard_fail = 0, expanded = 0; ~MrtsStats() { fprintf(stderr, "[mrts stats] searches %ld precheck-fail %ld guard %ld guard-fail %ld expansions %ld\n", searches, pre_fail, guard, guard_fail, expanded); } };
+inline MrtsStats& mrts_stats() { static MrtsStats s; return s; }
+#define MRTS_STAT(x) (mrts_stats().x)
+#else
+#define MRTS_STAT(x) ((void)0)
+#endif
+enum { ASTAR_GUARD_AFTER = 24 };  // expansions before a search is checked for reachability
 enum { MB_TYPE = 0, MB_MOVE = 6, MB_HARVEST = 10, MB_RETURN = 14, MB_PDIR = 18, MB_PTYPE = 22, MB_ATTACK = 29 };
 // no dynamic indexing of w[] (that would put the set in local memory); constant b folds away
 MRTS_HD void mset(Mask78& m, int b) {
@@ -53,7 +62,9 @@ MRTS_HD bool mget(const Mask78& m, int b) {
     return (w >> (b & 31)) & 1u;
 }
 
-MRTS_HD int astar_bytes(int W, int HW) { return ((3 * HW + (HW + W + (HW / W) + 2)) * 2 + HW * 2 + 15) & ~15; }
+// cost/parent/next per cell + one stack head per f value + stamps, then 3 row bitmaps (uint64 per map row) of the reachability guard
+MRTS_HD int astar_core_bytes(int W, int HW) { return ((3 * HW + (HW + W + (HW / W) + 2)) * 2 + HW * 2 + 15) & ~15; }
+MRTS_HD int astar_bytes(int W, int HW) { return astar_core_bytes(W, HW) + 3 * (HW / W) * 8; }
 
 // Per-step scalars the rules mutate; they live in the game's shared-memory region so that the
 // immutable view below (Sim) can be copied freely into the registers of out-of-line functions.
@@ -817,6 +828,110 @@ struct Sim {
         b.stamp = (uint16_t*)(b.head + astar_nf());
         return b;
     }
+    // ---- reachability guard of the search (see astar_first_move): row bitmaps, bit x of row y
+    MRTS_HD uint64_t* flood_rows() const { return (uint64_t*)((uint8_t*)astar + astar_core_bytes(W, HW)); }
+    // cells no search can enter because of the map or a unit (of the true state): built once per pass
+    // by the whole group; under partial observability the bot's view hides units, the leader
+    // rebuilds the rows for its view when it needs them
+    MRTS_HD void flood_base_rows(int vp, int tid, int nth) const {
+        if (W > 64) return;
+        uint64_t* F0 = flood_rows();
+#pragma unroll 1
+        for (int y = tid; y < H; y += nth) {
+            uint64_t row = 0;
+#pragma unroll 1
+            for (int x = 0; x < W; x++) {
+                const uint16_t g = grid[x + y * W];
+                if (g == G_NONE || (g < G_WALL && !inview(g, vp))) row |= 1ull << x;
+            }
+            F0[y] = row;
+        }
+    }
+    // W bits of a reservation bitmap (bit index = linear position + W) starting at the row's first cell
+    MRTS_HD uint64_t bits_row(const uint32_t* b, int y) const {
+        const int k0 = (y + 1) * W;
+        uint64_t row = 0;
+        int got = 0;
+#pragma unroll 1
+        while (got < W) {
+            const int k = k0 + got, w = k >> 5, o = k & 31;
+            const int take = (32 - o) < (W - got) ? (32 - o) : (W - got);
+            const uint32_t v = w < nbits_words ? b[w] : 0u;
+            row |= (uint64_t)((v >> o) & (take == 32 ? 0xFFFFFFFFu : ((1u << take) - 1u))) << got;
+            got += take;
+        }
+        return row;
+    }
+    static MRTS_HD uint64_t brev64(uint64_t v) {
+#if defined(__CUDA_ARCH__)
+        return __brevll(v);
+#else
+        uint64_t r = 0;
+        for (int k = 0; k < 64; k++) r |= ((v >> k) & 1ull) << (63 - k);
+        return r;
+#endif
+    }
+    // seeds S (subset of F) spread along the runs of ones of F, both ways (carry trick)
+    static MRTS_HD uint64_t hfill(uint64_t S, uint64_t F) {
+        const uint64_t up = (((F + S) ^ F) & F) | S;
+        const uint64_t Fr = brev64(F), Sr = brev64(S);
+        const uint64_t dn = (((Fr + Sr) ^ Fr) & Fr) | Sr;
+        return up | brev64(dn);
+    }
+    // Can a search from (sx,sy) ever pop a cell within `range` of (tx,ty)?  Flood fill of the
+    // enterable cells (exactly the cells astar_first_move would accept as neighbours) from the start.
+    // Only used to cut a search short that is bound to fail, so the result of the search is unchanged.
+    MRTS_HD bool flood_reaches(int sx, int sy, int tx, int ty, int range, int vp, bool rebuild_base) const {
+        if (W > 64) return true;  // no guard for wider maps
+        uint64_t* F0 = flood_rows();
+        uint64_t* F = F0 + H;
+        uint64_t* R = F + H;
+        if (rebuild_base) flood_base_rows(vp, 0, 1);
+#pragma unroll 1
+        for (int y = 0; y < H; y++) {
+            F[y] = F0[y] & ~bits_row(bitsB, y) & ~bits_row(bitsC, y);
+            R[y] = 0;
+        }
+        // the start cell itself is occupied: seed its enterable neighbours
+        if (sy > 0) R[sy - 1] = (1ull << sx) & F[sy - 1];
+        if (sy + 1 < H) R[sy + 1] = (1ull << sx) & F[sy + 1];
+        R[sy] = hfill((((1ull << sx) << 1) | ((1ull << sx) >> 1)) & F[sy], F[sy]);
+        bool changed = true;
+#pragma unroll 1
+        while (changed) {
+            changed = false;
+#pragma unroll 1
+            for (int pass = 0; pass < 2; pass++) {
+#pragma unroll 1
+                for (int k = 0; k < H; k++) {
+                    const int y = pass == 0 ? k : H - 1 - k;
+                    uint64_t seeds = R[y];
+                    if (y > 0) seeds |= R[y - 1];
+                    if (y + 1 < H) seeds |= R[y + 1];
+                    seeds &= F[y];
+                    const uint64_t filled = hfill(seeds, F[y]);
+                    if (filled != R[y]) {
+                        R[y] = filled;
+                        changed = true;
+                    }
+                }
+            }
+        }
+        const int sq = range * range;
+#pragma unroll 1
+        for (int dy = -range; dy <= range; dy++) {
+            const int y = ty + dy;
+            if (y < 0 || y >= H) continue;
+#pragma unroll 1
+            for (int dx = -range; dx <= range; dx++) {
+                const int x = tx + dx;
+                if (x < 0 || x >= W || dx * dx + dy * dy > sq) continue;
+                if ((R[y] >> x) & 1ull) return true;
+            }
+        }
+        return false;
+    }
+
     // once per game pass, by the whole thread group, before the leader runs (the region is scratch)
     MRTS_HD void astar_init(int tid, int nth) {
         AStarBuf b = astar_buf();
@@ -835,6 +950,28 @@ struct Sim {
         const int sq = range * range;
         const int startPos = su.y * W + su.x;
         const int h0 = iabs(su.x - tx) + iabs(su.y - ty);
+        // A search only ever pops its start or cells it accepted as enterable neighbours.  If the
+        // start is out of range and no enterable cell is in range the reference's search exhausts
+        // the reachable map and returns null -- the usual case of a worker queueing behind others
+        // around an enclosed target, retried on every frame: same answer here without the search.
+        if ((su.x - tx) * (su.x - tx) + (su.y - ty) * (su.y - ty) > sq) {
+            bool any = false;
+#pragma unroll 1
+            for (int dy = -range; dy <= range && !any; dy++) {
+#pragma unroll 1
+                for (int dx = -range; dx <= range && !any; dx++) {
+                    const int x = tx + dx, y = ty + dy;
+                    if (dx * dx + dy * dy > sq || x < 0 || y < 0 || x >= W || y >= H) continue;
+                    any = free_cell(x, y, vp) && !bit_get(bitsC, x + y * W);
+                }
+            }
+            if (!any) {
+                MRTS_STAT(pre_fail++);
+                return -1;
+            }
+        }
+        MRTS_STAT(searches++);
+        int expanded = 0;
         b.parent[startPos] = (int16_t)startPos;
         b.cost[startPos] = 0;
         b.stamp[startPos] = gen;
@@ -853,6 +990,15 @@ struct Sim {
             if ((x - tx) * (x - tx) + (y - ty) * (y - ty) <= sq) {
                 found = true;
                 break;
+            }
+            // a search that keeps growing is checked once against a flood fill: unreachable -> null right away
+            MRTS_STAT(expanded++);
+            if (++expanded == ASTAR_GUARD_AFTER) {
+                MRTS_STAT(guard++);
+                if (!flood_reaches(su.x, su.y, tx, ty, range, vp, partial != 0)) {
+                    MRTS_STAT(guard_fail++);
+                    break;
+                }
             }
             const int g1 = b.cost[pos] + 1;
             // neighbours in the reference's order: up, right, down, left (:236-262)

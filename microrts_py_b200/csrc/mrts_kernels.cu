@@ -145,6 +145,7 @@ struct mrts_env {
     int smem = 0;       // bytes per game at the staged capacity (P.scap)
     int smem_full = 0;  // bytes per game at the full capacity (overflow / debug launches)
     int32_t* d_ovf = nullptr;
+    long long* d_timing = nullptr;  // profiling aid (mrts_debug_timing)
     int N = 0;
     std::vector<void*> allocs;
     int* d_flag = nullptr;
@@ -185,6 +186,7 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     P.next_actions = next_actions;
     P.seed = seed;
     P.counter = next_actions ? e->sample_counter++ : 0;
+    P.timing = e->d_timing;
     const int GPB = e->gpb;
     const dim3 wgrid((P.n_games + GPB - 1) / GPB), bgrid(P.n_games);
     const cudaStream_t st = (cudaStream_t)stream;
@@ -426,6 +428,11 @@ static int debug_launch(mrts_env* e, int game, int op, const int32_t* rows7, int
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize((cudaStream_t)stream));
     if (op == 1 && gameover) CK(cudaMemcpy(gameover, e->d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    return MRTS_OK;
+}
+int mrts_debug_timing(mrts_env* e, long long* device_buf) {
+    if (!e) return fail(MRTS_EINVAL, "null env");
+    e->d_timing = device_buf;
     return MRTS_OK;
 }
 int mrts_debug_issue(mrts_env* e, int game, const int32_t* rows7, int n, void* stream) { return debug_launch(e, game, 0, rows7, n, nullptr, stream); }

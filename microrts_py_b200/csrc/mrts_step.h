@@ -38,6 +38,7 @@ struct EnvParams {
     int32_t* next_actions;          // (N, HW, 7) or null: masked-uniform sample for the resulting state
     uint64_t seed;                  // sampler key
     uint32_t counter;               // launch counter (sampler stream position)
+    long long* timing;              // profiling aid, normally null: per game {rules cycles, total cycles}
 };
 
 MRTS_HD int align16(int v) { return (v + 15) & ~15; }
@@ -121,6 +122,13 @@ struct alignas(16) Q16 {
     uint32_t a, b, c, d;
 };
 
+MRTS_HD long long cycles_now() {
+#if defined(__CUDA_ARCH__)
+    return clock64();
+#else
+    return 0;
+#endif
+}
 MRTS_HD void group_add(int* p, int v) {
 #if defined(__CUDA_ARCH__)
     atomicAdd(p, v);
@@ -142,6 +150,7 @@ MRTS_HD void defer_game(const EnvParams& P, int g) {
 // SYNC: functor executing a barrier over the game's thread group.
 template <int ELEM, int PLANES, class SYNC>
 MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync) {
+    const long long t_start = P.timing ? cycles_now() : 0;
     const Layout L = layout_of(P);
     Sim s;
     bind_sim(s, P, L, mem, g);
@@ -216,6 +225,8 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         }
     }
     scatter_grid();
+    sync();
+    if (P.mode == MODE_STEP && s.ai == AI_WORKER_RUSH && !P.partial) s.flood_base_rows(-1, tid, nth);
     // the agents' action rows of the units that may act, fetched by the whole group (the leader never waits on HBM)
     if (P.mode == MODE_STEP) s.prefetch_actions(P.actions + (size_t)env0 * P.HW * 7, tid, nth);
     sync();
@@ -223,7 +234,9 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     // ---------------- rules (leader)
     if (tid == 0) {
         if (P.mode == MODE_STEP) {
+            const long long t_rules = P.timing ? cycles_now() : 0;
             s.st->reset = s.step_game() ? 1 : 0;
+            if (P.timing) P.timing[2 * g] = cycles_now() - t_rules;
         } else if (P.partial) {
             for (int v = 0; v < nviews; v++) o_make_view(s.self, v);
         }
@@ -291,6 +304,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         copy16<Q16>(gblob, mem + L.blob, 32 + n * 32, tid, nth);
         if (P.has_bot && naa > 0) copy16<Q16>(gblob + 32 + P.cap * 32, s.aa, align16(naa * 12), tid, nth);
     }
+    if (P.timing && tid == 0) P.timing[2 * g + 1] = cycles_now() - t_start;
 }
 
 }  // namespace mrts

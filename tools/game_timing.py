@@ -1,0 +1,43 @@
+#!/usr/bin/env python
+"""Per-game cycle histogram of one launch (profiling aid, mrts_debug_timing): shows whether a launch
+is bounded by the sum of the games' work or by its slowest games.
+    python tools/game_timing.py [workload] [prewarm]"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
+import bench  # noqa: E402
+from microrts_py_b200 import _capi, microrts_ai  # noqa: E402
+from microrts_py_b200.envs import MicroRTSGridModeVecEnv  # noqa: E402
+
+name = sys.argv[1] if len(sys.argv) > 1 else "diag_wrush16"
+prewarm = int(sys.argv[2]) if len(sys.argv) > 2 else 300
+wl = bench.workload_setup(name, 0)
+env = MicroRTSGridModeVecEnv(wl["nsp"], wl["nbot"], partial_obs=wl["partial"], max_steps=wl["max_steps"], ai2s=[getattr(microrts_ai, b) for b in wl["bot_names"]],
+                             map_paths=[wl["map"]], device=0, return_torch=True, seed=1000)
+L = env._lib
+G = L.mrts_num_games(env._h)
+obs = env.reset()
+for _ in range(prewarm):
+    m = env.get_action_mask()
+    obs, r, d, _ = env.step(env.sample_actions())
+tim = torch.zeros((G, 2), dtype=torch.int64, device=env.device)
+_capi.check(L.mrts_debug_timing(env._h, C.c_void_p(tim.data_ptr())))
+hist = []
+for k in range(8):
+    m = env.get_action_mask()
+    obs, r, d, _ = env.step(env.sample_actions())
+    torch.cuda.synchronize()
+    hist.append(tim.cpu().numpy().copy())
+_capi.check(L.mrts_debug_timing(env._h, None))
+t = np.stack(hist).astype(np.float64)  # (8, G, 2)
+for lbl, x in (("rules", t[:, :, 0]), ("total", t[:, :, 1])):
+    q = np.percentile(x, [50, 90, 99, 99.9, 100])
+    print(f"{name} {lbl:5s} cycles/game: mean {x.mean():9.0f}  p50 {q[0]:9.0f}  p90 {q[1]:9.0f}  p99 {q[2]:9.0f}  p99.9 {q[3]:9.0f}  max {q[4]:9.0f}")
+state = [env.export_state(g)[1] for g in range(0, G, max(1, G // 256))]
+print("units/game mean", np.mean([len(s) for s in state]), "max", max(len(s) for s in state))
+env.close()
