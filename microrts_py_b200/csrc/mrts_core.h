@@ -40,6 +40,8 @@ struct Mask78 {
 };
 #if defined(MRTS_STATS) && !defined(__CUDA_ARCH__)
 #include <cstdio>
+#include <cstdlib>
+#include <vector>
 struct MrtsStats { long searches = 0, pre_fail = 0, guard = 0, guard_fail = 0, expanded = 0; ~MrtsStats() { fprintf(stderr, "[mrts stats] searches %ld precheck-fail %ld guard %ld guard-fail %ld expansions %ld\n", searches, pre_fail, guard, guard_fail, expanded); } };
 inline MrtsStats& mrts_stats() { static MrtsStats s; return s; }
 #define MRTS_STAT(x) (mrts_stats().x)
@@ -63,8 +65,19 @@ MRTS_HD bool mget(const Mask78& m, int b) {
 }
 
 // cost/parent/next per cell + one stack head per f value + stamps, then 3 row bitmaps (uint64 per map row) of the reachability guard
-MRTS_HD int astar_core_bytes(int W, int HW) { return ((3 * HW + (HW + W + (HW / W) + 2)) * 2 + HW * 2 + 15) & ~15; }
-MRTS_HD int astar_bytes(int W, int HW) { return astar_core_bytes(W, HW) + 3 * (HW / W) * 8; }
+MRTS_HD int ceil_log2(int v) {
+    int s = 0;
+    while ((1 << s) < v) s++;
+    return s;
+}
+// Maps up to 64 wide: cells are addressed as (y << ceil_log2(W)) | x (no division in the search) and
+// the enterable / visited / flood sets are one uint64 per map row.  Wider maps keep linear
+// positions and a per-cell stamp array.
+MRTS_HD int astar_cells(int W, int HW) { return W <= 64 ? ((HW / W) << ceil_log2(W)) : HW; }
+MRTS_HD int astar_core_bytes(int W, int HW) {
+    return ((3 * astar_cells(W, HW) + (HW + W + (HW / W) + 2)) * 2 + (W <= 64 ? 0 : HW * 2) + 15) & ~15;
+}
+MRTS_HD int astar_bytes(int W, int HW) { return astar_core_bytes(W, HW) + (W <= 64 ? 4 * (HW / W) * 8 : 0); }
 
 // Per-step scalars the rules mutate; they live in the game's shared-memory region so that the
 // immutable view below (Sim) can be copied freely into the registers of out-of-line functions.
@@ -73,7 +86,10 @@ struct St {
     int astar_gen;   // search counter (stamp generation)
     int gameover, winner;
     int reset;
+    int rows_ready;  // the enterable-cell rows of this bot call are built (see astar_rows)
     int nprod;       // pending PRODUCE assignments at load (capacity check)
+    int timing_on;   // profiling aid (mrts_debug_timing): fill tp[]
+    int tp[8];       // cycles: decode, bot census/puts, bot translate, issue agent, issue bot, cycle; then #searches, #expansions
     int rew[2][6];   // integer reward terms per player view (exact small integers)
 };
 
@@ -111,6 +127,13 @@ struct Sim {
 
     // ------------------------------------------------------------------ small helpers
     MRTS_HD int nunits() const { return hdr->nunits; }
+    MRTS_HD int tick() const {
+#if defined(__CUDA_ARCH__)
+        return st->timing_on ? (int)clock64() : 0;
+#else
+        return 0;
+#endif
+    }
     MRTS_HD bool alive(int i) const { return !(u[i].flags & UF_DEAD); }
     // membership of unit i in the state the caller looks at: vp < 0 = the true state,
     // vp = p = player p's partially observable view taken this step
@@ -821,21 +844,27 @@ struct Sim {
     MRTS_HD int astar_nf() const { return HW + W + H + 2; }
     MRTS_HD AStarBuf astar_buf() const {
         AStarBuf b;
+        const int nc = astar_cells(W, HW);
         b.cost = astar;
-        b.parent = b.cost + HW;
-        b.next = b.parent + HW;
-        b.head = b.next + HW;
+        b.parent = b.cost + nc;
+        b.next = b.parent + nc;
+        b.head = b.next + nc;
         b.stamp = (uint16_t*)(b.head + astar_nf());
         return b;
     }
-    // ---- reachability guard of the search (see astar_first_move): row bitmaps, bit x of row y
-    MRTS_HD uint64_t* flood_rows() const { return (uint64_t*)((uint8_t*)astar + astar_core_bytes(W, HW)); }
-    // cells no search can enter because of the map or a unit (of the true state): built once per pass
-    // by the whole group; under partial observability the bot's view hides units, the leader
-    // rebuilds the rows for its view when it needs them
+    // ---- row bitmaps of the search on maps up to 64 wide (bit x of row y): F0 = cells free of walls and
+    // of the units the bot sees (constant during a step), F = cells a search may enter during this
+    // bot call (F0 minus pending MOVE/PRODUCE targets, bitsB, minus the desires accepted so far,
+    // bitsC), V = cells pushed by the current search, R = flood-fill scratch
+    MRTS_HD uint64_t* rows_F0() const { return (uint64_t*)((uint8_t*)astar + astar_core_bytes(W, HW)); }
+    MRTS_HD uint64_t* rows_F() const { return rows_F0() + H; }
+    MRTS_HD uint64_t* rows_V() const { return rows_F0() + 2 * H; }
+    MRTS_HD uint64_t* rows_R() const { return rows_F0() + 3 * H; }
+    // built once per pass by the whole group; under partial observability the bot's view hides
+    // units, so the leader rebuilds the rows for its view when a search needs them
     MRTS_HD void flood_base_rows(int vp, int tid, int nth) const {
         if (W > 64) return;
-        uint64_t* F0 = flood_rows();
+        uint64_t* F0 = rows_F0();
 #pragma unroll 1
         for (int y = tid; y < H; y += nth) {
             uint64_t row = 0;
@@ -862,6 +891,21 @@ struct Sim {
         }
         return row;
     }
+    // F for this bot call, on the first search (translate_actions keeps it current afterwards)
+    MRTS_HD void rows_prepare(int vp) const {
+        if (st->rows_ready) return;
+        if (partial) flood_base_rows(vp, 0, 1);
+        const uint64_t* F0 = rows_F0();
+        uint64_t* F = rows_F();
+#pragma unroll 1
+        for (int y = 0; y < H; y++) F[y] = F0[y] & ~bits_row(bitsB, y) & ~bits_row(bitsC, y);
+        st->rows_ready = 1;
+    }
+    // a desire was accepted (its target is now in bitsC): later searches of this call may not enter it
+    MRTS_HD void rows_reserve(int pos) const {
+        if (W > 64 || !st->rows_ready || pos < 0 || pos >= HW) return;
+        rows_F()[pos / W] &= ~(1ull << (pos % W));
+    }
     static MRTS_HD uint64_t brev64(uint64_t v) {
 #if defined(__CUDA_ARCH__)
         return __brevll(v);
@@ -878,20 +922,13 @@ struct Sim {
         const uint64_t dn = (((Fr + Sr) ^ Fr) & Fr) | Sr;
         return up | brev64(dn);
     }
-    // Can a search from (sx,sy) ever pop a cell within `range` of (tx,ty)?  Flood fill of the
-    // enterable cells (exactly the cells astar_first_move would accept as neighbours) from the start.
-    // Only used to cut a search short that is bound to fail, so the result of the search is unchanged.
-    MRTS_HD bool flood_reaches(int sx, int sy, int tx, int ty, int range, int vp, bool rebuild_base) const {
-        if (W > 64) return true;  // no guard for wider maps
-        uint64_t* F0 = flood_rows();
-        uint64_t* F = F0 + H;
-        uint64_t* R = F + H;
-        if (rebuild_base) flood_base_rows(vp, 0, 1);
+    // Can a search from (sx,sy) ever pop a cell within `range` of (tx,ty)?  Flood fill of F from the
+    // start.  Only used to cut a search short that is bound to fail: the search result is unchanged.
+    MRTS_HD bool flood_reaches(int sx, int sy, int tx, int ty, int range) const {
+        const uint64_t* F = rows_F();
+        uint64_t* R = rows_R();
 #pragma unroll 1
-        for (int y = 0; y < H; y++) {
-            F[y] = F0[y] & ~bits_row(bitsB, y) & ~bits_row(bitsC, y);
-            R[y] = 0;
-        }
+        for (int y = 0; y < H; y++) R[y] = 0;
         // the start cell itself is occupied: seed its enterable neighbours
         if (sy > 0) R[sy - 1] = (1ull << sx) & F[sy - 1];
         if (sy + 1 < H) R[sy + 1] = (1ull << sx) & F[sy + 1];
@@ -917,6 +954,9 @@ struct Sim {
                 }
             }
         }
+        return rows_any_in_range(R, tx, ty, range);
+    }
+    MRTS_HD bool rows_any_in_range(const uint64_t* rows, int tx, int ty, int range) const {
         const int sq = range * range;
 #pragma unroll 1
         for (int dy = -range; dy <= range; dy++) {
@@ -926,10 +966,109 @@ struct Sim {
             for (int dx = -range; dx <= range; dx++) {
                 const int x = tx + dx;
                 if (x < 0 || x >= W || dx * dx + dy * dy > sq) continue;
-                if ((R[y] >> x) & 1ull) return true;
+                if ((rows[y] >> x) & 1ull) return true;
             }
         }
         return false;
+    }
+
+    // findPathToPositionInRange on a map up to 64 wide.  Same open-list order as astar_first_move
+    // (the generic form below, which documents it), with cells addressed as (y << ws) | x and the
+    // neighbour tests "enterable and not yet pushed" done on the row bitmaps.
+    MRTS_HD int astar_rows(int i, int targetpos, int range, int vp) {
+        const AStarBuf b = astar_buf();
+        const Unit& su = u[i];
+        const int ws = ceil_log2(W), WP = 1 << ws;
+        const int tx = targetpos % W, ty = targetpos / W;
+        const int sq = range * range;
+        const int sx = su.x, sy = su.y;
+        rows_prepare(vp);
+        const uint64_t* F = rows_F();
+        uint64_t* V = rows_V();
+        // A search only ever pops its start or cells it accepted as enterable neighbours.  If the
+        // start is out of range and no enterable cell is in range the reference's search exhausts
+        // the reachable map and returns null -- the usual case of a worker queueing behind others
+        // around an enclosed target, retried on every frame: same answer here without the search.
+        if ((sx - tx) * (sx - tx) + (sy - ty) * (sy - ty) > sq && !rows_any_in_range(F, tx, ty, range)) {
+            MRTS_STAT(pre_fail++);
+            return -1;
+        }
+        MRTS_STAT(searches++);
+        st->tp[6]++;
+#pragma unroll 1
+        for (int y = 0; y < H; y++) V[y] = 0;
+        const int startPk = (sy << ws) | sx;
+        const int h0 = iabs(sx - tx) + iabs(sy - ty);
+        V[sy] = 1ull << sx;
+        b.parent[startPk] = (int16_t)startPk;
+        b.cost[startPk] = 0;
+        b.next[startPk] = -1;
+        b.head[h0] = (int16_t)startPk;
+        int fmin = h0, fmax = h0, flo = h0, nopen = 1, expanded = 0;
+        bool found = false;
+        int pk = startPk;
+#pragma unroll 1
+        while (nopen > 0) {
+            while (b.head[fmin] < 0) fmin++;
+            pk = b.head[fmin];
+            b.head[fmin] = b.next[pk];
+            nopen--;
+            const int x = pk & (WP - 1), y = pk >> ws;
+            if ((x - tx) * (x - tx) + (y - ty) * (y - ty) <= sq) {
+                found = true;
+                break;
+            }
+            MRTS_STAT(expanded++);
+            st->tp[7]++;
+            // a search that keeps growing is checked once against a flood fill: unreachable -> null right away
+            if (++expanded == ASTAR_GUARD_AFTER) {
+                MRTS_STAT(guard++);
+                if (!flood_reaches(sx, sy, tx, ty, range)) {
+                    MRTS_STAT(guard_fail++);
+                    break;
+                }
+            }
+            const int g1 = b.cost[pk] + 1;
+            const uint64_t bx = 1ull << x;
+            // enterable and not yet pushed, in the reference's neighbour order: up, right, down, left (:236-262)
+            const uint64_t mid = F[y] & ~V[y];
+            const bool ok_up = y > 0 && ((F[y - 1] & ~V[y - 1]) & bx);
+            const bool ok_right = x + 1 < W && (mid & (bx << 1));
+            const bool ok_down = y + 1 < H && ((F[y + 1] & ~V[y + 1]) & bx);
+            const bool ok_left = x > 0 && (mid & (bx >> 1));
+#pragma unroll
+            for (int d = 0; d < 4; d++) {
+                const bool ok = d == D_UP ? ok_up : (d == D_RIGHT ? ok_right : (d == D_DOWN ? ok_down : ok_left));
+                if (!ok) continue;
+                const int nx = x + dir_dx(d), ny = y + dir_dy(d);
+                const int np = (ny << ws) | nx;
+                const int f = iabs(nx - tx) + iabs(ny - ty) + g1;
+                b.cost[np] = (int16_t)g1;
+                b.parent[np] = (int16_t)pk;
+                V[ny] |= 1ull << nx;
+                b.next[np] = b.head[f];
+                b.head[f] = (int16_t)np;
+                if (f < fmin) fmin = f;
+                if (f < flo) flo = f;
+                if (f > fmax) fmax = f;
+                nopen++;
+            }
+        }
+#pragma unroll 1
+        for (int f = flo; f <= fmax; f++) b.head[f] = -1;  // leave the stacks empty for the next search
+        if (!found) return -1;
+        int last = pk, parent = b.parent[pk];
+#pragma unroll 1
+        while (parent != pk) {
+            last = pk;
+            pk = parent;
+            parent = b.parent[pk];
+        }
+        if (last == pk + WP) return D_DOWN;
+        if (last == pk - 1) return D_LEFT;
+        if (last == pk - WP) return D_UP;
+        if (last == pk + 1) return D_RIGHT;
+        return -1;
     }
 
     // once per game pass, by the whole thread group, before the leader runs (the region is scratch)
@@ -937,12 +1076,58 @@ struct Sim {
         AStarBuf b = astar_buf();
 #pragma unroll 1
         for (int k = tid; k < astar_nf(); k += nth) b.head[k] = -1;
+        if (W > 64) {
 #pragma unroll 1
-        for (int k = tid; k < HW; k += nth) b.stamp[k] = 0;
+            for (int k = tid; k < HW; k += nth) b.stamp[k] = 0;
+        }
         st->astar_gen = 0;
     }
     // findPathToPositionInRange: direction of the first move, or -1 (null)
+#if defined(MRTS_STATS) && !defined(__CUDA_ARCH__)
+    int astar_check(int i, int targetpos, int range, int vp) {  // host-only cross-check: the generic search on private arrays
+        std::vector<int> cost(HW), parent(HW), next(HW), head(HW + W + H + 2, -1), seen(HW, 0);
+        const Unit& su = u[i];
+        const int tx = targetpos % W, ty = targetpos / W, sq = range * range;
+        const int startPos = su.y * W + su.x, h0 = iabs(su.x - tx) + iabs(su.y - ty);
+        parent[startPos] = startPos; cost[startPos] = 0; seen[startPos] = 1; next[startPos] = -1; head[h0] = startPos;
+        int fmin = h0, nopen = 1, pos = startPos;
+        bool found = false;
+        while (nopen > 0) {
+            while (head[fmin] < 0) fmin++;
+            pos = head[fmin]; head[fmin] = next[pos]; nopen--;
+            const int x = pos % W, y = pos / W;
+            if ((x - tx) * (x - tx) + (y - ty) * (y - ty) <= sq) { found = true; break; }
+            for (int d = 0; d < 4; d++) {
+                const int nx = x + dir_dx(d), ny = y + dir_dy(d);
+                if (nx < 0 || ny < 0 || nx >= W || ny >= H) continue;
+                const int np = nx + ny * W;
+                if (seen[np] || !free_cell(nx, ny, vp) || bit_get(bitsC, np)) continue;
+                const int f = iabs(nx - tx) + iabs(ny - ty) + cost[pos] + 1;
+                cost[np] = cost[pos] + 1; parent[np] = pos; seen[np] = 1; next[np] = head[f]; head[f] = np;
+                if (f < fmin) fmin = f;
+                nopen++;
+            }
+        }
+        if (!found) return -1;
+        int last = pos, par = parent[pos];
+        while (par != pos) { last = pos; pos = par; par = parent[pos]; }
+        if (last == pos + W) return D_DOWN;
+        if (last == pos - 1) return D_LEFT;
+        if (last == pos - W) return D_UP;
+        if (last == pos + 1) return D_RIGHT;
+        return -1;
+    }
+#endif
     MRTS_HD int astar_first_move(int i, int targetpos, int range, int vp) {
+#if defined(MRTS_STATS) && !defined(__CUDA_ARCH__)
+        if (W <= 64) {
+            const int want = astar_check(i, targetpos, range, vp);
+            const int got = astar_rows(i, targetpos, range, vp);
+            if (want != got) fprintf(stderr, "[astar mismatch] t=%d unit (%d,%d) target (%d,%d) range %d: rows %d generic %d\n", hdr->time, u[i].x, u[i].y, targetpos % W, targetpos / W, range, got, want);
+            return got;
+        }
+#endif
+        if (W <= 64) return astar_rows(i, targetpos, range, vp);
         const AStarBuf b = astar_buf();
         const Unit& su = u[i];
         const uint16_t gen = (uint16_t)++st->astar_gen;
@@ -971,7 +1156,7 @@ struct Sim {
             }
         }
         MRTS_STAT(searches++);
-        int expanded = 0;
+        st->tp[6]++;
         b.parent[startPos] = (int16_t)startPos;
         b.cost[startPos] = 0;
         b.stamp[startPos] = gen;
@@ -991,15 +1176,8 @@ struct Sim {
                 found = true;
                 break;
             }
-            // a search that keeps growing is checked once against a flood fill: unreachable -> null right away
             MRTS_STAT(expanded++);
-            if (++expanded == ASTAR_GUARD_AFTER) {
-                MRTS_STAT(guard++);
-                if (!flood_reaches(su.x, su.y, tx, ty, range, vp, partial != 0)) {
-                    MRTS_STAT(guard_fail++);
-                    break;
-                }
-            }
+            st->tp[7]++;
             const int g1 = b.cost[pos] + 1;
             // neighbours in the reference's order: up, right, down, left (:236-262)
 #pragma unroll
@@ -1179,6 +1357,7 @@ struct Sim {
         int costB[2];
         pending_usage(bitsB, costB, vp);
         bits_clear(bitsC);
+        st->rows_ready = 0;
         st->npa2 = 0;
         int na = hdr->n_aa, keep = 0;
 #pragma unroll 1
@@ -1195,7 +1374,10 @@ struct Sim {
                 if (aa_execute(r, i, vp, costB, out)) {
                     pa2[st->npa2++] = out;
                     int pos = usage_pos(u[i], out.type, out.param);
-                    if (pos != -0x7fff) bit_set(bitsC, pos);
+                    if (pos != -0x7fff) {
+                        bit_set(bitsC, pos);
+                        rows_reserve(pos);
+                    }
                 }
             }
             if (!del) aa[keep++] = r;  // r may carry Train's completed flag
@@ -1329,6 +1511,7 @@ struct Sim {
     // such workers are skipped and translate_actions keeps their entry -- provided an enemy is in
     // view at all (otherwise the reference puts nothing and the stale entry is checked as usual).
     MRTS_HD void worker_rush(int player, int vp) {
+        const int t_wr = tick();
         const int n = nunits();
         const int pres = hdr->res[player];
         // one pass: census (:124-137) + is any enemy in view
@@ -1399,7 +1582,10 @@ struct Sim {
             }
             if (hfree) o_bot_melee(self, harvester, player, vp);
         }
+        st->tp[1] = tick() - t_wr;
+        const int t_tr = tick();
         translate_actions(player, vp, enemy_seen);
+        st->tp[2] = tick() - t_tr;
     }
 
     // the scripted opponent's PlayerAction for `player` -> pa2
@@ -1437,13 +1623,22 @@ struct Sim {
                 v0 = 0;
                 v1 = 1;
             }
+            int t0 = tick();
             o_decode_actions(self, 0, v0);
+            int t1 = tick();
+            st->tp[0] = t1 - t0;
             bot_action(1, v1);
+            t0 = tick();
             o_issue_safe(self, pa, st->npa);
+            t1 = tick();
+            st->tp[3] = t1 - t0;
             o_issue_safe(self, pa2, st->npa2);
+            st->tp[4] = tick() - t1;
         }
+        const int tc = tick();
         cycle();
         eval_gameover();
+        st->tp[5] = tick() - tc;
         if (st->gameover) {  // WinLossRewardFunction.java:16-24
             st->rew[0][0] = st->winner == 0 ? 1 : -1;
             st->rew[1][0] = st->winner == 1 ? 1 : -1;

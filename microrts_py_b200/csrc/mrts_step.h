@@ -38,7 +38,7 @@ struct EnvParams {
     int32_t* next_actions;          // (N, HW, 7) or null: masked-uniform sample for the resulting state
     uint64_t seed;                  // sampler key
     uint32_t counter;               // launch counter (sampler stream position)
-    long long* timing;              // profiling aid, normally null: per game {rules cycles, total cycles}
+    long long* timing;              // profiling aid, normally null: per game 10 values {rules cycles, total cycles, St::tp[0..7]}
 };
 
 MRTS_HD int align16(int v) { return (v + 15) & ~15; }
@@ -204,8 +204,10 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (tid == 0) {
         *(Sim*)(mem + L.sim) = s;
         St z;
-        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = 0;
+        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.rows_ready = 0;
         z.winner = -1;
+        z.timing_on = P.timing != nullptr;
+        for (int k = 0; k < 8; k++) z.tp[k] = 0;
         for (int p = 0; p < 2; p++)
             for (int k = 0; k < 6; k++) z.rew[p][k] = 0;
         *s.st = z;
@@ -236,7 +238,10 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         if (P.mode == MODE_STEP) {
             const long long t_rules = P.timing ? cycles_now() : 0;
             s.st->reset = s.step_game() ? 1 : 0;
-            if (P.timing) P.timing[2 * g] = cycles_now() - t_rules;
+            if (P.timing) {
+                P.timing[10 * g] = cycles_now() - t_rules;
+                for (int k = 0; k < 8; k++) P.timing[10 * g + 2 + k] = s.st->tp[k];
+            }
         } else if (P.partial) {
             for (int v = 0; v < nviews; v++) o_make_view(s.self, v);
         }
@@ -304,7 +309,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         copy16<Q16>(gblob, mem + L.blob, 32 + n * 32, tid, nth);
         if (P.has_bot && naa > 0) copy16<Q16>(gblob + 32 + P.cap * 32, s.aa, align16(naa * 12), tid, nth);
     }
-    if (P.timing && tid == 0) P.timing[2 * g + 1] = cycles_now() - t_start;
+    if (P.timing && tid == 0) P.timing[10 * g + 1] = cycles_now() - t_start;
 }
 
 }  // namespace mrts

@@ -25,7 +25,7 @@ obs = env.reset()
 for _ in range(prewarm):
     m = env.get_action_mask()
     obs, r, d, _ = env.step(env.sample_actions())
-tim = torch.zeros((G, 2), dtype=torch.int64, device=env.device)
+tim = torch.zeros((G, 10), dtype=torch.int64, device=env.device)
 _capi.check(L.mrts_debug_timing(env._h, C.c_void_p(tim.data_ptr())))
 hist = []
 for k in range(8):
@@ -35,9 +35,10 @@ for k in range(8):
     hist.append(tim.cpu().numpy().copy())
 _capi.check(L.mrts_debug_timing(env._h, None))
 t = np.stack(hist).astype(np.float64)  # (8, G, 2)
-for lbl, x in (("rules", t[:, :, 0]), ("total", t[:, :, 1])):
+names = ["rules", "total", "decode", "bot-puts", "bot-translate", "issue-agent", "issue-bot", "cycle", "#searches", "#expansions"]
+for lbl, x in [(names[k], t[:, :, k]) for k in range(10)]:
     q = np.percentile(x, [50, 90, 99, 99.9, 100])
-    print(f"{name} {lbl:5s} cycles/game: mean {x.mean():9.0f}  p50 {q[0]:9.0f}  p90 {q[1]:9.0f}  p99 {q[2]:9.0f}  p99.9 {q[3]:9.0f}  max {q[4]:9.0f}")
+    print(f"{name} {lbl:14s} /game: mean {x.mean():9.0f}  p50 {q[0]:9.0f}  p90 {q[1]:9.0f}  p99 {q[2]:9.0f}  p99.9 {q[3]:9.0f}  max {q[4]:9.0f}")
 state = [env.export_state(g)[1] for g in range(0, G, max(1, G // 256))]
 print("units/game mean", np.mean([len(s) for s in state]), "max", max(len(s) for s in state))
 env.close()
