@@ -87,6 +87,7 @@ struct St {
     int gameover, winner;
     int reset;
     int rows_ready;  // the enterable-cell rows of this bot call are built (see astar_rows)
+    int nidle;       // idle mobile units of the scripted bot after this step (launch-order hint)
     int nprod;       // pending PRODUCE assignments at load (capacity check)
     int timing_on;   // profiling aid (mrts_debug_timing): fill tp[]
     int tp[8];       // cycles: decode, bot census/puts, bot translate, issue agent, issue bot, cycle; then #searches, #expansions

@@ -53,13 +53,35 @@ constexpr int GPB_MAX = 4;  // games per block is chosen per environment (mrts_e
 #ifndef MRTS_WARP_MIN_BLOCKS
 #define MRTS_WARP_MIN_BLOCKS 5
 #endif
-template <int ELEM, int PLANES>
-__global__ void __launch_bounds__(32 * GPB_MAX, MRTS_WARP_MIN_BLOCKS) mrts_pass_warp_kernel(const EnvParams P, const int smem_per_game) {
+// MINB = resident 128-thread blocks per SM the register budget must allow: 5 (96 registers) is
+// the best trade for 16x16 and larger maps; 8x8 maps (small state, many games per SM) run faster
+// with 8 (64 registers, 32+ games per SM).
+template <int ELEM, int PLANES, int MINB>
+__global__ void __launch_bounds__(32 * GPB_MAX, MINB) mrts_pass_warp_kernel(const EnvParams P, const int smem_per_game) {
     extern __shared__ uint4 smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int g = blockIdx.x * (blockDim.x >> 5) + warp;
-    if (g >= P.n_games) return;
+    const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
+    if (slot >= P.n_games) return;
+    int g = slot;
+    if (P.order) {  // longest games first: blocks are dispatched in index order
+        int k = slot, c = 0;
+        while (c < 3 && k >= P.order_n[c]) k -= P.order_n[c++];
+        g = P.order[c * P.n_games + k];
+    }
     game_pass<ELEM, PLANES>(P, g, (uint8_t*)smem_raw + (size_t)warp * smem_per_game, lane, 32, WarpSync());
+}
+
+// Launch order of a slab with scripted-bot games.  A bot game's step time has a heavy tail: one path
+// search per idle bot unit, several in one frame every ~10 frames.  The number of idle bot units is
+// known from the previous pass, so games are binned by it and launched slowest class first;
+// otherwise the launch ends with a few long games running alone.
+constexpr uint32_t ORDER_T0 = 4, ORDER_T1 = 2, ORDER_T2 = 0;  // idle bot units: >= 5, 3-4, 1-2, none
+__global__ void mrts_order_kernel(const uint32_t* cost, int n, int32_t* order, int32_t* order_n) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const uint32_t c = cost[g];
+    const int cls = c > ORDER_T0 ? 0 : (c > ORDER_T1 ? 1 : (c > ORDER_T2 ? 2 : 3));
+    order[cls * n + atomicAdd(&order_n[cls], 1)] = g;
 }
 
 // Games the warp kernel deferred because their unit table may outgrow the staged capacity
@@ -143,10 +165,13 @@ struct mrts_env {
     int device = 0;
     int threads = 64;
     int gpb = 1;  // warp kernel: games (warps) per block
+    int minb = MRTS_WARP_MIN_BLOCKS;  // warp kernel: register budget variant
     int smem = 0;       // bytes per game at the staged capacity (P.scap)
     int smem_full = 0;  // bytes per game at the full capacity (overflow / debug launches)
     int32_t* d_ovf = nullptr;
     long long* d_timing = nullptr;  // profiling aid (mrts_debug_timing)
+    uint32_t* d_cost = nullptr;     // bot slabs: last step cycles per game
+    int32_t* d_order = nullptr;     // 4 * n_games launch order + 4 class counts
     int N = 0;
     std::vector<void*> allocs;
     int* d_flag = nullptr;
@@ -195,6 +220,17 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     EnvParams F = P;  // full-capacity parameters of the overflow launch
     F.scap = P.cap;
     F.ovf = nullptr;
+    P.cost = e->d_cost;
+    P.order = nullptr;
+    P.order_n = nullptr;
+    if (e->d_order && e->threads == 32 && mode == MODE_STEP) {
+        int32_t* cnt = e->d_order + 4 * (size_t)P.n_games;
+        CK(cudaMemsetAsync(cnt, 0, 4 * sizeof(int32_t), st));
+        mrts_order_kernel<<<(P.n_games + 255) / 256, 256, 0, st>>>(e->d_cost, P.n_games, e->d_order, cnt);
+        P.order = e->d_order;
+        P.order_n = cnt;
+    }
+    F.cost = P.cost;
     if (defer) {
         P.ovf = e->d_ovf;
         CK(cudaMemsetAsync(e->d_ovf, 0, sizeof(int32_t), st));
@@ -204,7 +240,8 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     const int ogrid = P.n_games < 296 ? P.n_games : 296;
 #define MRTS_LAUNCH(E, PL)                                                                       \
     do {                                                                                         \
-        if (e->threads == 32) mrts_pass_warp_kernel<E, PL><<<wgrid, 32 * GPB, GPB * e->smem, st>>>(P, e->smem); \
+        if (e->threads == 32 && e->minb == 8) mrts_pass_warp_kernel<E, PL, 8><<<wgrid, 32 * GPB, GPB * e->smem, st>>>(P, e->smem); \
+        else if (e->threads == 32) mrts_pass_warp_kernel<E, PL, MRTS_WARP_MIN_BLOCKS><<<wgrid, 32 * GPB, GPB * e->smem, st>>>(P, e->smem); \
         else mrts_pass_kernel<E, PL><<<bgrid, e->threads, e->smem, st>>>(P);                     \
         if (defer) mrts_overflow_kernel<E, PL><<<ogrid, 128, e->smem_full, st>>>(F, e->d_ovf);   \
     } while (0)
@@ -287,6 +324,18 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         if (want < P.cap) P.scap = want;
     }
     e->smem = layout_of(P).total;
+    if (P.has_bot && e->threads == 32 && P.n_games >= 2048) {
+        void *c = nullptr, *o = nullptr;
+        if (cudaMalloc(&c, sizeof(uint32_t) * (size_t)P.n_games) == cudaSuccess && cudaMalloc(&o, sizeof(int32_t) * (4 * (size_t)P.n_games + 4)) == cudaSuccess) {
+            e->allocs.push_back(c);
+            e->allocs.push_back(o);
+            cudaMemset(c, 0, sizeof(uint32_t) * (size_t)P.n_games);
+            e->d_cost = (uint32_t*)c;
+            e->d_order = (int32_t*)o;
+        } else if (c) {
+            cudaFree(c);
+        }
+    }
     if (P.scap < P.cap) {
         void* o = nullptr;
         ce = cudaMalloc(&o, sizeof(int32_t) * (size_t)(P.n_games + 1));
@@ -319,13 +368,18 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
             if (w > best_w) best_w = w, best = g;
         }
         e->gpb = cfg->threads_per_game < 0 ? -cfg->threads_per_game : best;
+        e->minb = HW <= 64 ? 8 : MRTS_WARP_MIN_BLOCKS;
         if (e->gpb > GPB_MAX) e->gpb = GPB_MAX;
         const int wbytes = e->gpb * e->smem;
         if (wbytes > 48 * 1024) {
-            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
-            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
-            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 29>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
-            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 31>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 29, MRTS_WARP_MIN_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 31, MRTS_WARP_MIN_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 29, MRTS_WARP_MIN_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 31, MRTS_WARP_MIN_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 29, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<4, 31, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 29, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
+            cudaFuncSetAttribute(mrts_pass_warp_kernel<1, 31, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, wbytes);
         }
     }
     if (e->smem_full > 48 * 1024) {

@@ -17,6 +17,9 @@ struct EnvParams {
     int32_t n_games;                // num_selfplay / 2 + num_bot
     int32_t W, H, HW, cap, planes;  // cap = unit capacity of a game blob in HBM
     int32_t scap;                   // unit capacity staged in shared memory by this launch (<= cap); games that may exceed it go to `ovf`
+    uint32_t* cost;                 // per game: idle mobile bot units after its last pass = path searches due next step (launch order of bot slabs); null = not kept
+    const int32_t* order;           // launch slot -> game (4 classes of n_games entries each, see mrts_order_kernel) or null = identity
+    const int32_t* order_n;         // entries per class
     int32_t* ovf;                   // [0] = count, [1..] = game indices deferred to the full-capacity launch; null = no deferral
     int32_t partial, none_mode, max_steps;
     int32_t has_bot;                // any WorkerRush game: blob carries the abstract-action table
@@ -38,7 +41,7 @@ struct EnvParams {
     int32_t* next_actions;          // (N, HW, 7) or null: masked-uniform sample for the resulting state
     uint64_t seed;                  // sampler key
     uint32_t counter;               // launch counter (sampler stream position)
-    long long* timing;              // profiling aid, normally null: per game 10 values {rules cycles, total cycles, St::tp[0..7]}
+    long long* timing;              // profiling aid, normally null: per game 12 values {rules cycles, total cycles, St::tp[0..7], start ns, SM id}
 };
 
 MRTS_HD int align16(int v) { return (v + 15) & ~15; }
@@ -151,6 +154,16 @@ MRTS_HD void defer_game(const EnvParams& P, int g) {
 template <int ELEM, int PLANES, class SYNC>
 MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync) {
     const long long t_start = P.timing ? cycles_now() : 0;
+#if defined(__CUDA_ARCH__)
+    if (P.timing && tid == 0) {
+        unsigned long long ns;
+        unsigned sm;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns));
+        asm volatile("mov.u32 %0, %smid;" : "=r"(sm));
+        P.timing[12 * g + 10] = (long long)ns;
+        P.timing[12 * g + 11] = (long long)sm;
+    }
+#endif
     const Layout L = layout_of(P);
     Sim s;
     bind_sim(s, P, L, mem, g);
@@ -204,7 +217,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (tid == 0) {
         *(Sim*)(mem + L.sim) = s;
         St z;
-        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.rows_ready = 0;
+        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.rows_ready = z.nidle = 0;
         z.winner = -1;
         z.timing_on = P.timing != nullptr;
         for (int k = 0; k < 8; k++) z.tp[k] = 0;
@@ -239,8 +252,8 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
             const long long t_rules = P.timing ? cycles_now() : 0;
             s.st->reset = s.step_game() ? 1 : 0;
             if (P.timing) {
-                P.timing[10 * g] = cycles_now() - t_rules;
-                for (int k = 0; k < 8; k++) P.timing[10 * g + 2 + k] = s.st->tp[k];
+                P.timing[12 * g] = cycles_now() - t_rules;
+                for (int k = 0; k < 8; k++) P.timing[12 * g + 2 + k] = s.st->tp[k];
             }
         } else if (P.partial) {
             for (int v = 0; v < nviews; v++) o_make_view(s.self, v);
@@ -292,7 +305,14 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     // ---------------- mask: zero fill, then the 78 entries of every source unit
     if (P.mask)
         for (int v = 0; v < nviews; v++) zero_mask<ELEM>(P.HW, (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env, tid, nth);
+    if (P.cost && s.ai == AI_WORKER_RUSH) {
+        const int n = s.hdr->nunits;
+        int mine = 0;
+        for (int i = tid; i < n; i += nth) mine += s.u[i].player == 1 && s.u[i].a_type < 0 && ut_can_move(s.u[i].type);
+        if (mine) group_add(&s.st->nidle, mine);
+    }
     sync();  // zero-fill before patches (and umask complete)
+    if (P.cost && tid == 0) P.cost[g] = s.ai == AI_WORKER_RUSH ? (uint32_t)((volatile St*)s.st)->nidle : 0u;
     if (P.next_actions)
         for (int v = 0; v < nviews; v++)
             sample_actions(s, v, umask, P.next_actions + (size_t)(env0 + v) * P.HW * 7, P.seed, P.counter, (uint32_t)(env0 + v), tid, nth);
@@ -309,7 +329,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         copy16<Q16>(gblob, mem + L.blob, 32 + n * 32, tid, nth);
         if (P.has_bot && naa > 0) copy16<Q16>(gblob + 32 + P.cap * 32, s.aa, align16(naa * 12), tid, nth);
     }
-    if (P.timing && tid == 0) P.timing[10 * g + 1] = cycles_now() - t_start;
+    if (P.timing && tid == 0) P.timing[12 * g + 1] = cycles_now() - t_start;
 }
 
 }  // namespace mrts

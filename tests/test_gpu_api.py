@@ -171,3 +171,31 @@ def test_games_outgrowing_the_staged_capacity_take_the_full_capacity_launch(stag
             most = max(most, max(len(env.export_state(g)[1]) for g in range(6)))
     assert most > max(staged, 8), "the case was meant to exceed the staged capacity"
     env.close()
+
+
+def test_large_bot_slab_with_launch_ordering_matches_oracle():
+    """Slabs of >= 2048 scripted-bot games are launched slowest class first (mrts_order_kernel maps
+    launch slots to games).  The permutation must not change any result: a subsample of a 4,096-env
+    slab equals the oracle step by step, and every game is processed exactly once per step (the
+    per-env step counters advance together: all dones fire on the same max_steps frame)."""
+    import torch
+
+    n, sub = 4096, 12
+    ais = [W if i % 2 == 0 else P for i in range(n)]
+    env = _env(0, n, max_steps=90, ai2s=ais, map_paths=[MAP_16], return_torch=True, seed=9)
+    ref = _oracle(0, ais[:sub], MAP_16, max_steps=90)
+    np.testing.assert_array_equal(env.reset()[:sub].cpu().numpy(), ref.reset())
+    for t in range(200):
+        m = env.get_action_mask()
+        m_ref, _ = ref.get_masks()
+        np.testing.assert_array_equal(m[:sub].cpu().numpy(), m_ref, err_msg=f"mask {t}")
+        a = env.sample_actions()
+        o, r, d, infos = env.step(a)
+        o2, r2, d2 = ref.step(a[:sub].cpu().numpy())
+        np.testing.assert_array_equal(o[:sub].cpu().numpy(), o2, err_msg=f"obs {t}")
+        np.testing.assert_array_equal(infos.raw[:sub].cpu().numpy(), r2)
+        if (t + 1) % 90 == 0:
+            assert bool(d.all()), "every game must reach max_steps on the same frame"
+        elif t < 60:
+            assert not bool(d.any())
+    env.close()

@@ -25,7 +25,7 @@ obs = env.reset()
 for _ in range(prewarm):
     m = env.get_action_mask()
     obs, r, d, _ = env.step(env.sample_actions())
-tim = torch.zeros((G, 10), dtype=torch.int64, device=env.device)
+tim = torch.zeros((G, 12), dtype=torch.int64, device=env.device)
 _capi.check(L.mrts_debug_timing(env._h, C.c_void_p(tim.data_ptr())))
 hist = []
 for k in range(8):
@@ -39,6 +39,18 @@ names = ["rules", "total", "decode", "bot-puts", "bot-translate", "issue-agent",
 for lbl, x in [(names[k], t[:, :, k]) for k in range(10)]:
     q = np.percentile(x, [50, 90, 99, 99.9, 100])
     print(f"{name} {lbl:14s} /game: mean {x.mean():9.0f}  p50 {q[0]:9.0f}  p90 {q[1]:9.0f}  p99 {q[2]:9.0f}  p99.9 {q[3]:9.0f}  max {q[4]:9.0f}")
+# timeline of the last launch: resident games per SM over time, and how the launch ends
+last = hist[-1].astype(np.float64)
+start = last[:, 10] - last[:, 10].min()
+dur = last[:, 1] / 1.965  # cycles -> ns at 1965 MHz
+end = start + dur
+T = end.max()
+print(f"launch span {T/1e3:.1f} us; sum of game time {dur.sum()/1e6:.2f} ms -> mean concurrency {dur.sum()/T:.0f} games = {dur.sum()/T/148:.1f} per SM")
+for frac in (0.1, 0.25, 0.5, 0.75, 0.9, 0.95, 0.99):
+    t = frac * T
+    print(f"  at {frac:4.0%} of the span: {int(((start <= t) & (end > t)).sum()):6d} games resident, {int((start <= t).sum()):6d} started")
+order = np.argsort(start)
+print("  cost class of the first 2000 started (mean cycles)", last[order[:2000], 1].mean(), " of the last 2000", last[order[-2000:], 1].mean())
 state = [env.export_state(g)[1] for g in range(0, G, max(1, G // 256))]
 print("units/game mean", np.mean([len(s) for s in state]), "max", max(len(s) for s in state))
 env.close()
