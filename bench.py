@@ -288,9 +288,10 @@ def gpu_arm(args):
 
 def e2e_run(args, env_dev, wl, rank, dist, dev):
     """The call a user of the reference makes (ppo_gridnet.py:459-480 loop shape): get_action_mask()
-    -> NumPy, policy output -> NumPy, step(actions) -> NumPy obs / reward / done.  Host buffers are
-    pinned; every step moves the actions host->device and obs + mask + raw rewards + dones (and the
-    device policy's sampled actions, as `action.cpu().numpy()` does) device->host."""
+    -> NumPy, policy output -> NumPy, step(actions) -> NumPy obs / reward / done, all int32 / float64
+    host arrays as in the reference.  Every step moves the actions host->device and obs + mask + raw
+    rewards + dones (and the device policy's sampled action grid, as `action.cpu().numpy()` does)
+    device->host; the env's own traffic is bit-packed (mrts_step_host)."""
     import torch
 
     from microrts_py_b200 import microrts_ai
@@ -302,7 +303,7 @@ def e2e_run(args, env_dev, wl, rank, dist, dev):
     ai2s = [getattr(microrts_ai, wl["bot_names"][i * wl["nbot"] // nbot]) for i in range(nbot)] if nbot else []
     np_dtype = np.int32 if args.dtype == "int32" else np.uint8
     env = MicroRTSGridModeVecEnv(nsp, nbot, partial_obs=wl["partial"], max_steps=wl["max_steps"], ai2s=ai2s, map_paths=[wl["map"]],
-                                 device=dev.index, dtype=np_dtype, zero_copy=True, seed=77 + rank)
+                                 device=dev.index, dtype=np_dtype, host_transport=True, seed=77 + rank)
     a_host = torch.zeros((n, env.height * env.width, 7), dtype=torch.int32).pin_memory()
     env.reset()
     mask = env.get_action_mask()
@@ -332,11 +333,14 @@ def e2e_run(args, env_dev, wl, rank, dist, dev):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         world = dist.get_world_size()
     dt = float(t.item())
-    h2d = a_host.numel() * 4
-    d2h = obs.nbytes + m.nbytes + n * 6 * 8 + n + a_host.numel() * 4
+    hw = env.height * env.width
+    h2d = n * hw * 2                                            # packed action rows
+    d2h = n * hw * 16 + n * 6 * 8 + n + a_host.numel() * 4      # obs + mask bits, rewards, dones; + the policy's action grid
+    host_threads = env._lib.mrts_host_threads(env._h)
     env.close()
     return {"value": n * world * steps / dt, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "envs_per_gpu": n, "steps": steps,
-            "ms_per_step": 1e3 * dt / steps, "api": "MicroRTSGridModeVecEnv(zero_copy=True).step/get_action_mask with NumPy in/out (pinned host buffers)"}
+            "ms_per_step": 1e3 * dt / steps, "api": "MicroRTSGridModeVecEnv(host_transport=True).step/get_action_mask, NumPy int32 in/out; mrts_step_host moves 1 bit per element over PCIe and widens on %d host threads" % host_threads,
+            "host_bytes_written_per_step": int(obs.nbytes + m.nbytes)}
 
 
 def main():

@@ -93,6 +93,18 @@ int mrts_step_ex(mrts_env* env, const mrts_step_io* io, void* stream);
 /* The same sampler on the current state (e.g. after mrts_reset). */
 int mrts_sample_actions(mrts_env* env, int32_t* next_actions, uint64_t seed, void* stream);
 
+/* Host-buffer forms of reset / gameStep + getMasks: every pointer is a HOST pointer (pageable is fine),
+ * the call returns when the arrays are filled -- what the reference's NumPy-returning methods do
+ * (gym_microrts/envs/vec_env.py:278-282, 968-1061, 1091-1101).  obs (N,H,W,P) and mask (N,H*W,78) have
+ * the element type of the env (int32 / uint8); reward (N,6) float64; done (N,) uint8; actions
+ * (N,H*W,7) int32 or int64 (action_elem_bytes 4 / 8) -- only the rows of cells whose mask entry 0 was 1 in
+ * the mask last returned are read, as in vec_env.py:972-974.  Any output pointer may be NULL.  The
+ * values cross PCIe as one bit per element and are widened on the host by a thread pool (csrc/mrts_host.h);
+ * the library owns its own stream and pinned staging buffers for these calls. */
+int mrts_reset_host(mrts_env* env, void* obs, void* mask);
+int mrts_step_host(mrts_env* env, const void* actions, int action_elem_bytes, void* obs, void* mask, double* reward, uint8_t* done);
+int mrts_host_threads(const mrts_env* env); /* worker threads of the widening pool (0 before the first host call) */
+
 /* Introspection (synchronises the stream). */
 int mrts_num_envs(const mrts_env* env);
 int mrts_num_games(const mrts_env* env);

@@ -147,6 +147,9 @@ SYMBOLS = [
     "mrts_get_masks",
     "mrts_step_ex",
     "mrts_sample_actions",
+    "mrts_reset_host",
+    "mrts_step_host",
+    "mrts_host_threads",
     "mrts_num_envs",
     "mrts_num_games",
     "mrts_planes",
@@ -187,6 +190,9 @@ def lib():
         L.mrts_debug_issue.argtypes = [vp, C.c_int, vp, C.c_int, vp]
         L.mrts_debug_cycle.argtypes = [vp, C.c_int, C.POINTER(C.c_int), vp]
         L.mrts_debug_timing.argtypes = [vp, vp]
+        L.mrts_reset_host.argtypes = [vp, vp, vp]
+        L.mrts_step_host.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp]
+        L.mrts_host_threads.argtypes = [vp]
         L.mrts_last_error.restype = C.c_char_p
         L.mrts_version.restype = C.c_char_p
         _lib = L

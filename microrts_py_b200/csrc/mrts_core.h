@@ -361,15 +361,16 @@ struct Sim {
     }
     // whole thread group, before the rules: every idle owned unit fetches its cell's row of its
     // player view's (HW,7) block (self-play: view = player; bot game: only player 0 is driven)
-    MRTS_HD void prefetch_actions(const int32_t* a0, int tid, int nth) {
+    // a0 = the game's first view's (HW,7) int32 block, or (host transport) p0 = its (HW,) block of rows
+    // already packed by pack_action on the host
+    MRTS_HD void prefetch_actions(const int32_t* a0, const uint16_t* p0, int tid, int nth) {
         const int n = nunits();
-#pragma unroll 1
         for (int i = tid; i < n; i += nth) {
             Unit& un = u[i];
             if (un.player < 0 || un.a_type >= 0) continue;
             if (ai != AI_NONE && un.player != 0) continue;
-            const int32_t* a = a0 + ((size_t)un.player * HW + (un.x + un.y * W)) * 7;
-            un.pre = pack_action(a);
+            const size_t cell = (size_t)un.player * HW + (un.x + un.y * W);
+            un.pre = p0 ? p0[cell] : pack_action(a0 + cell * 7);
         }
     }
 

@@ -1,0 +1,271 @@
+// See mrts_host.h.  Plain C++17 + AVX2 where the CPU has it (checked at run time).
+#include "mrts_host.h"
+
+#include <sched.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
+
+namespace mrts_host {
+
+// ------------------------------------------------------------------------------------------------
+struct Pool {
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv_work, cv_done;
+    std::function<void(size_t, size_t)> fn;
+    size_t n = 0;
+    int generation = 0, pending = 0;
+    bool stop = false;
+    int nthreads = 1;
+};
+
+static void worker_main(Pool* p, int rank) {
+    int seen = 0;
+    for (;;) {
+        std::function<void(size_t, size_t)> fn;
+        size_t n;
+        {
+            std::unique_lock<std::mutex> lk(p->mu);
+            p->cv_work.wait(lk, [&] { return p->stop || p->generation != seen; });
+            if (p->stop) return;
+            seen = p->generation;
+            fn = p->fn;
+            n = p->n;
+        }
+        const size_t per = (n + p->nthreads - 1) / p->nthreads;
+        const size_t b = per * rank, e = b + per < n ? b + per : n;
+        if (b < e) fn(b, e);
+        {
+            std::lock_guard<std::mutex> lk(p->mu);
+            if (--p->pending == 0) p->cv_done.notify_all();
+        }
+    }
+}
+
+Pool* pool_create(int threads) {
+    if (threads <= 0) {
+        cpu_set_t set;
+        CPU_ZERO(&set);
+        threads = sched_getaffinity(0, sizeof(set), &set) == 0 ? CPU_COUNT(&set) : (int)std::thread::hardware_concurrency();
+        if (threads <= 0) threads = 1;
+    }
+    Pool* p = new Pool();
+    p->nthreads = threads;
+    for (int r = 1; r < threads; r++) p->workers.emplace_back(worker_main, p, r);  // rank 0 = the caller
+    return p;
+}
+void pool_destroy(Pool* p) {
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->stop = true;
+    }
+    p->cv_work.notify_all();
+    for (auto& t : p->workers) t.join();
+    delete p;
+}
+int pool_threads(const Pool* p) { return p ? p->nthreads : 1; }
+
+static void parallel_for(Pool* p, size_t n, const std::function<void(size_t, size_t)>& fn) {
+    if (!p || p->nthreads == 1 || n < 2) {
+        fn(0, n);
+        return;
+    }
+    {
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->fn = fn;
+        p->n = n;
+        p->pending = (int)p->workers.size();
+        p->generation++;
+    }
+    p->cv_work.notify_all();
+    const size_t per = (n + p->nthreads - 1) / p->nthreads;
+    if (per > 0) fn(0, per < n ? per : n);
+    std::unique_lock<std::mutex> lk(p->mu);
+    p->cv_done.wait(lk, [&] { return p->pending == 0; });
+}
+
+// ------------------------------------------------------------------------------------------------
+static void obs_scalar32(const uint32_t* w, size_t cells, int planes, int32_t* out) {
+    for (size_t c = 0; c < cells; c++) {
+        const uint32_t v = w[c];
+        int32_t* o = out + c * planes;
+        for (int k = 0; k < planes; k++) o[k] = (int32_t)((v >> k) & 1u);
+    }
+}
+static void obs_scalar8(const uint32_t* w, size_t cells, int planes, uint8_t* out) {
+    for (size_t c = 0; c < cells; c++) {
+        const uint32_t v = w[c];
+        uint8_t* o = out + c * planes;
+        for (int k = 0; k < planes; k++) o[k] = (uint8_t)((v >> k) & 1u);
+    }
+}
+
+#if defined(__x86_64__)
+// 8 planes per 256-bit store; a cell's last store spills into the next cell, which then overwrites it
+// (cells are written in increasing order); the final cell of the range is finished with scalar code.
+__attribute__((target("avx2"))) static void obs_avx2_32(const uint32_t* w, size_t cells, int planes, int32_t* out) {
+    if (cells == 0) return;
+    const __m256i one = _mm256_set1_epi32(1);
+    const __m256i s0 = _mm256_setr_epi32(0, 1, 2, 3, 4, 5, 6, 7);
+    const __m256i s1 = _mm256_setr_epi32(8, 9, 10, 11, 12, 13, 14, 15);
+    const __m256i s2 = _mm256_setr_epi32(16, 17, 18, 19, 20, 21, 22, 23);
+    const __m256i s3 = _mm256_setr_epi32(24, 25, 26, 27, 28, 29, 30, 31);
+    for (size_t c = 0; c + 1 < cells; c++) {
+        const __m256i v = _mm256_set1_epi32((int)w[c]);
+        int32_t* o = out + c * planes;
+        _mm256_storeu_si256((__m256i*)(o), _mm256_and_si256(_mm256_srlv_epi32(v, s0), one));
+        _mm256_storeu_si256((__m256i*)(o + 8), _mm256_and_si256(_mm256_srlv_epi32(v, s1), one));
+        _mm256_storeu_si256((__m256i*)(o + 16), _mm256_and_si256(_mm256_srlv_epi32(v, s2), one));
+        _mm256_storeu_si256((__m256i*)(o + 24), _mm256_and_si256(_mm256_srlv_epi32(v, s3), one));  // planes >= 24 + 5; spill <= 3 ints
+    }
+    obs_scalar32(w + cells - 1, 1, planes, out + (cells - 1) * planes);
+}
+// Aligned output (the usual case: NumPy's large arrays are page aligned and an env's block is a
+// multiple of 32 bytes): the env's elements are produced 8 at a time from the continuous bit stream
+// (as the device kernels do) and written with non-temporal stores -- the arrays are far larger
+// than the caches and are only read later, by the consumer.
+__attribute__((target("avx2"))) static void obs_avx2_stream32(const uint32_t* w, size_t cells, int planes, int32_t* out) {
+    const __m256i one = _mm256_set1_epi32(1);
+    const __m256i s0 = _mm256_setr_epi32(0, 1, 2, 3, 4, 5, 6, 7);
+    const size_t total = cells * (size_t)planes, n8 = total / 8;
+    size_t q = 0;
+    int o = 0;
+    for (size_t j = 0; j < n8; j++) {
+        const uint64_t keep = (1ull << planes) - 1;
+        const uint64_t lo = w[q] & keep, hi = q + 1 < cells ? (w[q + 1] & keep) : 0;
+        const uint32_t bits = (uint32_t)(((hi << planes) | lo) >> o);
+        _mm256_stream_si256((__m256i*)(out + 8 * j), _mm256_and_si256(_mm256_srlv_epi32(_mm256_set1_epi32((int)bits), s0), one));
+        o += 8;
+        if (o >= planes) {
+            o -= planes;
+            q++;
+        }
+    }
+    for (size_t e = n8 * 8; e < total; e++) out[e] = (int32_t)((w[e / planes] >> (e % planes)) & 1u);
+    _mm_sfence();
+}
+__attribute__((target("avx2"))) static void zero_stream(void* p, size_t bytes) {  // p 32-byte aligned
+    const __m256i z = _mm256_setzero_si256();
+    uint8_t* b = (uint8_t*)p;
+    size_t k = 0;
+    for (; k + 128 <= bytes; k += 128) {
+        _mm256_stream_si256((__m256i*)(b + k), z);
+        _mm256_stream_si256((__m256i*)(b + k + 32), z);
+        _mm256_stream_si256((__m256i*)(b + k + 64), z);
+        _mm256_stream_si256((__m256i*)(b + k + 96), z);
+    }
+    for (; k + 32 <= bytes; k += 32) _mm256_stream_si256((__m256i*)(b + k), z);
+    if (k < bytes) memset(b + k, 0, bytes - k);
+    _mm_sfence();
+}
+static bool has_avx2() {
+    static const bool v = __builtin_cpu_supports("avx2");
+    return v;
+}
+// Non-temporal stores are OFF unless MRTS_HOST_NT=1: on the B200 hosts measured (16-core Xeon VM) they
+// were slower than regular stores (561k vs 636k env-steps/s end to end at 16x16, 8,192 envs).
+static bool use_stream() {
+    static const bool v = [] {
+        const char* e = getenv("MRTS_HOST_NT");
+        return e && e[0] == '1';
+    }();
+    return v;
+}
+#endif
+
+void expand_obs(Pool* p, const uint32_t* words, size_t n_env, int hw, int planes, int elem, void* out) {
+    parallel_for(p, n_env, [=](size_t b, size_t e) {
+        const size_t cells = (e - b) * (size_t)hw;
+        const uint32_t* w = words + b * hw;
+        if (elem == 4) {
+            int32_t* o = (int32_t*)out + b * (size_t)hw * planes;
+#if defined(__x86_64__)
+            if (has_avx2() && use_stream() && (((uintptr_t)o) & 31) == 0 && planes <= 31) {
+                obs_avx2_stream32(w, cells, planes, o);
+                return;
+            }
+            if (has_avx2() && planes >= 29) {
+                obs_avx2_32(w, cells, planes, o);
+                return;
+            }
+#endif
+            obs_scalar32(w, cells, planes, o);
+        } else {
+            obs_scalar8(w, cells, planes, (uint8_t*)out + b * (size_t)hw * planes);
+        }
+    });
+}
+
+void expand_mask(Pool* p, const uint32_t* pmask, size_t n_env, int hw, int elem, void* out) {
+    parallel_for(p, n_env, [=](size_t b, size_t e) {
+        for (size_t env = b; env < e; env++) {
+            const uint32_t* pm = pmask + env * (size_t)hw * 3;
+            uint8_t* o = (uint8_t*)out + env * (size_t)hw * 78 * elem;
+#if defined(__x86_64__)
+            if (has_avx2() && use_stream() && (((uintptr_t)o) & 31) == 0) zero_stream(o, (size_t)hw * 78 * elem);
+            else
+#endif
+                memset(o, 0, (size_t)hw * 78 * elem);
+            for (int c = 0; c < hw; c++) {
+                const uint32_t m0 = pm[3 * c], m1 = pm[3 * c + 1], m2 = pm[3 * c + 2];
+                if ((m0 | m1 | m2) == 0) continue;
+                for (int k = 0; k < 78; k++) {
+                    const uint32_t word = k < 32 ? m0 : (k < 64 ? m1 : m2);
+                    const uint32_t bit = (word >> (k & 31)) & 1u;
+                    if (elem == 4) ((int32_t*)o)[(size_t)c * 78 + k] = (int32_t)bit;
+                    else o[(size_t)c * 78 + k] = (uint8_t)bit;
+                }
+            }
+        }
+    });
+}
+
+// same encoding as mrts::Sim::pack_action (mrts_core.h)
+template <class T>
+static inline uint16_t pack_row(const T* a) {
+    const long long t = (long long)a[0];
+    if (t < 1 || t > 5) return 0;
+    int pay = 0, bad = 0;
+    if (t == 4) {
+        if (a[5] < 0 || a[5] >= 7) return 0;
+        bad = a[4] < 0 || a[4] > 3;
+        pay = (bad ? 0 : (int)a[4]) | ((int)a[5] << 2);
+    } else if (t == 5) {
+        pay = (a[6] < 0 || a[6] > 48) ? 63 : (int)a[6];
+    } else {
+        const long long d = (long long)a[t];
+        bad = d < 0 || d > 3;
+        pay = bad ? 0 : (int)d;
+    }
+    return (uint16_t)(t | (pay << 3) | (bad << 9));
+}
+
+void pack_actions(Pool* p, const void* actions, int action_elem, const uint32_t* pmask, size_t n_env, int hw, uint16_t* out) {
+    parallel_for(p, n_env, [=](size_t b, size_t e) {
+        for (size_t env = b; env < e; env++) {
+            const uint32_t* pm = pmask + env * (size_t)hw * 3;
+            uint16_t* o = out + env * (size_t)hw;
+            for (int c = 0; c < hw; c++) {
+                if ((pm[3 * c] & 1u) == 0) {  // NOOP is legal exactly at the cells of units that may act
+                    o[c] = 0;
+                    continue;
+                }
+                const size_t row = (env * (size_t)hw + c) * 7;
+                o[c] = action_elem == 8 ? pack_row((const int64_t*)actions + row) : pack_row((const int32_t*)actions + row);
+            }
+        }
+    });
+}
+
+}  // namespace mrts_host

@@ -1,0 +1,31 @@
+// Host side of the packed transport used by the host-buffer entry points (mrts_reset_host /
+// mrts_step_host, include/mrts_b200.h).
+//
+// The reference hands NumPy int32 arrays to its caller (gym_microrts/envs/vec_env.py:278-282,
+// 1001-1061, 1091-1101): 109,568 B per env-step at 16x16, all of it 0/1 values.  Moving that
+// over PCIe costs more than computing it, so the kernels emit one BIT per element (mrts_step.h:
+// EnvParams::pobs / pmask), the bits cross the bus, and the functions below only widen them to
+// the int32 (or uint8) layout of the caller's arrays -- a transport codec, no game logic: every
+// value is computed on the device.  The other direction packs the caller's (N, HW, 7) action
+// grid into 16 bits per source cell (same encoding as Sim::pack_action).
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+namespace mrts_host {
+
+// persistent worker pool; parallel_for(n, f) runs f(begin, end) over [0, n) split into contiguous blocks
+struct Pool;
+Pool* pool_create(int threads /* 0 = all cores this process may use */);
+void pool_destroy(Pool* p);
+int pool_threads(const Pool* p);
+
+// obs words (n_env, hw) -> one-hot (n_env, hw, planes), elem = 4 (int32) or 1 (uint8)
+void expand_obs(Pool* p, const uint32_t* words, size_t n_env, int hw, int planes, int elem, void* out);
+// mask words (n_env, hw, 3) -> (n_env, hw, 78), elem = 4 or 1
+void expand_mask(Pool* p, const uint32_t* pmask, size_t n_env, int hw, int elem, void* out);
+// actions (n_env, hw, 7) int32 or int64 -> packed (n_env, hw) uint16, only at cells whose mask words
+// (the mask the caller was given for this state) are non-zero; other cells 0
+void pack_actions(Pool* p, const void* actions, int action_elem /* 4 or 8 */, const uint32_t* pmask, size_t n_env, int hw, uint16_t* out);
+
+}  // namespace mrts_host

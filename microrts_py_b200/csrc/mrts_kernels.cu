@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "../../include/mrts_b200.h"
+#include "mrts_host.h"
 #include "mrts_setup.h"
 
 using namespace mrts;
@@ -170,6 +171,19 @@ struct mrts_env {
     int smem_full = 0;  // bytes per game at the full capacity (overflow / debug launches)
     int32_t* d_ovf = nullptr;
     long long* d_timing = nullptr;  // profiling aid (mrts_debug_timing)
+    // ---- host-buffer entry points (mrts_reset_host / mrts_step_host): packed transport, see mrts_host.h
+    struct HostIO {
+        cudaStream_t stream = nullptr;
+        cudaEvent_t ev_obs = nullptr;
+        uint16_t *h_pact = nullptr, *d_pact = nullptr;
+        uint32_t *h_pobs = nullptr, *d_pobs = nullptr, *h_pmask = nullptr, *d_pmask = nullptr;
+        double *h_rew = nullptr, *d_rew = nullptr;
+        uint8_t *h_done = nullptr, *d_done = nullptr;
+        mrts_host::Pool* pool = nullptr;
+        bool ready = false, have_mask = false;
+    } hio;
+    const uint16_t* cur_pact = nullptr;  // per-launch packed pointers (set by the host entry points)
+    uint32_t *cur_pobs = nullptr, *cur_pmask = nullptr;
     uint32_t* d_cost = nullptr;     // bot slabs: last step cycles per game
     int32_t* d_order = nullptr;     // 4 * n_games launch order + 4 class counts
     int N = 0;
@@ -212,6 +226,11 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     P.next_actions = next_actions;
     P.seed = seed;
     P.counter = next_actions ? e->sample_counter++ : 0;
+    P.pact = e->cur_pact;
+    P.pobs = e->cur_pobs;
+    P.pmask = e->cur_pmask;
+    e->cur_pact = nullptr;
+    e->cur_pobs = e->cur_pmask = nullptr;
     P.timing = e->d_timing;
     const int GPB = e->gpb;
     const dim3 wgrid((P.n_games + GPB - 1) / GPB), bgrid(P.n_games);
@@ -413,6 +432,17 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
 void mrts_destroy(mrts_env* e) {
     if (!e) return;
     cudaSetDevice(e->device);
+    {
+        auto& h = e->hio;
+        if (h.stream) cudaStreamSynchronize(h.stream);
+        for (void* p : {(void*)h.h_pact, (void*)h.h_pobs, (void*)h.h_pmask, (void*)h.h_rew, (void*)h.h_done})
+            if (p) cudaFreeHost(p);
+        for (void* p : {(void*)h.d_pact, (void*)h.d_pobs, (void*)h.d_pmask, (void*)h.d_rew, (void*)h.d_done})
+            if (p) cudaFree(p);
+        if (h.ev_obs) cudaEventDestroy(h.ev_obs);
+        if (h.stream) cudaStreamDestroy(h.stream);
+        mrts_host::pool_destroy(h.pool);
+    }
     for (void* p : e->allocs) cudaFree(p);
     if (e->d_rows) cudaFree(e->d_rows);
     delete e;
@@ -439,6 +469,86 @@ int mrts_sample_actions(mrts_env* e, int32_t* next_actions, uint64_t seed, void*
     if (!next_actions) return fail(MRTS_EINVAL, "next_actions is null");
     return launch(e, MODE_OBSERVE, nullptr, nullptr, nullptr, nullptr, nullptr, stream, next_actions, seed);
 }
+
+static int hostio_init(mrts_env* e) {
+    auto& h = e->hio;
+    if (h.ready) return MRTS_OK;
+    CK(cudaSetDevice(e->device));
+    const size_t N = (size_t)e->N, HW = (size_t)e->P.HW;
+    CK(cudaStreamCreateWithFlags(&h.stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h.ev_obs, cudaEventDisableTiming));
+    CK(cudaMallocHost((void**)&h.h_pact, N * HW * sizeof(uint16_t)));
+    CK(cudaMallocHost((void**)&h.h_pobs, N * HW * sizeof(uint32_t)));
+    CK(cudaMallocHost((void**)&h.h_pmask, N * HW * 3 * sizeof(uint32_t)));
+    CK(cudaMallocHost((void**)&h.h_rew, N * 6 * sizeof(double)));
+    CK(cudaMallocHost((void**)&h.h_done, N));
+    CK(cudaMalloc((void**)&h.d_pact, N * HW * sizeof(uint16_t)));
+    CK(cudaMalloc((void**)&h.d_pobs, N * HW * sizeof(uint32_t)));
+    CK(cudaMalloc((void**)&h.d_pmask, N * HW * 3 * sizeof(uint32_t)));
+    CK(cudaMalloc((void**)&h.d_rew, N * 6 * sizeof(double)));
+    CK(cudaMalloc((void**)&h.d_done, N));
+    h.pool = mrts_host::pool_create(0);
+    h.ready = true;
+    return MRTS_OK;
+}
+
+// device -> pinned staging -> the caller's arrays; the observation is widened while the mask words are still in flight
+static int hostio_finish(mrts_env* e, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done) {
+    auto& h = e->hio;
+    const size_t N = (size_t)e->N, HW = (size_t)e->P.HW;
+    CK(cudaMemcpyAsync(h.h_pobs, h.d_pobs, N * HW * 4, cudaMemcpyDeviceToHost, h.stream));
+    CK(cudaEventRecord(h.ev_obs, h.stream));
+    CK(cudaMemcpyAsync(h.h_pmask, h.d_pmask, N * HW * 12, cudaMemcpyDeviceToHost, h.stream));
+    if (h_reward) CK(cudaMemcpyAsync(h.h_rew, h.d_rew, N * 48, cudaMemcpyDeviceToHost, h.stream));
+    if (h_done) CK(cudaMemcpyAsync(h.h_done, h.d_done, N, cudaMemcpyDeviceToHost, h.stream));
+    CK(cudaEventSynchronize(h.ev_obs));
+    if (h_obs) mrts_host::expand_obs(h.pool, h.h_pobs, N, (int)HW, e->P.planes, e->P.elem, h_obs);
+    CK(cudaStreamSynchronize(h.stream));
+    h.have_mask = true;
+    if (h_mask) mrts_host::expand_mask(h.pool, h.h_pmask, N, (int)HW, e->P.elem, h_mask);
+    if (h_reward) memcpy(h_reward, h.h_rew, N * 48);
+    if (h_done) memcpy(h_done, h.h_done, N);
+    return MRTS_OK;
+}
+
+int mrts_reset_host(mrts_env* e, void* h_obs, void* h_mask) {
+    if (!e) return fail(MRTS_EINVAL, "null env");
+    int rc = hostio_init(e);
+    if (rc) return rc;
+    e->cur_pobs = e->hio.d_pobs;
+    e->cur_pmask = e->hio.d_pmask;
+    rc = launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, e->hio.stream);
+    if (rc) return rc;
+    return hostio_finish(e, h_obs, h_mask, nullptr, nullptr);
+}
+
+int mrts_step_host(mrts_env* e, const void* h_actions, int action_elem_bytes, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done) {
+    if (!e || !h_actions) return fail(MRTS_EINVAL, "null argument");
+    if (action_elem_bytes != 4 && action_elem_bytes != 8) return fail(MRTS_EINVAL, "actions must be int32 or int64");
+    int rc = hostio_init(e);
+    if (rc) return rc;
+    auto& h = e->hio;
+    const size_t N = (size_t)e->N, HW = (size_t)e->P.HW;
+    if (!h.have_mask) {  // first call without a preceding mrts_reset_host: fetch the mask words of the current state
+        e->cur_pobs = h.d_pobs;
+        e->cur_pmask = h.d_pmask;
+        rc = launch(e, MODE_OBSERVE, nullptr, nullptr, nullptr, nullptr, nullptr, h.stream);
+        if (rc) return rc;
+        rc = hostio_finish(e, nullptr, nullptr, nullptr, nullptr);
+        if (rc) return rc;
+    }
+    mrts_host::pack_actions(h.pool, h_actions, action_elem_bytes, h.h_pmask, N, (int)HW, h.h_pact);
+    CK(cudaMemcpyAsync(h.d_pact, h.h_pact, N * HW * 2, cudaMemcpyHostToDevice, h.stream));
+    e->cur_pact = h.d_pact;
+    e->cur_pobs = h.d_pobs;
+    e->cur_pmask = h.d_pmask;
+    // `actions` is unused when the packed rows are given; pass a valid non-null pointer for the argument check
+    rc = launch(e, MODE_STEP, (const int32_t*)h.d_pact, nullptr, nullptr, h.d_rew, h.d_done, h.stream);
+    if (rc) return rc;
+    return hostio_finish(e, h_obs, h_mask, h_reward, h_done);
+}
+
+int mrts_host_threads(const mrts_env* e) { return e && e->hio.pool ? mrts_host::pool_threads(e->hio.pool) : 0; }
 
 int mrts_num_envs(const mrts_env* e) { return e ? e->N : MRTS_EINVAL; }
 int mrts_num_games(const mrts_env* e) { return e ? e->P.n_games : MRTS_EINVAL; }

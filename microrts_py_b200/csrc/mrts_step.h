@@ -38,6 +38,10 @@ struct EnvParams {
     void* mask;                     // (N, HW, 78) or null
     double* reward;                 // (N, 6) or null
     uint8_t* done;                  // (N,) or null
+    // packed transport of the host-buffer entry points (mrts_step_host): one bit per one-hot element
+    const uint16_t* pact;           // (N, HW) action rows packed by Sim::pack_action, replaces `actions` when non-null
+    uint32_t* pobs;                 // (N, HW) observation words (bit k = plane k) or null
+    uint32_t* pmask;                // (N, HW, 3) mask words (bit k of the 78) or null
     int32_t* next_actions;          // (N, HW, 7) or null: masked-uniform sample for the resulting state
     uint64_t seed;                  // sampler key
     uint32_t counter;               // launch counter (sampler stream position)
@@ -243,7 +247,8 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     sync();
     if (P.mode == MODE_STEP && s.ai == AI_WORKER_RUSH && !P.partial) s.flood_base_rows(-1, tid, nth);
     // the agents' action rows of the units that may act, fetched by the whole group (the leader never waits on HBM)
-    if (P.mode == MODE_STEP) s.prefetch_actions(P.actions + (size_t)env0 * P.HW * 7, tid, nth);
+    if (P.mode == MODE_STEP)
+        s.prefetch_actions(P.pact ? nullptr : P.actions + (size_t)env0 * P.HW * 7, P.pact ? P.pact + (size_t)env0 * P.HW : nullptr, tid, nth);
     sync();
 
     // ---------------- rules (leader)
@@ -284,7 +289,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     // ---------------- observations, one view at a time (before compaction: stale views keep the dead)
     const size_t obs_env = (size_t)P.HW * PLANES * ELEM;
     const size_t mask_env = (size_t)P.HW * 78 * ELEM;
-    if (P.obs) {
+    if (P.obs || P.pobs) {
         for (int v = 0; v < nviews; v++) {
             obs_words_cells(s, v, P.partial ? v : -1, grid0, words, tid, nth);
             if (P.partial) {
@@ -292,7 +297,8 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
                 obs_words_dead(s, v, v, words, tid, nth);
             }
             sync();
-            store_obs<ELEM, PLANES>(words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, tid, nth);
+            if (P.obs) store_obs<ELEM, PLANES>(words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, tid, nth);
+            if (P.pobs) copy16<uint32_t>(P.pobs + (size_t)(env0 + v) * P.HW, words, P.HW * 4, tid, nth);
             sync();
         }
     }
@@ -300,11 +306,15 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         if (tid == 0) s.compact();
         sync();
     }
-    if (P.mask || P.next_actions) unit_masks(s, umask, tid, nth);
+    if (P.mask || P.pmask || P.next_actions) unit_masks(s, umask, tid, nth);
 
     // ---------------- mask: zero fill, then the 78 entries of every source unit
     if (P.mask)
         for (int v = 0; v < nviews; v++) zero_mask<ELEM>(P.HW, (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env, tid, nth);
+    if (P.pmask) {
+        uint32_t* pm = P.pmask + (size_t)env0 * P.HW * 3;
+        for (int k = tid; k < nviews * P.HW * 3; k += nth) pm[k] = 0;
+    }
     if (P.cost && s.ai == AI_WORKER_RUSH) {
         const int n = s.hdr->nunits;
         int mine = 0;
@@ -320,6 +330,17 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         for (int v = 0; v < nviews; v++) {
             void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;
             patch_mask<ELEM>(s, v, umask, m, tid, nth);
+        }
+    }
+    if (P.pmask) {
+        const int n = s.hdr->nunits;
+        for (int i = tid; i < n; i += nth) {
+            const Unit& un = s.u[i];
+            if (un.player < 0 || un.player >= nviews || un.a_type >= 0 || (un.flags & UF_DEAD)) continue;
+            uint32_t* pm = P.pmask + ((size_t)(env0 + un.player) * P.HW + (un.x + un.y * s.W)) * 3;
+            pm[0] = umask[3 * i];
+            pm[1] = umask[3 * i + 1];
+            pm[2] = umask[3 * i + 2];
         }
     }
 

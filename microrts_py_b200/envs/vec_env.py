@@ -15,6 +15,10 @@ Extra keyword-only arguments (all default to the reference's behaviour):
   return_torch  return device tensors instead of NumPy arrays (no host round trip)
   zero_copy     NumPy mode only: return views of two alternating pinned host buffers instead of
                 fresh arrays (an array stays valid until the second next call of the same method)
+  host_transport NumPy mode only: use the library's host-buffer entry points (mrts_reset_host /
+                mrts_step_host): results cross PCIe as one bit per element and are widened into the
+                NumPy arrays by the library's thread pool; same values, shapes and dtypes.  Arrays are
+                two alternating buffers per output (as with ``zero_copy``)
   fuse_mask     compute the action mask of the resulting state inside ``step`` (one launch,
                 the state is staged once); ``get_action_mask`` then only hands it out
 """
@@ -125,6 +129,7 @@ class MicroRTSGridModeVecEnv:
         return_torch=False,
         zero_copy=False,
         fuse_mask=True,
+        host_transport=False,
         microrts_path=None,
         threads_per_game=0,
         staged_units=0,
@@ -186,6 +191,7 @@ class MicroRTSGridModeVecEnv:
         self.return_torch = bool(return_torch)
         self.zero_copy = bool(zero_copy)
         self.fuse_mask = bool(fuse_mask)
+        self.host_transport = bool(host_transport) and not self.return_torch
 
         self._lib = _capi.lib()
         cfg, self._keep = _capi.make_config(
@@ -231,6 +237,15 @@ class MicroRTSGridModeVecEnv:
         self.source_unit_mask = None
         self._closed = False
         self._sample_seed = int(seed)
+        if self.host_transport:
+            self._hbuf = {
+                "obs": [np.zeros(self._shape_obs, self._np_dtype) for _ in range(2)],
+                "mask": [np.zeros(self._shape_mask, self._np_dtype) for _ in range(2)],
+                "raw": [np.zeros((N, 6), np.float64) for _ in range(2)],
+                "done": [np.zeros((N,), np.uint8) for _ in range(2)],
+            }
+            self._hcur = 0
+            self._h_mask_np = None
 
     # ------------------------------------------------------------------------------ helpers
     def _stream(self):
@@ -269,6 +284,12 @@ class MicroRTSGridModeVecEnv:
     def reset(self):
         """JNIGridnetVecClient.reset + _encode_obs (vec_env.py:278-282): (N,H,W,P) observations."""
         self._check_open()
+        if self.host_transport:
+            self._hcur ^= 1
+            o, m = self._hbuf["obs"][self._hcur], self._hbuf["mask"][self._hcur]
+            _capi.check(self._lib.mrts_reset_host(self._h, o.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.c_void_p)))
+            self._h_mask_np = m
+            return o
         obs = self._new(self._shape_obs, self._t_dtype)
         mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
         with torch.cuda.device(self.device):
@@ -283,6 +304,11 @@ class MicroRTSGridModeVecEnv:
         """vec_env.py:1091-1101: (N, H*W, 78) mask of the current state; also refreshes
         ``source_unit_mask`` (N, H*W)."""
         self._check_open()
+        if self.host_transport:
+            if self._h_mask_np is None:
+                raise RuntimeError("get_action_mask() before reset()")
+            self.source_unit_mask = self._h_mask_np[:, :, 0]
+            return self._h_mask_np
         if not self._mask_valid:
             mask = self._new(self._shape_mask, self._t_dtype)
             with torch.cuda.device(self.device):
@@ -303,6 +329,13 @@ class MicroRTSGridModeVecEnv:
         ``source_unit_mask`` is 1; the device decode applies the same rule to the current state
         (PlayerAction.java:407), so the full grid is uploaded as is."""
         self._check_open()
+        if self.host_transport:
+            a = actions.cpu().numpy() if isinstance(actions, torch.Tensor) else np.asarray(actions)
+            a = a.reshape(self._shape_act)
+            if a.dtype not in (np.int32, np.int64) or not a.flags.c_contiguous:
+                a = np.ascontiguousarray(a, np.int64)
+            self._pending_actions = a
+            return
         if isinstance(actions, torch.Tensor):
             a = actions.reshape(self._shape_act)
             if a.device.type == "cuda":
@@ -326,6 +359,17 @@ class MicroRTSGridModeVecEnv:
         a = self._pending_actions
         self._pending_actions = None
         N = self.num_envs
+        if self.host_transport:
+            self._hcur ^= 1
+            k = self._hcur
+            o, m, reward, d = self._hbuf["obs"][k], self._hbuf["mask"][k], self._hbuf["raw"][k], self._hbuf["done"][k]
+            vp = C.c_void_p
+            _capi.check(self._lib.mrts_step_host(self._h, a.ctypes.data_as(vp), a.dtype.itemsize, o.ctypes.data_as(vp), m.ctypes.data_as(vp),
+                                                 reward.ctypes.data_as(vp), d.ctypes.data_as(vp)))
+            self._h_mask_np = m
+            if not self.reward_shaping:
+                reward[:, 1:] = 0
+            return o, reward @ self.reward_weight, d.astype(np.bool_), _LazyInfos(reward)
         obs = self._new(self._shape_obs, self._t_dtype)
         mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
         raw = self._new((N, 6), torch.float64)

@@ -26,11 +26,12 @@ def _oracle(nsp, ais, mp, partial=False, max_steps=2000):
     return OracleVecEnv(nsp, len(ais), max_steps, partial, templates_for([mp] * n), [a(None).ai_id for a in ais])
 
 
-@pytest.mark.parametrize("mode", ["torch", "uint8", "unfused", "zero_copy"])
+@pytest.mark.parametrize("mode", ["torch", "uint8", "unfused", "zero_copy", "host_transport", "host_transport_uint8"])
 def test_modes_match_oracle(mode):
     import torch
 
-    kw = dict(torch=dict(return_torch=True), uint8=dict(dtype=np.uint8), unfused=dict(fuse_mask=False), zero_copy=dict(zero_copy=True))[mode]
+    kw = dict(torch=dict(return_torch=True), uint8=dict(dtype=np.uint8), unfused=dict(fuse_mask=False), zero_copy=dict(zero_copy=True),
+              host_transport=dict(host_transport=True), host_transport_uint8=dict(host_transport=True, dtype=np.uint8))[mode]
     ais = [P, W]
     env = _env(4, 2, max_steps=150, ai2s=ais, map_paths=[MAP_16], **kw)
     ref = _oracle(4, ais, MAP_16, max_steps=150)
