@@ -41,6 +41,12 @@ WORKLOADS = {
     "cfg5_bloodbath64": (MAP_64, 29, 2048, 1.0, (), False, 2000, "64x64 (4)BloodBath.scmB self-play"),
 }
 DEFAULT_WORKLOAD = "cfg2_rollout16"
+# dram__bytes_read.sum + dram__bytes_write.sum of the pass kernel, bytes per launch, from the ncu --set full captures
+# under profiles/ (same command line, same slab size); None where no capture exists
+NCU_TRAFFIC = {
+    ("cfg2_rollout16", "int32"): 40_811_008 + 2_742_958_000,   # profiles/ncu_r01_cfg2_details.csv (read + write)
+    ("cfg1_selfplay16", "int32"): 34_422_272 + 3_641_051_000,  # profiles/ncu_r01_cfg1_details.csv
+}
 
 
 def algorithmic_bytes(hw, planes, elem):
@@ -272,10 +278,13 @@ def gpu_arm(args):
             "dtype": args.dtype, "data": "synthetic (real reference maps; actions drawn on the device by the fused masked-uniform sampler)",
             "config": {"workload": args.workload, "description": wl["desc"], "map": wl["map"], "envs_per_gpu": N, "selfplay_views": nsp, "bot_envs": nbot,
                        "partial_obs": wl["partial"], "max_steps": wl["max_steps"], "prewarm_steps": args.prewarm, "l2": "outputs per step (%.2f GB) exceed the 126 MB L2; no flush needed" % (B * N / 1e9),
-                       "mean_acting_units_per_view": units_mean, "threads_per_game": L.mrts_threads_per_game(env._h), "smem_per_game": L.mrts_smem_bytes(env._h)},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                         "kernel": "mrts_pass_kernel", "bytes_per_env_step": B, "env_steps_per_launch": N, "kernel_ms": kern_ms, "peak_source": peak_src},
-            "e2e": e2e, "gpu_launches": args.steps, "clocks": clk,
+                       "mean_acting_units_per_view": units_mean, "threads_per_game": L.mrts_threads_per_game(env._h), "smem_per_game": L.mrts_smem_bytes(env._h),
+                       "staged_units_per_game": L.mrts_staged_units(env._h), "unit_capacity": L.mrts_unit_capacity(env._h),
+                       "kernels_per_step": L.mrts_launches_per_step(env._h)},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC.get((args.workload, args.dtype)),
+                         "kernel": "mrts_pass_warp_kernel" if L.mrts_threads_per_game(env._h) == 32 else "mrts_pass_kernel",
+                         "kernel_ms_note": "CUDA events around each step on the launching stream (includes the tiny launch-order / overflow kernels of bot slabs)", "bytes_per_env_step": B, "env_steps_per_launch": N, "kernel_ms": kern_ms, "peak_source": peak_src},
+            "e2e": e2e, "gpu_launches": args.steps * L.mrts_launches_per_step(env._h), "clocks": clk,
         }
         if cpu_v is not None:
             line["cpu_baseline"] = {"value": cpu_v, "unit": "env-steps/s", "cores": cores, "kind": "port",

@@ -112,6 +112,9 @@ int mrts_planes(const mrts_env* env);
 int mrts_unit_capacity(const mrts_env* env);
 int mrts_threads_per_game(const mrts_env* env);
 int mrts_smem_bytes(const mrts_env* env);
+int mrts_staged_units(const mrts_env* env);     /* units per game the warp kernel stages in shared memory */
+int mrts_launches_per_step(const mrts_env* env); /* kernels one mrts_step enqueues: the pass itself, + the launch-order kernel of
+                                                    large bot slabs, + the full-capacity overflow launch when staged < capacity */
 /* State of one game for cross-checks against the oracle: hdr5 = time, res0, res1, steps, nunits;
  * rows12 = per unit: type, player, x, y, res, hp, a_type (-1 idle), a_param, a_x, a_y, a_utype, a_time.
  * Returns the number of units (or a negative error); host pointers. */

@@ -156,6 +156,8 @@ SYMBOLS = [
     "mrts_unit_capacity",
     "mrts_threads_per_game",
     "mrts_smem_bytes",
+    "mrts_staged_units",
+    "mrts_launches_per_step",
     "mrts_export_state",
     "mrts_debug_issue",
     "mrts_debug_cycle",
@@ -184,7 +186,7 @@ def lib():
         L.mrts_get_masks.argtypes = [vp, vp, vp]
         L.mrts_step_ex.argtypes = [vp, C.POINTER(StepIOC), vp]
         L.mrts_sample_actions.argtypes = [vp, vp, C.c_uint64, vp]
-        for f in ("mrts_num_envs", "mrts_num_games", "mrts_planes", "mrts_unit_capacity", "mrts_threads_per_game", "mrts_smem_bytes"):
+        for f in ("mrts_num_envs", "mrts_num_games", "mrts_planes", "mrts_unit_capacity", "mrts_threads_per_game", "mrts_smem_bytes", "mrts_staged_units", "mrts_launches_per_step"):
             getattr(L, f).argtypes = [vp]
         L.mrts_export_state.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
         L.mrts_debug_issue.argtypes = [vp, C.c_int, vp, C.c_int, vp]

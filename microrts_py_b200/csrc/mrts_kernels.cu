@@ -377,17 +377,18 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         // Games per block: a block's shared memory and warp slots are only released when its slowest
         // game is done and game times vary widely (scripted-bot path finding), so take the smallest
         // count that still reaches the most resident games per SM.
+        e->minb = HW <= 64 ? 8 : MRTS_WARP_MIN_BLOCKS;
+        const int by_regs = 4 * e->minb;  // warps per SM the register budget of the variant allows (__launch_bounds__(128, minb))
         int best = 1, best_w = 0;
         for (int g = 1; g <= GPB_MAX; g *= 2) {
             if (g * e->smem > maxsm) break;
             int blocks = smem_sm / (g * e->smem + 1024);  // 1 KB per-block reservation
             if (blocks > max_blocks) blocks = max_blocks;
             int w = blocks * g;
-            if (w > 64) w = 64;
+            if (w > by_regs) w = by_regs;
             if (w > best_w) best_w = w, best = g;
         }
         e->gpb = cfg->threads_per_game < 0 ? -cfg->threads_per_game : best;
-        e->minb = HW <= 64 ? 8 : MRTS_WARP_MIN_BLOCKS;
         if (e->gpb > GPB_MAX) e->gpb = GPB_MAX;
         const int wbytes = e->gpb * e->smem;
         if (wbytes > 48 * 1024) {
@@ -548,6 +549,11 @@ int mrts_step_host(mrts_env* e, const void* h_actions, int action_elem_bytes, vo
     return hostio_finish(e, h_obs, h_mask, h_reward, h_done);
 }
 
+int mrts_launches_per_step(const mrts_env* e) {
+    if (!e) return MRTS_EINVAL;
+    return 1 + (e->d_order && e->threads == 32 ? 1 : 0) + (e->threads == 32 && e->P.scap < e->P.cap ? 1 : 0);
+}
+int mrts_staged_units(const mrts_env* e) { return e ? e->P.scap : MRTS_EINVAL; }
 int mrts_host_threads(const mrts_env* e) { return e && e->hio.pool ? mrts_host::pool_threads(e->hio.pool) : 0; }
 
 int mrts_num_envs(const mrts_env* e) { return e ? e->N : MRTS_EINVAL; }
