@@ -124,9 +124,53 @@ struct Sim {
     int nbits_words;
     int16_t* astar;  // bot games: A* scratch (astar_bytes)
     St* st;          // per-step mutable scalars
+    int lane, nl;    // the rules run on the game's first warp, every lane executing the same (uniform) code on the
+                     // shared state; lane / lane count (32 on the device, 1 in the host build) drive the per-unit scans
     const Sim* self; // where this view is stored for the out-of-line entry points
 
     // ------------------------------------------------------------------ small helpers
+    // ---- warp primitives of the rules phase (no-ops / identities with one lane)
+    static MRTS_HD unsigned wballot(bool p) {
+#if defined(__CUDA_ARCH__)
+        return __ballot_sync(0xFFFFFFFFu, p);
+#else
+        return p ? 1u : 0u;
+#endif
+    }
+    static MRTS_HD int wmin(int v) {
+#if defined(__CUDA_ARCH__)
+        return __reduce_min_sync(0xFFFFFFFFu, v);
+#else
+        return v;
+#endif
+    }
+    static MRTS_HD int wadd(int v) {
+#if defined(__CUDA_ARCH__)
+        return __reduce_add_sync(0xFFFFFFFFu, v);
+#else
+        return v;
+#endif
+    }
+    static MRTS_HD void wsync() {
+#if defined(__CUDA_ARCH__)
+        __syncwarp();
+#endif
+    }
+    static MRTS_HD int popc(unsigned v) {
+#if defined(__CUDA_ARCH__)
+        return __popc(v);
+#else
+        return __builtin_popcount(v);
+#endif
+    }
+    MRTS_HD unsigned lanes_below() const { return (1u << lane) - 1u; }
+    static MRTS_HD int lane_now() {
+#if defined(__CUDA_ARCH__)
+        return (int)(threadIdx.x & 31);
+#else
+        return 0;
+#endif
+    }
     MRTS_HD int nunits() const { return hdr->nunits; }
     MRTS_HD int tick() const {
 #if defined(__CUDA_ARCH__)
@@ -1653,26 +1697,32 @@ struct Sim {
 // ---- out-of-line entry points (see the declarations above Sim)
 MRTS_HDN int o_astar(const Sim* sp, int i, int targetpos, int range, int vp) {
     Sim s = *sp;
+    s.lane = Sim::lane_now();
     return s.astar_first_move(i, targetpos, range, vp);
 }
 MRTS_HDN void o_issue_safe(const Sim* sp, PAct* list, int cnt) {
     Sim s = *sp;
+    s.lane = Sim::lane_now();
     s.issue_safe(list, cnt);
 }
 MRTS_HDN void o_decode_actions(const Sim* sp, int player, int vp) {
     Sim s = *sp;
+    s.lane = Sim::lane_now();
     s.decode_actions(player, vp);
 }
 MRTS_HDN void o_make_view(const Sim* sp, int p) {
     Sim s = *sp;
+    s.lane = Sim::lane_now();
     s.make_view(p);
 }
 MRTS_HDN void o_bot_melee(const Sim* sp, int i, int player, int vp) {
     Sim s = *sp;
+    s.lane = Sim::lane_now();
     s.bot_melee(i, player, vp);
 }
 MRTS_HDN void o_fill_with_nones(const Sim* sp, PAct* list, int* cnt, int player, int duration, int vp) {
     Sim s = *sp;
+    s.lane = Sim::lane_now();
     int c = *cnt;
     s.fill_with_nones(list, c, player, duration, vp);
     *cnt = c;

@@ -114,6 +114,8 @@ __global__ void mrts_debug_kernel(const EnvParams P, const DebugArgs A) {
     Sim s;
     bind_sim(s, P, L, mem, A.game);
     s.partial = 0;
+    s.nl = 32;
+    s.lane = tid & 31;
     const MapTpl tpl = P.maps[P.game_map[A.game]];
     uint8_t* gblob = P.games + (size_t)A.game * P.game_stride;
     copy16<Q16>(mem + L.blob, gblob, 32 + P.cap * 32, tid, nth);
@@ -124,12 +126,15 @@ __global__ void mrts_debug_kernel(const EnvParams P, const DebugArgs A) {
     if (tid == 0) {
         *(Sim*)(mem + L.sim) = s;
         St z;
-        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.timing_on = z.rows_ready = 0;
+        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.timing_on = z.rows_ready = z.nidle = 0;
         z.winner = -1;
         for (int k = 0; k < 8; k++) z.tp[k] = 0;
         for (int p = 0; p < 2; p++)
             for (int k = 0; k < 6; k++) z.rew[p][k] = 0;
         *s.st = z;
+    }
+    __syncthreads();
+    if (tid < 32) {  // the rules run on one warp, every lane executing the same code (see Sim::lane)
         if (A.op == 0) {
             int cnt = 0;
             for (int k = 0; k < A.n && cnt < P.cap; k++) {

@@ -113,6 +113,8 @@ MRTS_HD void bind_sim(Sim& s, const EnvParams& P, const Layout& L, uint8_t* mem,
     s.bitsB = s.bitsA + L.nbits_words;
     s.bitsC = s.bitsB + L.nbits_words;
     s.astar = (int16_t*)(mem + L.astar);
+    s.lane = 0;
+    s.nl = 1;
     s.st = (St*)(mem + L.misc);
     s.self = (const Sim*)(mem + L.sim);
 }
@@ -171,6 +173,9 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     const Layout L = layout_of(P);
     Sim s;
     bind_sim(s, P, L, mem, g);
+    s.nl = nth < 32 ? nth : 32;  // lanes of the rules phase: the group's first warp
+    s.lane = tid & 31;
+    const bool rules_lane = tid < s.nl;
     uint32_t* words = (uint32_t*)(mem + L.words);
     uint32_t* umask = (uint32_t*)(mem + L.umask);
 
@@ -251,12 +256,14 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         s.prefetch_actions(P.pact ? nullptr : P.actions + (size_t)env0 * P.HW * 7, P.pact ? P.pact + (size_t)env0 * P.HW : nullptr, tid, nth);
     sync();
 
-    // ---------------- rules (leader)
-    if (tid == 0) {
+    // ---------------- rules (first warp, uniform)
+    if (rules_lane) {
         if (P.mode == MODE_STEP) {
             const long long t_rules = P.timing ? cycles_now() : 0;
-            s.st->reset = s.step_game() ? 1 : 0;
-            if (P.timing) {
+            const int r = s.step_game() ? 1 : 0;
+            Sim::wsync();
+            s.st->reset = r;
+            if (P.timing && tid == 0) {
                 P.timing[12 * g] = cycles_now() - t_rules;
                 for (int k = 0; k < 8; k++) P.timing[12 * g + 2 + k] = s.st->tp[k];
             }
@@ -280,7 +287,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         scatter_grid();
         sync();
         if (P.partial) {
-            if (tid == 0)
+            if (rules_lane)
                 for (int v = 0; v < nviews; v++) o_make_view(s.self, v);
             sync();
         }
@@ -303,7 +310,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         }
     }
     if (P.mode == MODE_STEP && !reset) {
-        if (tid == 0) s.compact();
+        if (rules_lane) s.compact();
         sync();
     }
     if (P.mask || P.pmask || P.next_actions) unit_masks(s, umask, tid, nth);
