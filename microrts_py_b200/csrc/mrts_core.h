@@ -156,6 +156,13 @@ struct Sim {
         __syncwarp();
 #endif
     }
+    static MRTS_HD int ffs32(unsigned v) {  // 1-based index of the lowest set bit, 0 if none
+#if defined(__CUDA_ARCH__)
+        return __ffs((int)v);
+#else
+        return __builtin_ffs((int)v);
+#endif
+    }
     static MRTS_HD int popc(unsigned v) {
 #if defined(__CUDA_ARCH__)
         return __popc(v);
@@ -217,9 +224,21 @@ struct Sim {
         }
         return pos;
     }
-    MRTS_HD void bits_clear(uint32_t* b) const {
+    MRTS_HD void bits_clear(uint32_t* b) const {  // all lanes together
+        wsync();
 #pragma unroll 1
-        for (int i = 0; i < nbits_words; i++) b[i] = 0;
+        for (int i = lane; i < nbits_words; i += nl) b[i] = 0;
+        wsync();
+    }
+    // set from a lane-parallel scan (lanes hold different positions)
+    MRTS_HD void bit_set_par(uint32_t* b, int pos) const {
+        int k = pos + W;
+        if (k < 0 || k >= nbits_words * 32) return;
+#if defined(__CUDA_ARCH__)
+        atomicOr(&b[k >> 5], 1u << (k & 31));
+#else
+        b[k >> 5] |= 1u << (k & 31);
+#endif
     }
     MRTS_HD bool bit_get(const uint32_t* b, int pos) const {
         int k = pos + W;
@@ -355,19 +374,20 @@ struct Sim {
         int c0 = 0, c1 = 0;  // scalars: a dynamically indexed cost[] would live in local memory
         const int n = nunits();
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
+        for (int i = lane; i < n; i += nl) {  // one unit per lane
             const Unit& un = u[i];
             if (un.a_type != T_MOVE && un.a_type != T_PRODUCE) continue;
             if (!inview(i, vp)) continue;
-            bit_set(bits, usage_pos(un, un.a_type, un.a_param));
+            bit_set_par(bits, usage_pos(un, un.a_type, un.a_param));
             if (un.a_type == T_PRODUCE) {
                 const int c = ut_cost(un.a_utype);
                 if (un.player == 0) c0 += c;
                 else c1 += c;
             }
         }
-        cost[0] = c0;
-        cost[1] = c1;
+        cost[0] = wadd(c0);
+        cost[1] = wadd(c1);
+        wsync();
     }
     // ResourceUsage.consistentWith(other) for a single-action `other` against an accumulated base
     // (ResourceUsage.java:31-50)
@@ -431,20 +451,40 @@ struct Sim {
         }
         int cnt = 0;
         const int n = nunits();
-        // own idle units sorted by cell index (insertion sort over the handful of candidates)
+        // own idle units in ascending cell order: one unit per lane marks its cell in a bitmap (bitsC is
+        // free here), then the set bits are walked in order
+        bits_clear(bitsC);
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
+        for (int i = lane; i < n; i += nl) {
             const Unit& un = u[i];
             if (un.player != player || un.a_type >= 0 || !inview(i, vp)) continue;
-            int pos = un.x + un.y * W;
-            int k = cnt++;
-#pragma unroll 1
-            while (k > 0 && (u[pa[k - 1].unit].x + u[pa[k - 1].unit].y * W) > pos) {
-                pa[k].unit = pa[k - 1].unit;
-                k--;
-            }
-            pa[k].unit = (uint16_t)i;
+            const int pos = un.x + un.y * W;
+#if defined(__CUDA_ARCH__)
+            atomicOr(&bitsC[pos >> 5], 1u << (pos & 31));
+#else
+            bitsC[pos >> 5] |= 1u << (pos & 31);
+#endif
         }
+        wsync();
+        const int nw = (HW + 31) >> 5;
+#pragma unroll 1
+        for (int base = 0; base < nw; base += nl) {
+            const int wi = base + lane;
+            unsigned nz = wballot(wi < nw && bitsC[wi] != 0);
+#pragma unroll 1
+            while (nz) {
+                const int k = ffs32(nz) - 1;
+                nz &= nz - 1;
+                uint32_t m = bitsC[base + k];
+#pragma unroll 1
+                while (m) {
+                    const int b = ffs32(m) - 1;
+                    m &= m - 1;
+                    pa[cnt++].unit = grid[32 * (base + k) + b];
+                }
+            }
+        }
+        wsync();
         int kept = 0;
         const int have = player == 0 ? hdr->res[0] : hdr->res[1];
         int used = player == 0 ? cost0 : cost1;
@@ -488,25 +528,35 @@ struct Sim {
     MRTS_HD void fill_with_nones(PAct* list, int& cnt, int player, int duration, int vp) {
         const int n = nunits();
         const int have = cnt;
+        wsync();
 #pragma unroll 1
-        for (int k = 0; k < have; k++) u[list[k].unit].flags |= UF_LISTED;
+        for (int k = lane; k < have; k += nl) u[list[k].unit].flags |= UF_LISTED;  // distinct units: no two lanes share a record
+        wsync();
+        int total = have;
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
-            Unit& un = u[i];
-            if (un.flags & UF_LISTED) {
-                un.flags &= (uint8_t)~UF_LISTED;
-                continue;
+        for (int base = 0; base < n; base += nl) {  // one unit per lane; the ballot keeps unit order
+            const int i = base + lane;
+            bool take = false;
+            if (i < n) {
+                Unit& un = u[i];
+                if (un.flags & UF_LISTED) un.flags &= (uint8_t)~UF_LISTED;
+                else take = un.player == player && un.a_type < 0 && inview(i, vp);
             }
-            if (un.player != player || un.a_type >= 0 || !inview(i, vp)) continue;
-            PAct e;
-            e.unit = (uint16_t)i;
-            e.type = T_NONE;
-            e.param = (int16_t)none_param(duration);
-            e.utype = -1;
-            e.x = e.y = 0;
-            e.pad = 0;
-            list[cnt++] = e;
+            const unsigned m = wballot(take);
+            if (take) {
+                PAct e;
+                e.unit = (uint16_t)i;
+                e.type = T_NONE;
+                e.param = (int16_t)none_param(duration);
+                e.utype = -1;
+                e.x = e.y = 0;
+                e.pad = 0;
+                list[total + popc(m & lanes_below())] = e;
+            }
+            total += popc(m);
         }
+        wsync();
+        cnt = total;
     }
 
     // ------------------------------------------------------------------ issueSafe + issue
@@ -530,16 +580,18 @@ struct Sim {
     }
 
     MRTS_HD void issue_safe(PAct* list, int cnt) {
+        wsync();
         const int time = hdr->time;
         // target cells of every pending MOVE / PRODUCE (a superset is fine: it only gates the exact scan)
         bits_clear(bitsB);
         {
             const int n = nunits();
 #pragma unroll 1
-            for (int j = 0; j < n; j++) {
+            for (int j = lane; j < n; j += nl) {  // one unit per lane
                 const Unit& ou = u[j];
-                if (ou.a_type == T_MOVE || ou.a_type == T_PRODUCE) bit_set(bitsB, usage_pos(ou, ou.a_type, ou.a_param));
+                if (ou.a_type == T_MOVE || ou.a_type == T_PRODUCE) bit_set_par(bitsB, usage_pos(ou, ou.a_type, ou.a_param));
             }
+            wsync();
         }
 #pragma unroll 1
         for (int k = 0; k < cnt; k++) {
@@ -715,29 +767,45 @@ struct Sim {
 
     // GameState.cycle.  Dead units stay in the array (flagged) until compact().
     MRTS_HD void cycle() {
+        wsync();
         hdr->time++;
         const int time = hdr->time;
         const int n = nunits();  // units born this cycle have no assignment
-        // ready non-NONE assignments, sorted by issue order; NONEs just vanish (no effect)
+        // ready non-NONE assignments, sorted by issue order; NONEs just vanish (no effect).
+        // One unit per lane finds the ready ones (ballot keeps unit order), then the few are sorted.
         int nr = 0;
         uint16_t* ready = (uint16_t*)pa;  // pa is free again
+        wsync();
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
-            Unit& un = u[i];
-            if (un.a_type < 0) continue;
-            int e = eta(un.type, un.a_type, un.a_param, un.a_utype >= 0 ? un.a_utype : 0);
-            if (e + un.a_time > time) continue;
-            if (un.a_type == T_NONE) {
-                un.a_type = -1;
-                continue;
+        for (int base = 0; base < n; base += nl) {
+            const int i = base + lane;
+            bool rdy = false;
+            if (i < n) {
+                Unit& un = u[i];
+                if (un.a_type >= 0) {
+                    const int e = eta(un.type, un.a_type, un.a_param, un.a_utype >= 0 ? un.a_utype : 0);
+                    if (e + un.a_time <= time) {
+                        if (un.a_type == T_NONE) un.a_type = -1;
+                        else rdy = true;
+                    }
+                }
             }
-            int k = nr++;
+            const unsigned m = wballot(rdy);
+            if (rdy) ready[nr + popc(m & lanes_below())] = (uint16_t)i;
+            nr += popc(m);
+        }
+        wsync();
 #pragma unroll 1
-            while (k > 0 && u[ready[k - 1]].a_seq > un.a_seq) {
+        for (int a = 1; a < nr; a++) {  // insertion sort by issue order (uniform)
+            const uint16_t v = ready[a];
+            const uint32_t sv = u[v].a_seq;
+            int k = a;
+#pragma unroll 1
+            while (k > 0 && u[ready[k - 1]].a_seq > sv) {
                 ready[k] = ready[k - 1];
                 k--;
             }
-            ready[k] = (uint16_t)i;
+            ready[k] = v;
         }
 #pragma unroll 1
         for (int k = 0; k < nr; k++) {
@@ -753,29 +821,41 @@ struct Sim {
     // stable compaction after cycle (PhysicalGameState.removeUnit keeps relative order) + grid fix-up
     MRTS_HD void compact() {
         const int n = nunits();
+        wsync();
         int k = 0;
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
-            if (u[i].flags & UF_DEAD) continue;
-            if (k != i) {
-                u[k] = u[i];
-                grid[u[k].x + u[k].y * W] = (uint16_t)k;
+        for (int base = 0; base < n; base += nl) {  // one unit per lane; a chunk's records are read before any is moved
+            const int i = base + lane;
+            const bool live = i < n && !(u[i].flags & UF_DEAD);
+            const unsigned m = wballot(live);
+            const int dst = k + popc(m & lanes_below());
+            Unit rec;
+            if (live) rec = u[i];
+            wsync();
+            if (live && dst != i) {
+                u[dst] = rec;
+                grid[rec.x + rec.y * W] = (uint16_t)dst;
             }
-            k++;
+            k += popc(m);
+            wsync();
         }
         hdr->nunits = k;
+        wsync();
     }
 
     // PhysicalGameState.gameover / st->winner (PhysicalGameState.java:319-372) over live units
     MRTS_HD void eval_gameover() {
         int c0 = 0, c1 = 0;
         const int n = nunits();
+        wsync();
 #pragma unroll 1
-        for (int i = 0; i < n; i++)
+        for (int i = lane; i < n; i += nl)  // one unit per lane
             if (alive(i)) {
                 c0 += u[i].player == 0;
                 c1 += u[i].player == 1;
             }
+        c0 = wadd(c0);
+        c1 = wadd(c1);
         if (c0 + c1 == 0) {
             st->gameover = 1;
             st->winner = -1;
@@ -1400,6 +1480,7 @@ struct Sim {
 
     // AbstractionLayerAI.translateActions, AbstractionLayerAI.java:58-113 -> pa2
     MRTS_HD void translate_actions(int player, int vp, bool enemy_seen) {
+        wsync();
         int costB[2];
         pending_usage(bitsB, costB, vp);
         bits_clear(bitsC);
@@ -1557,6 +1638,7 @@ struct Sim {
     // such workers are skipped and translate_actions keeps their entry -- provided an enemy is in
     // view at all (otherwise the reference puts nothing and the stale entry is checked as usual).
     MRTS_HD void worker_rush(int player, int vp) {
+        wsync();
         const int t_wr = tick();
         const int n = nunits();
         const int pres = hdr->res[player];
@@ -1647,6 +1729,7 @@ struct Sim {
     // array still contains units killed this cycle (flagged) so that stale partially observable
     // views can be encoded; the caller then runs compact() or reloads the map template.
     MRTS_HD bool step_game() {
+        wsync();
         for (int p = 0; p < 2; p++)
             for (int k = 0; k < 6; k++) st->rew[p][k] = 0;
         if (ai == AI_NONE) {
