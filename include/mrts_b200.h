@@ -103,6 +103,12 @@ int mrts_sample_actions(mrts_env* env, int32_t* next_actions, uint64_t seed, voi
  * the library owns its own stream and pinned staging buffers for these calls. */
 int mrts_reset_host(mrts_env* env, void* obs, void* mask);
 int mrts_step_host(mrts_env* env, const void* actions, int action_elem_bytes, void* obs, void* mask, double* reward, uint8_t* done);
+/* The transport codec alone, host arrays in and out (no device needed): observation words (n_env, hw) ->
+ * one-hot (n_env, hw, planes); mask words (n_env, hw, 3) -> (n_env, hw, 78); action grid (n_env, hw, 7) ->
+ * 16-bit rows at the cells whose mask word 0 has bit 0 set. */
+int mrts_host_expand_obs(const uint32_t* words, int64_t n_env, int hw, int planes, int elem_bytes, void* out);
+int mrts_host_expand_mask(const uint32_t* mask_words, int64_t n_env, int hw, int elem_bytes, void* out);
+int mrts_host_pack_actions(const void* actions, int action_elem_bytes, const uint32_t* mask_words, int64_t n_env, int hw, uint16_t* out);
 int mrts_host_threads(const mrts_env* env); /* worker threads of the widening pool (0 before the first host call) */
 
 /* Introspection (synchronises the stream). */

@@ -150,6 +150,9 @@ SYMBOLS = [
     "mrts_reset_host",
     "mrts_step_host",
     "mrts_host_threads",
+    "mrts_host_expand_obs",
+    "mrts_host_expand_mask",
+    "mrts_host_pack_actions",
     "mrts_num_envs",
     "mrts_num_games",
     "mrts_planes",
@@ -195,6 +198,9 @@ def lib():
         L.mrts_reset_host.argtypes = [vp, vp, vp]
         L.mrts_step_host.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp]
         L.mrts_host_threads.argtypes = [vp]
+        L.mrts_host_expand_obs.argtypes = [vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]
+        L.mrts_host_expand_mask.argtypes = [vp, C.c_int64, C.c_int, C.c_int, vp]
+        L.mrts_host_pack_actions.argtypes = [vp, C.c_int, vp, C.c_int64, C.c_int, vp]
         L.mrts_last_error.restype = C.c_char_p
         L.mrts_version.restype = C.c_char_p
         _lib = L

@@ -559,6 +559,28 @@ int mrts_launches_per_step(const mrts_env* e) {
     return 1 + (e->d_order && e->threads == 32 ? 1 : 0) + (e->threads == 32 && e->P.scap < e->P.cap ? 1 : 0);
 }
 int mrts_staged_units(const mrts_env* e) { return e ? e->P.scap : MRTS_EINVAL; }
+// the transport codec on its own (host arrays in, host arrays out): lets the CPU test-suite check it without a GPU
+int mrts_host_expand_obs(const uint32_t* words, int64_t n_env, int hw, int planes, int elem_bytes, void* out) {
+    if (!words || !out || (elem_bytes != 4 && elem_bytes != 1) || planes < 1 || planes > 31) return fail(MRTS_EINVAL, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    mrts_host::expand_obs(p, words, (size_t)n_env, hw, planes, elem_bytes, out);
+    mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
+int mrts_host_expand_mask(const uint32_t* mask_words, int64_t n_env, int hw, int elem_bytes, void* out) {
+    if (!mask_words || !out || (elem_bytes != 4 && elem_bytes != 1)) return fail(MRTS_EINVAL, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    mrts_host::expand_mask(p, mask_words, (size_t)n_env, hw, elem_bytes, out);
+    mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
+int mrts_host_pack_actions(const void* actions, int action_elem_bytes, const uint32_t* mask_words, int64_t n_env, int hw, uint16_t* out) {
+    if (!actions || !mask_words || !out || (action_elem_bytes != 4 && action_elem_bytes != 8)) return fail(MRTS_EINVAL, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    mrts_host::pack_actions(p, actions, action_elem_bytes, mask_words, (size_t)n_env, hw, out);
+    mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
 int mrts_host_threads(const mrts_env* e) { return e && e->hio.pool ? mrts_host::pool_threads(e->hio.pool) : 0; }
 
 int mrts_num_envs(const mrts_env* e) { return e ? e->N : MRTS_EINVAL; }

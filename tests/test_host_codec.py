@@ -1,0 +1,79 @@
+"""The PCIe transport codec of the host-buffer entry points (csrc/mrts_host.cpp), checked on CPU:
+bit words -> one-hot arrays exactly as NumPy would unpack them, and action rows packed the way the
+device decodes them (Sim::pack_action; UnitAction.fromVectorAction, J/rts/UnitAction.java:681-715).
+The library is only loaded, no device call is made."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from microrts_py_b200 import _capi
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+@pytest.mark.parametrize("hw,planes,dtype", [(64, 29, np.int32), (256, 29, np.int32), (100, 31, np.int32), (81, 29, np.int32), (256, 31, np.uint8), (1, 29, np.int32)])
+def test_observation_words_expand_to_one_hot(hw, planes, dtype):
+    L = _capi.lib()
+    rng = np.random.default_rng(hw * planes)
+    n = 37
+    words = rng.integers(0, 2 ** planes, size=(n, hw), dtype=np.uint32)
+    want = ((words[:, :, None] >> np.arange(planes, dtype=np.uint32)) & 1).astype(dtype)
+    for off in (0, 1):  # aligned and unaligned destination
+        buf = np.zeros(n * hw * planes + 64, dtype)
+        out = buf[off : off + n * hw * planes].reshape(n, hw, planes)
+        _capi.check(L.mrts_host_expand_obs(_p(words), n, hw, planes, np.dtype(dtype).itemsize, _p(out)))
+        np.testing.assert_array_equal(out, want)
+        assert not buf[off + n * hw * planes :].any() and not buf[:off].any()
+
+
+@pytest.mark.parametrize("dtype", [np.int32, np.uint8])
+def test_mask_words_expand_to_78(dtype):
+    L = _capi.lib()
+    rng = np.random.default_rng(5)
+    n, hw = 19, 144
+    pm = np.zeros((n, hw, 3), np.uint32)
+    cells = rng.random((n, hw)) < 0.05
+    pm[cells] = rng.integers(0, 2 ** 32, size=(int(cells.sum()), 3), dtype=np.uint64).astype(np.uint32)
+    pm[:, :, 2] &= (1 << 14) - 1  # 78 bits
+    bits = np.concatenate([(pm[:, :, k : k + 1] >> np.arange(32, dtype=np.uint32)) & 1 for k in range(3)], axis=2)[:, :, :78]
+    out = np.full((n, hw, 78), 7, dtype)
+    _capi.check(L.mrts_host_expand_mask(_p(pm), n, hw, np.dtype(dtype).itemsize, _p(out)))
+    np.testing.assert_array_equal(out, bits.astype(dtype))
+
+
+def _pack_ref(a):
+    t = int(a[0])
+    if t < 1 or t > 5:
+        return 0
+    if t == 4:
+        if not 0 <= a[5] < 7:
+            return 0
+        bad = not 0 <= a[4] <= 3
+        pay = (0 if bad else int(a[4])) | (int(a[5]) << 2)
+    elif t == 5:
+        bad, pay = False, (63 if not 0 <= a[6] <= 48 else int(a[6]))
+    else:
+        bad = not 0 <= a[t] <= 3
+        pay = 0 if bad else int(a[t])
+    return t | (pay << 3) | (int(bad) << 9)
+
+
+@pytest.mark.parametrize("dtype", [np.int32, np.int64])
+def test_action_rows_pack_only_at_source_cells(dtype):
+    L = _capi.lib()
+    rng = np.random.default_rng(11)
+    n, hw = 23, 64
+    a = rng.integers(-2, 9, size=(n, hw, 7)).astype(dtype)
+    a[:, :, 6] = rng.integers(-3, 60, size=(n, hw))
+    pm = np.zeros((n, hw, 3), np.uint32)
+    src = rng.random((n, hw)) < 0.3
+    pm[src, 0] = 1 | (rng.integers(0, 2 ** 20, size=int(src.sum())).astype(np.uint32) << 1)
+    out = np.full((n, hw), 0xFFFF, np.uint16)
+    _capi.check(L.mrts_host_pack_actions(_p(a), np.dtype(dtype).itemsize, _p(pm), n, hw, _p(out)))
+    want = np.zeros((n, hw), np.uint16)
+    for e, c in zip(*np.nonzero(src)):
+        want[e, c] = _pack_ref(a[e, c])
+    np.testing.assert_array_equal(out, want)
