@@ -896,12 +896,21 @@ struct Sim {
 
     // ================================================================== scripted opponents
     // AbstractionLayerAI table helpers (J/ai/abstraction/AbstractionLayerAI.java:36,115-141)
-    MRTS_HD int aa_find(uint16_t uid) const {
+    MRTS_HD int aa_find(uint16_t uid) const {  // one table entry per lane
+        const int na = hdr->n_aa;
+        wsync();
 #pragma unroll 1
-        for (int k = 0; k < hdr->n_aa; k++)
-            if (aa[k].unit == uid) return k;
+        for (int base = 0; base < na; base += nl) {
+            const int k = base + lane;
+            const unsigned m = wballot(k < na && aa[k].unit == uid);
+            if (m) return base + ffs32(m) - 1;
+        }
         return -1;
     }
+    // arg-min over the units of a warp-parallel scan: key = (value << 16) | unit index, so that among
+    // equal values the lowest index wins -- what a strict `<` scan in unit order keeps.  -1 if no candidate.
+    static MRTS_HD int argmin_key(int value, int index) { return (value << 16) | index; }
+    enum { NO_KEY = 0x7FFFFFFF };
     MRTS_HD void aa_put(const AbstractAct& r, int i) {  // LinkedHashMap.put: re-put keeps the slot; i = the unit's index
         int k = aa_find(r.unit);
         if (k < 0) {
@@ -1020,11 +1029,14 @@ struct Sim {
     // F for this bot call, on the first search (translate_actions keeps it current afterwards)
     MRTS_HD void rows_prepare(int vp) const {
         if (st->rows_ready) return;
-        if (partial) flood_base_rows(vp, 0, 1);
+        wsync();
+        if (partial) flood_base_rows(vp, lane, nl);
+        wsync();
         const uint64_t* F0 = rows_F0();
         uint64_t* F = rows_F();
 #pragma unroll 1
-        for (int y = 0; y < H; y++) F[y] = F0[y] & ~bits_row(bitsB, y) & ~bits_row(bitsC, y);
+        for (int y = lane; y < H; y += nl) F[y] = F0[y] & ~bits_row(bitsB, y) & ~bits_row(bitsC, y);  // one row per lane
+        wsync();
         st->rows_ready = 1;
     }
     // a desire was accepted (its target is now in bitsC): later searches of this call may not enter it
@@ -1121,8 +1133,10 @@ struct Sim {
         }
         MRTS_STAT(searches++);
         st->tp[6]++;
+        wsync();
 #pragma unroll 1
-        for (int y = 0; y < H; y++) V[y] = 0;
+        for (int y = lane; y < H; y += nl) V[y] = 0;
+        wsync();
         const int startPk = (sy << ws) | sx;
         const int h0 = iabs(sx - tx) + iabs(sy - ty);
         V[sy] = 1ull << sx;
@@ -1180,8 +1194,10 @@ struct Sim {
                 nopen++;
             }
         }
+        wsync();
 #pragma unroll 1
-        for (int f = flo; f <= fmax; f++) b.head[f] = -1;  // leave the stacks empty for the next search
+        for (int f = flo + lane; f <= fmax; f += nl) b.head[f] = -1;  // leave the stacks empty for the next search
+        wsync();
         if (!found) return -1;
         int last = pk, parent = b.parent[pk];
 #pragma unroll 1
@@ -1345,23 +1361,21 @@ struct Sim {
 
     // Train.score, J/ai/abstraction/Train.java:98-127
     MRTS_HD int train_score(int x, int y, int ut, int player, int vp) const {
-        int distance = 0;
-        bool first = true;
         const int n = nunits();
         const bool harv = ut_can_harvest(ut);
+        int best = NO_KEY;
+        wsync();
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
+        for (int i = lane; i < n; i += nl) {  // one unit per lane
             if (!inview(i, vp)) continue;
             const Unit& o = u[i];
-            bool cand = harv ? ut_is_resource(o.type) : (o.player >= 0 && o.player != player);
+            const bool cand = harv ? ut_is_resource(o.type) : (o.player >= 0 && o.player != player);
             if (!cand) continue;
-            int d = iabs(o.x - x) + iabs(o.y - y);
-            if (first || d < distance) {
-                distance = d;
-                first = false;
-            }
+            const int d = iabs(o.x - x) + iabs(o.y - y);
+            if (d < best) best = d;
         }
-        return -distance;
+        best = wmin(best);
+        return best == NO_KEY ? 0 : -best;
     }
 
     // AbstractAction.execute: true + primitive action in `out`, or false (null)
@@ -1555,19 +1569,20 @@ struct Sim {
     }
 
     MRTS_HD void bot_melee(int i, int player, int vp) {  // WorkerRush.meleeUnitBehavior, WorkerRush.java:106-122
-        int closest = -1, cd = 0;
         const int n = nunits();
+        const int ux = u[i].x, uy = u[i].y;
+        int best = NO_KEY;
+        wsync();
 #pragma unroll 1
-        for (int j = 0; j < n; j++) {
+        for (int j = lane; j < n; j += nl) {  // one unit per lane
             if (!inview(j, vp)) continue;
             const Unit& o = u[j];
             if (o.player < 0 || o.player == player) continue;
-            int d = iabs(o.x - u[i].x) + iabs(o.y - u[i].y);
-            if (closest < 0 || d < cd) {
-                closest = j;
-                cd = d;
-            }
+            const int key = argmin_key(iabs(o.x - ux) + iabs(o.y - uy), j);
+            if (key < best) best = key;
         }
+        best = wmin(best);
+        const int closest = best == NO_KEY ? -1 : (best & 0xFFFF);
         if (closest >= 0) {
             AbstractAct r;
             r.unit = u[i].uid;
@@ -1591,27 +1606,26 @@ struct Sim {
     }
     // WorkerRush.workersBehavior tail, WorkerRush.java:148-197: true = the worker stays free
     MRTS_HD bool bot_harvest(int w, int player, int vp) {
-        int cres = -1, cbase = -1, cd = 0;
         const int n = nunits();
+        const int wx = u[w].x, wy = u[w].y;
+        int kres = NO_KEY, kbase = NO_KEY;
+        wsync();
 #pragma unroll 1
-        for (int j = 0; j < n; j++) {
-            if (!inview(j, vp) || !ut_is_resource(u[j].type)) continue;
-            int d = iabs(u[j].x - u[w].x) + iabs(u[j].y - u[w].y);
-            if (cres < 0 || d < cd) {
-                cres = j;
-                cd = d;
+        for (int j = lane; j < n; j += nl) {  // one unit per lane: nearest resource and nearest own stockpile
+            if (!inview(j, vp)) continue;
+            const int d = iabs(u[j].x - wx) + iabs(u[j].y - wy);
+            if (ut_is_resource(u[j].type)) {
+                const int key = argmin_key(d, j);
+                if (key < kres) kres = key;
+            }
+            if (ut_is_stockpile(u[j].type) && u[j].player == player) {
+                const int key = argmin_key(d, j);
+                if (key < kbase) kbase = key;
             }
         }
-        cd = 0;
-#pragma unroll 1
-        for (int j = 0; j < n; j++) {
-            if (!inview(j, vp) || !ut_is_stockpile(u[j].type) || u[j].player != player) continue;
-            int d = iabs(u[j].x - u[w].x) + iabs(u[j].y - u[w].y);
-            if (cbase < 0 || d < cd) {
-                cbase = j;
-                cd = d;
-            }
-        }
+        kres = wmin(kres);
+        kbase = wmin(kbase);
+        const int cres = kres == NO_KEY ? -1 : (kres & 0xFFFF), cbase = kbase == NO_KEY ? -1 : (kbase & 0xFFFF);
         const int k = aa_find(u[w].uid);
         const bool isharv = k >= 0 && aa[k].kind == AA_HARVEST;
         if (u[w].res > 0) {
@@ -1642,41 +1656,74 @@ struct Sim {
         const int t_wr = tick();
         const int n = nunits();
         const int pres = hdr->res[player];
-        // one pass: census (:124-137) + is any enemy in view
-        int nbases = 0, nworkers = 0, w0 = -1, w1 = -1;
+        // census (:124-137) + is any enemy in view + which units need a put this frame: one unit per lane
+        int nbases = 0, nworkers = 0, kw0 = NO_KEY, kw1 = NO_KEY;
         bool enemy_seen = false;
+        wsync();
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
-            const Unit& un = u[i];
-            if (un.player == player) {
-                if (un.type == UT_BASE) nbases++;
-                if (ut_can_harvest(un.type)) {
-                    if (nworkers == 0) w0 = i;
-                    else if (nworkers == 1) w1 = i;
-                    nworkers++;
+        for (int base = 0; base < n; base += nl) {
+            const int i = base + lane;
+            bool is_base = false, is_worker = false, is_enemy = false;
+            if (i < n) {
+                const Unit& un = u[i];
+                if (un.player == player) {
+                    is_base = un.type == UT_BASE;
+                    is_worker = ut_can_harvest(un.type);
+                } else {
+                    is_enemy = un.player >= 0 && inview(i, vp);
                 }
-            } else if (un.player >= 0 && inview(i, vp)) {
-                enemy_seen = true;
             }
+            const unsigned mw = wballot(is_worker);
+            nbases += popc(wballot(is_base));
+            enemy_seen = enemy_seen || wballot(is_enemy) != 0;
+            if (mw) {  // first and second worker in unit order
+                const int f = base + ffs32(mw) - 1;
+                if (kw0 == NO_KEY) {
+                    kw0 = f;
+                    const unsigned rest = mw & (mw - 1);
+                    if (rest) kw1 = base + ffs32(rest) - 1;
+                } else if (kw1 == NO_KEY) {
+                    kw1 = f;
+                }
+            }
+            nworkers += popc(mw);
         }
+        const int w0 = kw0 == NO_KEY ? -1 : kw0, w1 = kw1 == NO_KEY ? -1 : kw1;
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
-            const Unit& un = u[i];
-            if (un.type == UT_BASE && un.player == player && un.a_type < 0 && pres >= ut_cost(UT_WORKER)) {
+        for (int base = 0; base < n; base += nl) {  // idle bases train (:102-104), idle melee units attack (:106-122)
+            const int i = base + lane;
+            bool train = false, melee = false;
+            if (i < n) {
+                const Unit& un = u[i];
+                train = un.type == UT_BASE && un.player == player && un.a_type < 0 && pres >= ut_cost(UT_WORKER);
+                melee = ut_can_attack(un.type) && !ut_can_harvest(un.type) && un.player == player && un.a_type < 0;
+            }
+            unsigned mt = wballot(train);
+#pragma unroll 1
+            while (mt) {
+                const int j = base + ffs32(mt) - 1;
+                mt &= mt - 1;
                 AbstractAct r;
-                r.unit = un.uid;
+                r.unit = u[j].uid;
                 r.kind = AA_TRAIN;
                 r.utype = UT_WORKER;
                 r.x = r.y = 0;
                 r.target = 0;
                 r.base = NO_UID;
-                aa_put(r, i);
+                aa_put(r, j);
             }
+            wsync();
         }
 #pragma unroll 1
-        for (int i = 0; i < n; i++) {
-            const Unit& un = u[i];
-            if (ut_can_attack(un.type) && !ut_can_harvest(un.type) && un.player == player && un.a_type < 0) o_bot_melee(self, i, player, vp);
+        for (int base = 0; base < n; base += nl) {
+            const int i = base + lane;
+            unsigned mm = wballot(i < n && ut_can_attack(u[i].type) && !ut_can_harvest(u[i].type) && u[i].player == player && u[i].a_type < 0);
+#pragma unroll 1
+            while (mm) {
+                const int j = base + ffs32(mm) - 1;
+                mm &= mm - 1;
+                o_bot_melee(self, j, player, vp);
+            }
         }
         // workersBehavior, WorkerRush.java:124-204
         if (nworkers > 0) {
@@ -1701,12 +1748,21 @@ struct Sim {
             bool hfree = false;
             if (harvester >= 0) hfree = bot_harvest(harvester, player, vp);
 #pragma unroll 1
-            for (int i = 0; i < n; i++) {
-                const Unit& un = u[i];
-                if (un.player != player || !ut_can_harvest(un.type)) continue;
-                if (i == builder || i == harvester) continue;
-                if (enemy_seen && un.a_type >= 0 && (un.flags & UF_AA_ATTACK)) continue;  // unobservable re-put, see above
-                o_bot_melee(self, i, player, vp);
+            for (int base = 0; base < n; base += nl) {  // one unit per lane picks the workers that need a put, in unit order
+                const int i = base + lane;
+                bool need = false;
+                if (i < n) {
+                    const Unit& un = u[i];
+                    need = un.player == player && ut_can_harvest(un.type) && i != builder && i != harvester &&
+                           !(enemy_seen && un.a_type >= 0 && (un.flags & UF_AA_ATTACK));  // unobservable re-put, see above
+                }
+                unsigned mn = wballot(need);
+#pragma unroll 1
+                while (mn) {
+                    const int j = base + ffs32(mn) - 1;
+                    mn &= mn - 1;
+                    o_bot_melee(self, j, player, vp);
+                }
             }
             if (hfree) o_bot_melee(self, harvester, player, vp);
         }
