@@ -44,8 +44,8 @@ DEFAULT_WORKLOAD = "cfg2_rollout16"
 # dram__bytes_read.sum + dram__bytes_write.sum of the pass kernel, bytes per launch, from the ncu --set full captures
 # under profiles/ (same command line, same slab size); None where no capture exists
 NCU_TRAFFIC = {
-    ("cfg2_rollout16", "int32"): 40_811_008 + 2_742_958_000,   # profiles/ncu_r01_cfg2_details.csv (read + write)
-    ("cfg1_selfplay16", "int32"): 34_422_272 + 3_641_051_000,  # profiles/ncu_r01_cfg1_details.csv
+    ("cfg2_rollout16", "int32"): 26_024_448 + 2_797_501_000,   # profiles/ncu_r01_cfg2_details.csv (read + write)
+    ("cfg1_selfplay16", "int32"): 23_728_640 + 3_705_619_000,  # profiles/ncu_r01_cfg1_details.csv
 }
 
 

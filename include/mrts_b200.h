@@ -74,6 +74,15 @@ int mrts_step(mrts_env* env, const int32_t* actions, void* obs, void* mask, doub
 /* JNIGridnetVecClient.getMasks (:307-316) of the current state. */
 int mrts_get_masks(mrts_env* env, void* mask, void* stream);
 
+/* cycle_maps of MicroRTSGridModeVecEnv (gym_microrts/envs/vec_env.py:132-133, 1038-1056): after every
+ * mrts_step, each game whose episode ended takes the next entry of a round-robin list shared by the whole
+ * env (ascending env order, starting at entry 0) as its map and restarts from it; the obs / mask /
+ * next_actions rows of its view(s) are those of the new map, reward and done stay the step's.
+ * template_idx[k] indexes cfg->maps of mrts_create (so rotation maps are part of that table and share its
+ * size).  n = 0 turns the rotation off.  Only for all-bot or all-self-play envs: with both kinds the
+ * reference's `done_idx < num_bot_envs` test addresses the wrong clients.  Synchronises the device. */
+int mrts_set_cycle_maps(mrts_env* env, const int32_t* template_idx, int n);
+
 /* gameStep + getMasks + (optionally) a masked-uniform random policy for the resulting state,
  * the sampling recipe of the reference's hello_world.py:27-67 moved onto the device so that a
  * random-policy rollout never touches the host.  next_actions (N, H*W, 7) int32 receives, at the

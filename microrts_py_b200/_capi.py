@@ -77,10 +77,13 @@ def make_config(
     elem_bytes: int = 4,
     threads_per_game: int = 0,
     staged_units: int = 0,
+    cycle_templates: Sequence[MapTemplate] = None,
 ):
     """Build an ``mrts_config``.  ``templates`` has one entry per env (as ``map_paths`` after
     broadcasting); identical templates are de-duplicated by object identity / name.
-    Returns (cfg, keepalive) -- keep ``keepalive`` referenced while ``cfg`` is in use."""
+    Returns (cfg, keepalive) -- keep ``keepalive`` referenced while ``cfg`` is in use.  With
+    ``cycle_templates`` (the rotation maps of ``mrts_set_cycle_maps``) those templates join the table and
+    a third value is returned: their indices in it (int32 array)."""
     n = num_selfplay_envs + num_bot_envs
     if len(templates) != n:
         raise ValueError(f"need one map template per env ({n}), got {len(templates)}")
@@ -95,6 +98,12 @@ def make_config(
             index[key] = len(uniq)
             uniq.append(t)
         env_map[e] = index[key]
+    cycle_idx = np.zeros(len(cycle_templates or ()), np.int32)
+    for k, t in enumerate(cycle_templates or ()):
+        if id(t) not in index:
+            index[id(t)] = len(uniq)
+            uniq.append(t)
+        cycle_idx[k] = index[id(t)]
     arr = (MapTemplateC * len(uniq))()
     keep = [arr, env_map]
     for k, t in enumerate(uniq):
@@ -124,6 +133,8 @@ def make_config(
     cfg.elem_bytes = elem_bytes
     cfg.threads_per_game = threads_per_game
     cfg.staged_units = staged_units
+    if cycle_templates is not None:
+        return cfg, keep, cycle_idx
     return cfg, keep
 
 
@@ -165,6 +176,7 @@ SYMBOLS = [
     "mrts_debug_issue",
     "mrts_debug_cycle",
     "mrts_debug_timing",
+    "mrts_set_cycle_maps",
     "mrts_last_error",
     "mrts_version",
 ]
@@ -195,6 +207,7 @@ def lib():
         L.mrts_debug_issue.argtypes = [vp, C.c_int, vp, C.c_int, vp]
         L.mrts_debug_cycle.argtypes = [vp, C.c_int, C.POINTER(C.c_int), vp]
         L.mrts_debug_timing.argtypes = [vp, vp]
+        L.mrts_set_cycle_maps.argtypes = [vp, vp, C.c_int]
         L.mrts_reset_host.argtypes = [vp, vp, vp]
         L.mrts_step_host.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp]
         L.mrts_host_threads.argtypes = [vp]

@@ -98,6 +98,44 @@ __global__ void __launch_bounds__(128) mrts_overflow_kernel(const EnvParams P, c
     }
 }
 
+// cycle_maps (gym_microrts/envs/vec_env.py:132-133, 1038-1056): after a step, every client whose episode
+// ended gets `mapPath = next(cycle)` and is reset again, in ascending env order.  One block: each thread
+// owns a contiguous run of games (order kept), counts its ended games, a block scan gives each its rank,
+// the k-th ended game takes rotation entry (pos + k) mod n_cyc.  list = [count, games...] feeds the reset launch.
+constexpr int CYCLE_THREADS = 1024;
+__global__ void __launch_bounds__(CYCLE_THREADS) mrts_cycle_kernel(const uint8_t* ended, int n_games, const int32_t* cyc, int n_cyc, int32_t* pos,
+                                                                   int32_t* game_map, int32_t* list) {
+    __shared__ int part[CYCLE_THREADS / 32];
+    const int t = threadIdx.x, per = (n_games + CYCLE_THREADS - 1) / CYCLE_THREADS;
+    const int g0 = t * per, g1 = min(n_games, g0 + per);
+    int mine = 0;
+    for (int g = g0; g < g1; g++) mine += ended[g] != 0;
+    int incl = mine;  // inclusive scan: warp shuffle, then the warp totals
+    for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if ((t & 31) >= d) incl += v;
+    }
+    if ((t & 31) == 31) part[t >> 5] = incl;
+    __syncthreads();
+    int before = incl - mine, total = 0;
+    for (int w = 0; w < CYCLE_THREADS / 32; w++) {
+        if (w < (t >> 5)) before += part[w];
+        total += part[w];
+    }
+    const int p0 = *pos;
+    for (int g = g0; g < g1; g++)
+        if (ended[g]) {
+            game_map[g] = cyc[(p0 + before) % n_cyc];
+            list[1 + before] = g;
+            before++;
+        }
+    __syncthreads();
+    if (t == 0) {
+        list[0] = total;
+        *pos = (p0 + total) % n_cyc;
+    }
+}
+
 // ---- raw engine access (trace replay): one block, one game
 struct DebugArgs {
     int game;
@@ -191,7 +229,12 @@ struct mrts_env {
     uint32_t *cur_pobs = nullptr, *cur_pmask = nullptr;
     uint32_t* d_cost = nullptr;     // bot slabs: last step cycles per game
     int32_t* d_order = nullptr;     // 4 * n_games launch order + 4 class counts
+    // cycle_maps (mrts_set_cycle_maps): rotation list, its position, per-game ended flags, list of games to restart
+    int n_cycle = 0;
+    int32_t *d_cycle = nullptr, *d_cycle_pos = nullptr, *d_cycle_list = nullptr;
+    uint8_t* d_ended = nullptr;
     int N = 0;
+    int n_maps = 0;
     std::vector<void*> allocs;
     int* d_flag = nullptr;
     int32_t* d_rows = nullptr;
@@ -237,6 +280,8 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     e->cur_pact = nullptr;
     e->cur_pobs = e->cur_pmask = nullptr;
     P.timing = e->d_timing;
+    const bool rotate = e->n_cycle > 0 && mode == MODE_STEP;
+    P.ended = rotate ? e->d_ended : nullptr;
     const int GPB = e->gpb;
     const dim3 wgrid((P.n_games + GPB - 1) / GPB), bgrid(P.n_games);
     const cudaStream_t st = (cudaStream_t)stream;
@@ -262,12 +307,27 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
         P.ovf = nullptr;
     }
     const int ogrid = P.n_games < 296 ? P.n_games : 296;
+    // map rotation: the games that ended restart once more from their new template; only their obs / mask /
+    // sampled-action rows are rewritten (reward and done keep the step's values, vec_env.py:1057)
+    EnvParams R = F;
+    R.mode = MODE_RESET;
+    R.actions = nullptr;
+    R.pact = nullptr;
+    R.reward = nullptr;
+    R.done = nullptr;
+    R.ended = nullptr;
+    R.cost = nullptr;
 #define MRTS_LAUNCH(E, PL)                                                                       \
     do {                                                                                         \
         if (e->threads == 32 && e->minb == 8) mrts_pass_warp_kernel<E, PL, 8><<<wgrid, 32 * GPB, GPB * e->smem, st>>>(P, e->smem); \
         else if (e->threads == 32) mrts_pass_warp_kernel<E, PL, MRTS_WARP_MIN_BLOCKS><<<wgrid, 32 * GPB, GPB * e->smem, st>>>(P, e->smem); \
         else mrts_pass_kernel<E, PL><<<bgrid, e->threads, e->smem, st>>>(P);                     \
         if (defer) mrts_overflow_kernel<E, PL><<<ogrid, 128, e->smem_full, st>>>(F, e->d_ovf);   \
+        if (rotate) {                                                                            \
+            mrts_cycle_kernel<<<1, CYCLE_THREADS, 0, st>>>(e->d_ended, P.n_games, e->d_cycle, e->n_cycle, e->d_cycle_pos, \
+                                                           const_cast<int32_t*>(P.game_map), e->d_cycle_list); \
+            mrts_overflow_kernel<E, PL><<<ogrid, 128, e->smem_full, st>>>(R, e->d_cycle_list);   \
+        }                                                                                        \
     } while (0)
     if (P.elem == 4 && P.planes == 29) MRTS_LAUNCH(4, 29);
     else if (P.elem == 4) MRTS_LAUNCH(4, 31);
@@ -295,6 +355,7 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
     mrts_env* e = new mrts_env();
     e->device = cfg->device;
     e->N = S.N;
+    e->n_maps = cfg->n_maps;
     e->P = S.P;
     EnvParams& P = e->P;
     const int W = P.W, HW = P.HW, cap = P.cap;
@@ -556,7 +617,7 @@ int mrts_step_host(mrts_env* e, const void* h_actions, int action_elem_bytes, vo
 
 int mrts_launches_per_step(const mrts_env* e) {
     if (!e) return MRTS_EINVAL;
-    return 1 + (e->d_order && e->threads == 32 ? 1 : 0) + (e->threads == 32 && e->P.scap < e->P.cap ? 1 : 0);
+    return 1 + (e->d_order && e->threads == 32 ? 1 : 0) + (e->threads == 32 && e->P.scap < e->P.cap ? 1 : 0) + (e->n_cycle > 0 ? 2 : 0);
 }
 int mrts_staged_units(const mrts_env* e) { return e ? e->P.scap : MRTS_EINVAL; }
 // the transport codec on its own (host arrays in, host arrays out): lets the CPU test-suite check it without a GPU
@@ -626,6 +687,42 @@ static int debug_launch(mrts_env* e, int game, int op, const int32_t* rows7, int
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize((cudaStream_t)stream));
     if (op == 1 && gameover) CK(cudaMemcpy(gameover, e->d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    return MRTS_OK;
+}
+int mrts_set_cycle_maps(mrts_env* e, const int32_t* template_idx, int n) {
+    if (!e || n < 0 || (n > 0 && !template_idx)) return fail(MRTS_EINVAL, "bad argument");
+    if (n > 0 && e->P.num_selfplay > 0 && e->P.num_bot > 0)
+        return fail(MRTS_EINVAL, "cycle maps need all-bot or all-self-play envs: with both kinds the reference's index test (vec_env.py:1041) addresses the wrong clients");
+    for (int k = 0; k < n; k++)
+        if (template_idx[k] < 0 || template_idx[k] >= e->n_maps) return fail(MRTS_EINVAL, "cycle map index outside the templates given to mrts_create");
+    CK(cudaSetDevice(e->device));
+    CK(cudaDeviceSynchronize());
+    e->n_cycle = 0;
+    if (n == 0) return MRTS_OK;
+    if (!e->d_ended) {
+        void *a = nullptr, *b = nullptr, *c = nullptr;
+        if (cudaMalloc(&a, (size_t)e->P.n_games) != cudaSuccess || cudaMalloc(&b, sizeof(int32_t)) != cudaSuccess ||
+            cudaMalloc(&c, sizeof(int32_t) * ((size_t)e->P.n_games + 1)) != cudaSuccess) {
+            cudaFree(a);
+            cudaFree(b);
+            cudaFree(c);
+            return fail(MRTS_ENOMEM, "cudaMalloc(cycle maps)");
+        }
+        e->allocs.push_back(a);
+        e->allocs.push_back(b);
+        e->allocs.push_back(c);
+        e->d_ended = (uint8_t*)a;
+        e->d_cycle_pos = (int32_t*)b;
+        e->d_cycle_list = (int32_t*)c;
+    }
+    void* d = nullptr;
+    CK(cudaMalloc(&d, sizeof(int32_t) * (size_t)n));
+    e->allocs.push_back(d);
+    e->d_cycle = (int32_t*)d;
+    CK(cudaMemcpy(d, template_idx, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice));
+    CK(cudaMemset(e->d_cycle_pos, 0, sizeof(int32_t)));  // itertools.cycle starts at the first entry (vec_env.py:133)
+    CK(cudaMemset(e->d_ended, 0, (size_t)e->P.n_games));
+    e->n_cycle = n;
     return MRTS_OK;
 }
 int mrts_debug_timing(mrts_env* e, long long* device_buf) {

@@ -45,6 +45,7 @@ struct EnvParams {
     int32_t* next_actions;          // (N, HW, 7) or null: masked-uniform sample for the resulting state
     uint64_t seed;                  // sampler key
     uint32_t counter;               // launch counter (sampler stream position)
+    uint8_t* ended;                 // cycle_maps: per game, 1 when the step ended its episode (read by the map-rotation pass)
     long long* timing;              // profiling aid, normally null: per game 12 values {rules cycles, total cycles, St::tp[0..7], start ns, SM id}
 };
 
@@ -280,6 +281,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
             if (P.reward) P.reward[(size_t)env0 * 6 + k] = (double)s.st->rew[k / 6][k % 6];
         for (int v = tid; v < nviews; v += nth)
             if (P.done) P.done[env0 + v] = (uint8_t)reset;
+        if (P.ended && tid == 0) P.ended[g] = (uint8_t)reset;
     }
     if (reset) {  // JNIGridnetClient.reset: fresh game from the map, scripted opponent re-created
         load_template();

@@ -152,9 +152,13 @@ class MicroRTSGridModeVecEnv:
         self.reward_weight = np.asarray(reward_weight, np.float64)
         if str(prior_mode) != "none":
             raise NotImplementedError("the knowledge-graph prior (prior_mode != 'none') is outside the device hot path")
-        if len(cycle_maps) > 0:
-            raise NotImplementedError("cycle_maps is not built yet (SURVEY 8f, next)")
-        self.cycle_maps = []
+        # per-episode map rotation (vec_env.py:132-133, 1038-1056): done on the device after every step
+        self.cycle_maps = list(cycle_maps)
+        if self.cycle_maps and num_selfplay_envs > 0 and num_bot_envs > 0:
+            raise NotImplementedError(
+                "cycle_maps with both self-play and bot envs: the reference's `done_idx < num_bot_envs` test (vec_env.py:1041) "
+                "addresses the wrong clients there; use all-bot or all-self-play envs"
+            )
         if num_selfplay_envs % 2:
             raise ValueError("num_selfplay_envs must be even (two player views per self-play game)")
         self.microrts_path = microrts_path or next((p for p in _DEFAULT_MICRORTS_PATHS if p and os.path.isdir(p)), "")
@@ -166,6 +170,11 @@ class MicroRTSGridModeVecEnv:
             if p not in cache:
                 cache[p] = load_map(p, self.microrts_path)
             templates.append(cache[p])
+        cycle_templates = []
+        for p in self.cycle_maps:
+            if p not in cache:
+                cache[p] = load_map(p, self.microrts_path)
+            cycle_templates.append(cache[p])
         self.height, self.width = templates[0].height, templates[0].width
 
         # ---- scripted opponents -> device bot ids
@@ -194,13 +203,16 @@ class MicroRTSGridModeVecEnv:
         self.host_transport = bool(host_transport) and not self.return_torch
 
         self._lib = _capi.lib()
-        cfg, self._keep = _capi.make_config(
+        cfg, self._keep, cycle_idx = _capi.make_config(
             num_selfplay_envs, num_bot_envs, max_steps, partial_obs, templates, ai_ids,
             none_mode=_capi.NONE_FORK, device=dev_index, elem_bytes=self._np_dtype.itemsize, threads_per_game=threads_per_game, staged_units=staged_units,
+            cycle_templates=cycle_templates,
         )  # fmt: skip
         h = C.c_void_p()
         _capi.check(self._lib.mrts_create(C.byref(cfg), C.byref(h)))
         self._h = h
+        if len(cycle_idx):
+            _capi.check(self._lib.mrts_set_cycle_maps(self._h, cycle_idx.ctypes.data, len(cycle_idx)))
 
         # ---- the reference's computed properties (vec_env.py:229-254)
         self.real_utt = None

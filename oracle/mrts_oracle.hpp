@@ -202,6 +202,10 @@ struct VecEnv {
     void reset(int32_t* obs);
     void get_masks(int32_t* mask78, int32_t* source_unit_mask);
     void step(const int32_t* actions, int32_t* obs, double* rewards, uint8_t* done);
+    // cycle_maps (vec_env.py:1038-1056): `client.mapPath = next(self.next_map); client.reset(...)` for the
+    // client of env `env` (a bot env, or view 0 of a self-play game); the rows of its view(s) in `obs`
+    // (the full (N,H,W,P) array) are replaced as the Python loop does.
+    void swap_map_and_reset(int env, const MapTemplate& m, int32_t* obs);
 
    private:
     void observe(const GameState& view, const GameState& truth, int player, int32_t* obs_out) const;

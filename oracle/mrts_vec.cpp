@@ -77,6 +77,27 @@ void VecEnv::reset(int32_t* obs) {
     }
 }
 
+void VecEnv::swap_map_and_reset(int env, const MapTemplate& m, int32_t* obs) {
+    const size_t stride = (size_t)H * W * planes;
+    if (env < num_selfplay) {  // selfPlayClients[g].mapPath = ...; reset(); getResponse(0), getResponse(1)
+        const int g = env / 2;
+        maps[2 * g] = m;
+        reset_game(selfplay[g], maps[2 * g], -1);
+        for (int i = 0; i < 2; i++) {
+            const GameState& gs = selfplay[g].gs;
+            if (partial_obs) observe(gs.pogs(i), gs, i, obs + (2 * g + i) * stride);
+            else observe(gs, gs, i, obs + (2 * g + i) * stride);
+        }
+    } else {  // clients[b].mapPath = ...; reset(0)  (JNIGridnetClient.java:228-247)
+        const int b = env - num_selfplay;
+        maps[env] = m;
+        reset_game(botgames[b], maps[env], ai_ids[b]);
+        const GameState& gs = botgames[b].gs;
+        if (partial_obs) observe(gs.pogs(0), gs, 0, obs + env * stride);
+        else observe(gs, gs, 0, obs + env * stride);
+    }
+}
+
 void VecEnv::get_masks(int32_t* mask78, int32_t* source_unit_mask) {
     const int HW = H * W;
     auto run = [&](int e0, int e1) {

@@ -102,6 +102,9 @@ void orc_vec_step(void* h, const int32_t* actions, int32_t* obs, double* rewards
     ((VecEnv*)h)->step(actions, obs, rewards, done);
 }
 int orc_vec_planes(void* h) { return ((VecEnv*)h)->planes; }
+void orc_vec_swap_map(void* h, int env, int W, int H, const uint8_t* terrain, int res0, int res1, int nunits, const int32_t* units7, int32_t* obs) {
+    ((VecEnv*)h)->swap_map_and_reset(env, make_template(W, H, terrain, res0, res1, nunits, units7), obs);
+}
 // state of one env's game: returns number of units; rows of 12:
 // type, player, x, y, res, hp, a_type, a_param, a_x, a_y, a_utype, a_time (a_type = -1 when idle)
 int orc_vec_game_state(void* h, int env, int32_t* hdr3 /*time,res0,res1*/, int32_t* rows, int cap);

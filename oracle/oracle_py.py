@@ -41,6 +41,7 @@ def lib():
         L.orc_vec_masks.argtypes = [vp, C.c_void_p, C.c_void_p]
         L.orc_vec_step.argtypes = [vp, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_vec_planes.argtypes = [vp]
+        L.orc_vec_swap_map.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_vec_game_state.argtypes = [vp, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_vec_destroy.argtypes = [vp]
         L.orc_game_create.restype = vp
@@ -167,6 +168,27 @@ class OracleVecEnv:
             obs, rew, done = out
         self.L.orc_vec_step(self.h, _p(a), _p(obs), _p(rew), _p(done))
         return obs, rew, done
+
+    def cycle_maps_after_step(self, obs, done, num_bot_envs, next_map):
+        """The map-rotation loop of MicroRTSGridModeVecEnv.step_wait (vec_env.py:1038-1056), index tests
+        as written there: `done_idx < num_bot_envs` picks the bot branch.  `next_map` is the
+        itertools.cycle over the rotation templates; `obs` is patched in place.  Only all-bot or all-self-play
+        envs: with both kinds the reference's index test addresses the wrong clients and obs rows (Java orders
+        self-play envs first, JNIGridnetVecClient.java:117-124), which nothing could rely on."""
+        assert num_bot_envs in (0, self.N)
+        for done_idx, d in enumerate(done):
+            if done_idx < num_bot_envs:
+                if d:
+                    self._swap(self.N - num_bot_envs + done_idx, next(next_map), obs)  # clients[done_idx]
+            elif d and done_idx % 2 == 0:
+                self._swap(2 * ((done_idx - num_bot_envs) // 2), next(next_map), obs)  # selfPlayClients[(done_idx - num_bot_envs) // 2]
+        return obs
+
+    def _swap(self, env, t, obs):
+        assert (t.height, t.width) == (self.H, self.W) and obs.flags.c_contiguous and obs.dtype == np.int32
+        terr = np.ascontiguousarray(t.terrain, np.uint8)
+        units = np.ascontiguousarray(t.units, np.int32)
+        self.L.orc_vec_swap_map(self.h, env, t.width, t.height, _p(terr), t.resources[0], t.resources[1], len(units), _p(units), _p(obs))
 
     def game_state(self, env):
         cap = self.W * self.H

@@ -7,6 +7,8 @@
 
 so that the known-answer tests read like the reference's own tests/test_*.py.
 """
+import itertools
+
 import numpy as np
 
 from microrts_py_b200 import microrts_ai
@@ -18,8 +20,11 @@ AI_IDS = {microrts_ai.passiveAI: 0, microrts_ai.workerRushAI: 1}
 class _HostEnv:
     """Reference-shaped wrapper (vec_env.py:278-282, 1001-1061, 1091-1101) over a raw engine."""
 
-    def __init__(self, engine, num_envs, h, w, reward_weight, reward_shaping=True):
+    def __init__(self, engine, num_envs, h, w, reward_weight, reward_shaping=True, num_bot_envs=0, cycle_templates=()):
         self.e = engine
+        # oracle only: the rotation loop of the reference's step_wait runs here, over the engine's clients
+        self.num_bot_envs = num_bot_envs
+        self.next_map = itertools.cycle(cycle_templates) if len(cycle_templates) else None
         self.num_envs, self.height, self.width = num_envs, h, w
         self.reward_weight = np.asarray(reward_weight, np.float64)
         self.reward_shaping = reward_shaping
@@ -37,6 +42,8 @@ class _HostEnv:
         obs, reward, done = self.e.step(np.asarray(actions).reshape(self.num_envs, self.height * self.width, 7))[:3]
         if not self.reward_shaping:
             reward[:, 1:] = 0
+        if self.next_map is not None:
+            self.e.cycle_maps_after_step(obs, done, self.num_bot_envs, self.next_map)
         infos = [{"raw_rewards": item} for item in reward]
         return obs, reward @ self.reward_weight, done.astype(bool), infos
 
@@ -44,14 +51,14 @@ class _HostEnv:
         pass
 
 
-def make_env(backend, num_selfplay_envs=0, num_bot_envs=0, partial_obs=False, max_steps=2000, ai2s=(), map_paths=(), reward_weight=(0.0, 1.0, 0.0, 0.0, 0.0, 5.0), **kw):
+def make_env(backend, num_selfplay_envs=0, num_bot_envs=0, partial_obs=False, max_steps=2000, ai2s=(), map_paths=(), reward_weight=(0.0, 1.0, 0.0, 0.0, 0.0, 5.0), cycle_maps=(), **kw):
     n = num_selfplay_envs + num_bot_envs
     paths = list(map_paths) * n if len(map_paths) == 1 else list(map_paths)
     if backend == "cuda":
         from microrts_py_b200.envs import MicroRTSGridModeVecEnv
 
         return MicroRTSGridModeVecEnv(
-            num_selfplay_envs, num_bot_envs, partial_obs=partial_obs, max_steps=max_steps, ai2s=list(ai2s), map_paths=paths, reward_weight=np.asarray(reward_weight), **kw
+            num_selfplay_envs, num_bot_envs, partial_obs=partial_obs, max_steps=max_steps, ai2s=list(ai2s), map_paths=paths, reward_weight=np.asarray(reward_weight), cycle_maps=list(cycle_maps), **kw
         )
     t = templates_for(paths)
     ids = [AI_IDS[a] for a in ai2s]
@@ -59,10 +66,11 @@ def make_env(backend, num_selfplay_envs=0, num_bot_envs=0, partial_obs=False, ma
         from oracle.oracle_py import OracleVecEnv
 
         eng = OracleVecEnv(num_selfplay_envs, num_bot_envs, max_steps, partial_obs, t, ids)
+        return _HostEnv(eng, n, t[0].height, t[0].width, reward_weight, num_bot_envs=num_bot_envs, cycle_templates=templates_for(list(cycle_maps)))
     elif backend == "hostsim":
         from tests.hostsim import HostSimVecEnv
 
-        eng = HostSimVecEnv(num_selfplay_envs, num_bot_envs, max_steps, partial_obs, t, ids)
+        eng = HostSimVecEnv(num_selfplay_envs, num_bot_envs, max_steps, partial_obs, t, ids, cycle_templates=templates_for(list(cycle_maps)))
     else:
         raise ValueError(backend)
     return _HostEnv(eng, n, t[0].height, t[0].width, reward_weight)

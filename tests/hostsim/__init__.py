@@ -29,6 +29,7 @@ def lib():
         L.hs_step.argtypes = [vp, vp, vp, vp, vp, vp]
         L.hs_get_masks.argtypes = [vp, vp]
         L.hs_planes.argtypes = [vp]
+        L.hs_set_cycle_maps.argtypes = [vp, vp, C.c_int]
         L.hs_unit_capacity.argtypes = [vp]
         L.hs_export_state.argtypes = [vp, C.c_int, vp, vp, C.c_int]
         L.hs_last_error.restype = C.c_char_p
@@ -43,14 +44,18 @@ def _p(a):
 class HostSimVecEnv:
     """Same call surface as oracle.oracle_py.OracleVecEnv."""
 
-    def __init__(self, num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=1, elem_bytes=4):
+    def __init__(self, num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=1, elem_bytes=4, cycle_templates=()):
         self.L = lib()
-        cfg, self._keep = make_config(num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=none_mode, elem_bytes=elem_bytes)
+        cfg, self._keep, cyc = make_config(
+            num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=none_mode, elem_bytes=elem_bytes, cycle_templates=list(cycle_templates)
+        )
         h = C.c_void_p()
         rc = self.L.hs_create(C.byref(cfg), C.byref(h))
         if rc:
             raise ValueError(self.L.hs_last_error().decode())
         self.h = h
+        if len(cyc) and self.L.hs_set_cycle_maps(self.h, cyc.ctypes.data, len(cyc)):
+            raise ValueError("cycle maps rejected")
         self.N = num_selfplay + num_bot
         self.H, self.W = templates[0].height, templates[0].width
         self.P = self.L.hs_planes(self.h)

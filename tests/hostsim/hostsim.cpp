@@ -18,6 +18,9 @@ struct hs_env {
     HostSetup S;
     std::vector<uint8_t> games;
     std::vector<uint8_t> mem;
+    std::vector<int32_t> cycle;  // map rotation (the host loop standing in for mrts_cycle_kernel)
+    std::vector<uint8_t> ended;
+    int cycle_pos = 0, n_maps = 0;
 };
 struct NoSync {
     void operator()() const {}
@@ -38,11 +41,28 @@ static void pass(hs_env* e, int mode, const int32_t* actions, void* obs, void* m
     P.mask = mask;
     P.reward = reward;
     P.done = done;
-    for (int g = 0; g < P.n_games; g++) {
-        if (P.elem == 4 && P.planes == 29) game_pass<4, 29>(P, g, e->mem.data(), 0, 1, NoSync());
-        else if (P.elem == 4) game_pass<4, 31>(P, g, e->mem.data(), 0, 1, NoSync());
-        else if (P.planes == 29) game_pass<1, 29>(P, g, e->mem.data(), 0, 1, NoSync());
-        else game_pass<1, 31>(P, g, e->mem.data(), 0, 1, NoSync());
+    const bool rotate = mode == MODE_STEP && !e->cycle.empty();
+    P.ended = rotate ? e->ended.data() : nullptr;
+    auto one = [&](const EnvParams& Q, int g) {
+        if (Q.elem == 4 && Q.planes == 29) game_pass<4, 29>(Q, g, e->mem.data(), 0, 1, NoSync());
+        else if (Q.elem == 4) game_pass<4, 31>(Q, g, e->mem.data(), 0, 1, NoSync());
+        else if (Q.planes == 29) game_pass<1, 29>(Q, g, e->mem.data(), 0, 1, NoSync());
+        else game_pass<1, 31>(Q, g, e->mem.data(), 0, 1, NoSync());
+    };
+    for (int g = 0; g < P.n_games; g++) one(P, g);
+    if (rotate) {  // same rule as mrts_cycle_kernel + the reset launch (mrts_kernels.cu)
+        EnvParams R = P;
+        R.mode = MODE_RESET;
+        R.actions = nullptr;
+        R.reward = nullptr;
+        R.done = nullptr;
+        R.ended = nullptr;
+        for (int g = 0; g < P.n_games; g++)
+            if (e->ended[g]) {
+                e->S.game_map[g] = e->cycle[e->cycle_pos];
+                e->cycle_pos = (e->cycle_pos + 1) % (int)e->cycle.size();
+                one(R, g);
+            }
     }
 }
 
@@ -56,6 +76,8 @@ int hs_create(const mrts_config* cfg, hs_env** out) {
         return rc;
     }
     const EnvParams& P = e->S.P;
+    e->n_maps = cfg->n_maps;
+    e->ended.assign(P.n_games, 0);
     e->games.assign((size_t)P.n_games * P.game_stride + 64, 0);
     e->mem.assign(layout_of(P).total + 64, 0);
     pass(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr);
@@ -73,6 +95,14 @@ int hs_step(hs_env* e, const int32_t* actions, void* obs, void* mask, double* re
 }
 int hs_get_masks(hs_env* e, void* mask) {
     pass(e, MODE_OBSERVE, nullptr, nullptr, mask, nullptr, nullptr);
+    return 0;
+}
+int hs_set_cycle_maps(hs_env* e, const int32_t* idx, int n) {
+    if (n > 0 && e->S.P.num_selfplay > 0 && e->S.P.num_bot > 0) return -1;
+    for (int k = 0; k < n; k++)
+        if (idx[k] < 0 || idx[k] >= e->n_maps) return -1;
+    e->cycle.assign(idx, idx + n);
+    e->cycle_pos = 0;
     return 0;
 }
 int hs_planes(hs_env* e) { return e->S.P.planes; }

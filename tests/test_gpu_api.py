@@ -200,3 +200,33 @@ def test_large_bot_slab_with_launch_ordering_matches_oracle():
         elif t < 60:
             assert not bool(d.any())
     env.close()
+
+
+@pytest.mark.parametrize("mode", ["device", "host_transport"])
+def test_cycle_maps_on_a_large_slab_follow_the_reference_order(mode):
+    """Map rotation with more games than the rotation pass has threads (each thread then ranks a run of
+    games) and every env ending on the same frame: the k-th ended env, ascending, must get the k-th next
+    map of the shared list (vec_env.py:1038-1056), also through the packed host transport."""
+    from tests.backends import make_env
+
+    n = 2600
+    ais = [W if i % 3 == 0 else P for i in range(n)]
+    rotation = ["maps/8x8/basesWorkers8x8Obstacle.xml", "maps/8x8/FourBasesWorkers8x8.xml", MAP_8, "maps/8x8/melee8x8Mixed6.xml", "maps/8x8/basesWorkers8x8L.xml"]
+    kw = dict(num_selfplay_envs=0, num_bot_envs=n, max_steps=23, ai2s=ais, map_paths=[MAP_8], cycle_maps=rotation)
+    env = make_env("cuda", host_transport=(mode == "host_transport"), **kw)
+    ref = make_env("oracle", **kw)
+    rng = np.random.default_rng(5)
+    np.testing.assert_array_equal(env.reset(), ref.reset())
+    ended = 0
+    for t in range(60):
+        m_ref = ref.get_action_mask()
+        np.testing.assert_array_equal(env.get_action_mask(), m_ref, err_msg=f"mask {t}")
+        a = sample_actions(m_ref, rng, 0.02)
+        o, r, d, _ = env.step(a)
+        o2, r2, d2, _ = ref.step(a)
+        np.testing.assert_array_equal(d, d2, err_msg=f"done {t}")
+        np.testing.assert_array_equal(o, o2, err_msg=f"obs {t}")
+        np.testing.assert_array_equal(r, r2)
+        ended += int(d.sum())
+    assert ended >= 2 * n
+    env.close()

@@ -59,3 +59,43 @@ def test_trajectory_matches_oracle(engine, case):
     if steps > max_steps:
         assert n_done > 0, "the case was meant to cross an auto-reset"
     env.close()
+
+
+# Per-episode map rotation (gym_microrts/envs/vec_env.py:132-133, 1038-1056): every
+# client whose episode ended takes the next map of ONE round-robin list (ascending env order) and is
+# reset again.  Short episodes so that several envs end in the same step and the list wraps.
+CYCLE_CASES = {
+    # name: (num_selfplay, ai2s, start map, rotation, partial_obs, max_steps per env?, steps)
+    "bots16": (0, [P, W, W, P, W], MAP_16, ["maps/16x16/basesWorkers16x16B.xml", "maps/16x16/TwoBasesBarracks16x16.xml", "maps/16x16/basesWorkers16x16noResources.xml"], False, 37, 400),
+    "selfplay8": (6, [], MAP_8, ["maps/8x8/basesWorkers8x8Obstacle.xml", "maps/8x8/FourBasesWorkers8x8.xml", MAP_8, "maps/8x8/melee8x8Mixed6.xml"], False, 29, 300),
+    "bots8_partial": (0, [W, W, P], MAP_8, ["maps/8x8/basesWorkers8x8L.xml", "maps/8x8/basesWorkersBarracks8x8.xml"], True, 41, 300),
+}
+
+
+@pytest.mark.parametrize("engine", _engines())
+@pytest.mark.parametrize("case", list(CYCLE_CASES))
+def test_cycle_maps_match_the_reference_rotation(engine, case):
+    nsp, ais, mp, rotation, partial, max_steps, steps = CYCLE_CASES[case]
+    kw = dict(num_selfplay_envs=nsp, num_bot_envs=len(ais), partial_obs=partial, max_steps=max_steps, ai2s=ais, map_paths=[mp], reward_weight=RW, cycle_maps=rotation)
+    ref = make_env("oracle", **kw)
+    env = make_env(engine, **kw)
+    rng = np.random.default_rng(99)
+    np.testing.assert_array_equal(env.reset(), ref.reset(), err_msg="reset observation")
+    n_done = 0
+    for t in range(steps):
+        m_ref = ref.get_action_mask()
+        np.testing.assert_array_equal(env.get_action_mask(), m_ref, err_msg=f"{case}: mask at step {t}")
+        a = sample_actions(m_ref, rng, 0.05)
+        o, r, d, info = env.step(a)
+        o2, r2, d2, info2 = ref.step(a)
+        np.testing.assert_array_equal(o, o2, err_msg=f"{case}: observation at step {t}")
+        np.testing.assert_array_equal(r, r2, err_msg=f"{case}: weighted reward at step {t}")
+        np.testing.assert_array_equal(d, d2, err_msg=f"{case}: done at step {t}")
+        n_done += int(d.sum())
+    assert n_done > 2 * len(rotation), "the rotation list was meant to wrap"
+    env.close()
+
+
+def test_cycle_maps_with_both_env_kinds_are_refused():
+    with pytest.raises((NotImplementedError, ValueError)):
+        make_env("hostsim", 2, 1, ai2s=[P], map_paths=[MAP_8], cycle_maps=[MAP_8])
