@@ -49,6 +49,25 @@ NCU_TRAFFIC = {
 }
 
 
+_RESULT_OUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout; libraries (NCCL's version banner, torchrun notices) also
+    write to fd 1.  Keep a private handle to the real stdout for the result line and point fd 1 at stderr."""
+    global _RESULT_OUT
+    if _RESULT_OUT is None:
+        sys.stdout.flush()
+        _RESULT_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _RESULT_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def algorithmic_bytes(hw, planes, elem):
     """B = obs + mask + actions_in + 6*8 + 1 per env-step, at the stored dtypes."""
     return hw * planes * elem + hw * 78 * elem + hw * 7 * 4 + 49
@@ -175,7 +194,7 @@ def reference_arm(args):
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -289,7 +308,7 @@ def gpu_arm(args):
         if cpu_v is not None:
             line["cpu_baseline"] = {"value": cpu_v, "unit": "env-steps/s", "cores": cores, "kind": "port",
                                     "sample": f"{args.cpu_envs} envs of the workload, {cpu_k} steps ({cpu_spent:.1f} s), get_masks + step timed, action sampling excluded"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     env.close()
     if dist is not None:
         dist.destroy_process_group()
@@ -353,6 +372,7 @@ def e2e_run(args, env_dev, wl, rank, dist, dev):
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
