@@ -35,6 +35,8 @@ WORKLOADS = {
                        "ppo_gridnet rollout shape x1024: 16x16 basesWorkers16x16A, bot envs, half vs passiveAI half vs workerRushAI"),
     "diag_passive16": (MAP_16, 29, 24576, 0.0, ("passiveAI",), False, 2000, "diagnostic: 16x16 bot envs, all vs passiveAI"),
     "diag_wrush16": (MAP_16, 29, 24576, 0.0, ("workerRushAI",), False, 2000, "diagnostic: 16x16 bot envs, all vs workerRushAI"),
+    "diag_lrush16": (MAP_16, 29, 24576, 0.0, ("lightRushAI",), False, 2000, "diagnostic: 16x16 bot envs, all vs lightRushAI"),
+    "diag_mix3_16": (MAP_16, 29, 24576, 0.0, ("passiveAI", "workerRushAI", "lightRushAI"), False, 2000, "diagnostic: 16x16 bot envs, thirds vs passiveAI / workerRushAI / lightRushAI"),
     "cfg1_selfplay16": (MAP_16, 29, 32768, 1.0, (), False, 2000, "16x16 basesWorkers16x16A self-play"),
     "cfg3_selfplay8": (MAP_8, 29, 65536, 1.0, (), False, 2000, "8x8 basesWorkers8x8 self-play, 65,536 envs per GPU"),
     "cfg4_partial32": (MAP_32, 31, 16384, 1.0, (), True, 2000, "32x32 BWDistantResources32x32 self-play, partial_obs, 16,384 envs per GPU"),
@@ -143,7 +145,7 @@ def cpu_run(wl, n_envs, steps, warmup, budget_s, threads):
 
     nsp = int(n_envs * (wl["nsp"] / wl["n"])) // 2 * 2
     nbot = n_envs - nsp
-    ids = [{"passiveAI": 0, "workerRushAI": 1}[wl["bot_names"][i * wl["nbot"] // nbot]] for i in range(nbot)] if nbot else []
+    ids = [{"passiveAI": 0, "workerRushAI": 1, "lightRushAI": 2}[wl["bot_names"][i * wl["nbot"] // nbot]] for i in range(nbot)] if nbot else []
     env = OracleVecEnv(nsp, nbot, wl["max_steps"], wl["partial"], templates_for([wl["map"]] * n_envs), ids, threads=threads)
     rng = np.random.default_rng(0)
     obs = env.reset()

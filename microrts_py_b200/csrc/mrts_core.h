@@ -1547,8 +1547,10 @@ struct Sim {
         o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);
     }
 
-    // AbstractionLayerAI.findBuildingPosition, AbstractionLayerAI.java:143-228 (reserved list is empty for WorkerRush)
-    MRTS_HD int find_building_position(int dX, int dY, int vp) const {
+    // AbstractionLayerAI.findBuildingPosition, AbstractionLayerAI.java:143-228.  `reserved` = the one position an
+    // earlier build of this frame took (LightRush: base, then barracks), NO_POS when the list is empty.
+    enum { NO_POS = -2 };
+    MRTS_HD int find_building_position(int dX, int dY, int vp, int reserved = NO_POS) const {
         const int mx = H > W ? H : W;
 #pragma unroll 1
         for (int l = 1; l < mx; l++) {
@@ -1561,7 +1563,7 @@ struct Sim {
                     int x = horiz ? dX + dd : fixed;
                     int y = horiz ? fixed : dY + dd;
                     if (x < 0 || y < 0 || x >= W || y >= H) continue;
-                    if (!wall_at(x, y) && unit_at_v(x, y, vp) < 0) return x + y * W;
+                    if (x + y * W != reserved && !wall_at(x, y) && unit_at_v(x, y, vp) < 0) return x + y * W;
                 }
             }
         }
@@ -1772,10 +1774,123 @@ struct Sim {
         st->tp[2] = tick() - t_tr;
     }
 
+    // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245; returns the position it reserved, or `reserved` unchanged
+    MRTS_HD int build_if_not_building(int i, int ut, int vp, int reserved) {
+        const int k = aa_find(u[i].uid);
+        if (k >= 0 && aa[k].kind == AA_BUILD && aa[k].utype == ut) return reserved;
+        const int pos = find_building_position(u[i].x, u[i].y, vp, reserved);
+        AbstractAct r;
+        r.unit = u[i].uid;
+        r.kind = AA_BUILD;
+        r.utype = (int8_t)ut;
+        r.x = (int16_t)(pos % W);  // pos == -1 -> (-1, 0): Java % and / truncate like C++
+        r.y = (int16_t)(pos / W);
+        r.target = NO_UID;
+        r.base = NO_UID;
+        aa_put(r, i);
+        return pos;  // reservedPositions.add(pos), also when it is -1
+    }
+    MRTS_HD void aa_train(int i, int ut) {
+        AbstractAct r;
+        r.unit = u[i].uid;
+        r.kind = AA_TRAIN;
+        r.utype = (int8_t)ut;
+        r.x = r.y = 0;
+        r.target = 0;
+        r.base = NO_UID;
+        aa_put(r, i);
+    }
+
+    // LightRush.getAction, J/ai/abstraction/LightRush.java:77-254 -> pa2.  Every put of the reference is made,
+    // in its order: bases, barracks, melee units, then the workers (builders, harvesters, the rest attack).
+    MRTS_HD void light_rush(int player, int vp) {
+        wsync();
+        const int t_lr = tick();
+        const int n = nunits();
+        const int pres = hdr->res[player];
+        int nbases = 0, nbarracks = 0, nworkers = 0;
+        wsync();
+#pragma unroll 1
+        for (int base = 0; base < n; base += nl) {  // census, one unit per lane (a bot sees only its view)
+            const int i = base + lane;
+            const bool mine = i < n && u[i].player == player && inview(i, vp);
+            nbases += popc(wballot(mine && u[i].type == UT_BASE));
+            nbarracks += popc(wballot(mine && u[i].type == UT_BARRACKS));
+            nworkers += popc(wballot(mine && u[i].type == UT_WORKER));
+        }
+        // three passes in the reference's order (:93-119): idle bases, idle barracks, idle melee units
+#pragma unroll 1
+        for (int pass = 0; pass < 3; pass++) {
+            if (pass == 0 && !(nworkers < 1 && pres >= ut_cost(UT_WORKER))) continue;  // baseBehavior, :131-142
+            if (pass == 1 && pres < ut_cost(UT_LIGHT)) continue;                       // barracksBehavior, :144-148
+#pragma unroll 1
+            for (int base = 0; base < n; base += nl) {
+                const int i = base + lane;
+                bool pick = false;
+                if (i < n && u[i].player == player && u[i].a_type < 0 && inview(i, vp)) {
+                    const int t = u[i].type;
+                    pick = pass == 0 ? t == UT_BASE : pass == 1 ? t == UT_BARRACKS : (ut_can_attack(t) && !ut_can_harvest(t));
+                }
+                unsigned m = wballot(pick);
+#pragma unroll 1
+                while (m) {
+                    const int j = base + ffs32(m) - 1;
+                    m &= m - 1;
+                    if (pass == 0) aa_train(j, UT_WORKER);
+                    else if (pass == 1) aa_train(j, UT_LIGHT);
+                    else o_bot_melee(self, j, player, vp);
+                }
+                wsync();
+            }
+        }
+        // workersBehavior, :160-254: the workers in unit order; the first may build a base, the next a barracks
+        uint16_t* still_free = (uint16_t*)pa2;  // pa2 is only filled by translate_actions below
+        int nfree = 0, used = 0, reserved = NO_POS, taken = 0;
+        const bool want_base = nbases == 0 && pres >= ut_cost(UT_BASE);
+#pragma unroll 1
+        for (int base = 0; base < n; base += nl) {
+            const int i = base + lane;
+            unsigned m = wballot(i < n && u[i].player == player && ut_can_harvest(u[i].type) && inview(i, vp));
+#pragma unroll 1
+            while (m) {
+                const int j = base + ffs32(m) - 1;
+                m &= m - 1;
+                if (taken == 0 && want_base) {
+                    reserved = build_if_not_building(j, UT_BASE, vp, reserved);
+                    used += ut_cost(UT_BASE);
+                    taken = 1;
+                    continue;
+                }
+                if (taken <= 1 && nbarracks == 0 && pres >= ut_cost(UT_BARRACKS) + used) {
+                    if (taken == 0 || want_base) {  // at most one barracks builder: the first worker left after the base builder
+                        reserved = build_if_not_building(j, UT_BARRACKS, vp, reserved);
+                        used += ut_cost(UT_BARRACKS);
+                        taken = 2;
+                        continue;
+                    }
+                }
+                if (taken < 2) taken = 2;  // the builder slots are decided by the first workers only
+                if (bot_harvest(j, player, vp)) {
+                    if (lane == 0) still_free[nfree] = (uint16_t)j;
+                    nfree++;
+                }
+            }
+        }
+        wsync();
+#pragma unroll 1
+        for (int k = 0; k < nfree; k++) o_bot_melee(self, still_free[k], player, vp);
+        wsync();
+        st->tp[1] = tick() - t_lr;
+        const int t_tr = tick();
+        translate_actions(player, vp, false);
+        st->tp[2] = tick() - t_tr;
+    }
+
     // the scripted opponent's PlayerAction for `player` -> pa2
     MRTS_HD void bot_action(int player, int vp) {
         st->npa2 = 0;
         if (ai == AI_WORKER_RUSH) worker_rush(player, vp);
+        else if (ai == AI_LIGHT_RUSH) light_rush(player, vp);
         else o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
     }
 

@@ -117,11 +117,11 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
     P.elem = cfg->elem_bytes;
     P.has_bot = 0;
     for (int b = 0; b < cfg->num_bot_envs; b++) {
-        if (cfg->bot_ai[b] != MRTS_AI_PASSIVE && cfg->bot_ai[b] != MRTS_AI_WORKER_RUSH) {
+        if (cfg->bot_ai[b] != MRTS_AI_PASSIVE && cfg->bot_ai[b] != MRTS_AI_WORKER_RUSH && cfg->bot_ai[b] != MRTS_AI_LIGHT_RUSH) {
             err = "unsupported scripted opponent id";
             return MRTS_EINVAL;
         }
-        if (cfg->bot_ai[b] == MRTS_AI_WORKER_RUSH) P.has_bot = 1;
+        if (ai_plans(cfg->bot_ai[b])) P.has_bot = 1;
     }
     P.game_stride = blob_bytes(cap, P.has_bot);
 

@@ -223,7 +223,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         if (P.has_bot && naa > 0) copy16<Q16>(s.aa, gblob + 32 + P.cap * 32, align16(naa * 12), tid, nth);
         copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
     }
-    if (P.mode == MODE_STEP && s.ai == AI_WORKER_RUSH) s.astar_init(tid, nth);
+    if (P.mode == MODE_STEP && ai_plans(s.ai)) s.astar_init(tid, nth);
     if (tid == 0) {
         *(Sim*)(mem + L.sim) = s;
         St z;
@@ -251,7 +251,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     }
     scatter_grid();
     sync();
-    if (P.mode == MODE_STEP && s.ai == AI_WORKER_RUSH && !P.partial) s.flood_base_rows(-1, tid, nth);
+    if (P.mode == MODE_STEP && ai_plans(s.ai) && !P.partial) s.flood_base_rows(-1, tid, nth);
     // the agents' action rows of the units that may act, fetched by the whole group (the leader never waits on HBM)
     if (P.mode == MODE_STEP)
         s.prefetch_actions(P.pact ? nullptr : P.actions + (size_t)env0 * P.HW * 7, P.pact ? P.pact + (size_t)env0 * P.HW : nullptr, tid, nth);
@@ -324,14 +324,14 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         uint32_t* pm = P.pmask + (size_t)env0 * P.HW * 3;
         for (int k = tid; k < nviews * P.HW * 3; k += nth) pm[k] = 0;
     }
-    if (P.cost && s.ai == AI_WORKER_RUSH) {
+    if (P.cost && ai_plans(s.ai)) {
         const int n = s.hdr->nunits;
         int mine = 0;
         for (int i = tid; i < n; i += nth) mine += s.u[i].player == 1 && s.u[i].a_type < 0 && ut_can_move(s.u[i].type);
         if (mine) group_add(&s.st->nidle, mine);
     }
     sync();  // zero-fill before patches (and umask complete)
-    if (P.cost && tid == 0) P.cost[g] = s.ai == AI_WORKER_RUSH ? (uint32_t)((volatile St*)s.st)->nidle : 0u;
+    if (P.cost && tid == 0) P.cost[g] = ai_plans(s.ai) ? (uint32_t)((volatile St*)s.st)->nidle : 0u;
     if (P.next_actions)
         for (int v = 0; v < nviews; v++)
             sample_actions(s, v, umask, P.next_actions + (size_t)(env0 + v) * P.HW * 7, P.seed, P.counter, (uint32_t)(env0 + v), tid, nth);

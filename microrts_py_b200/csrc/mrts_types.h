@@ -22,7 +22,9 @@ enum { D_UP = 0, D_RIGHT = 1, D_DOWN = 2, D_LEFT = 3 };
 enum { UT_RESOURCE = 0, UT_BASE = 1, UT_BARRACKS = 2, UT_WORKER = 3, UT_LIGHT = 4, UT_HEAVY = 5, UT_RANGED = 6, N_UTYPES = 7 };
 // how `new UnitAction(TYPE_NONE, d)` behaves: the fork forces parameter -1 (J/rts/UnitAction.java:149-154)
 enum { NONE_UPSTREAM = 0, NONE_FORK = 1 };
-enum { AI_NONE = -1, AI_PASSIVE = 0, AI_WORKER_RUSH = 1 };
+enum { AI_NONE = -1, AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2 };
+// scripted opponents built on AbstractionLayerAI: abstract-action table in the blob, path searches
+MRTS_HD bool ai_plans(int ai) { return ai == AI_WORKER_RUSH || ai == AI_LIGHT_RUSH; }
 
 MRTS_HD int dir_dx(int d) { return d == D_RIGHT ? 1 : (d == D_LEFT ? -1 : 0); }
 MRTS_HD int dir_dy(int d) { return d == D_DOWN ? 1 : (d == D_UP ? -1 : 0); }

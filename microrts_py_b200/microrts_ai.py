@@ -7,6 +7,7 @@ returning the opponent.  In the reference the result is a Java ``ai.core.AI`` ob
 
   passiveAI     ai.PassiveAI             (J/ai/PassiveAI.java:41-45)
   workerRushAI  ai.abstraction.WorkerRush (J/ai/abstraction/WorkerRush.java:63-204)
+  lightRushAI   ai.abstraction.LightRush  (J/ai/abstraction/LightRush.java:77-254)
 
 Every other factory of the reference (random, search-based or closed-jar bots) raises
 ``NotImplementedError`` with the reason.
@@ -31,6 +32,10 @@ def workerRushAI(utt=None):
     return DeviceAI("WorkerRush", 1)
 
 
+def lightRushAI(utt=None):
+    return DeviceAI("LightRush", 2)
+
+
 def _unsupported(name, why):
     def f(utt=None):
         raise NotImplementedError(f"{name}: {why}")
@@ -43,7 +48,6 @@ _RANDOM = "draws from an unseeded java.util.Random; not reproducible, outside th
 _SEARCH = "wall-clock-budgeted search / closed competition jar; outside the device hot path"
 randomBiasedAI = _unsupported("randomBiasedAI", _RANDOM)
 randomAI = _unsupported("randomAI", _RANDOM)
-lightRushAI = _unsupported("lightRushAI", "not built yet (next after workerRushAI, SURVEY 8f)")
 POLightRush = _unsupported("POLightRush", "not built yet")
 POWorkerRush = _unsupported("POWorkerRush", "not built yet")
 for _n in ("naiveMCTSAI", "mixedBot", "rojo", "izanagi", "tiamat", "droplet", "guidedRojoA3N", "coacAI", "mayari"):

@@ -12,7 +12,7 @@ from microrts_py_b200 import microrts_ai
 from tests.backends import make_env
 from tests.common import MAP_4, MAP_8, MAP_16, MAP_32, MAP_64, sample_actions
 
-P, W = microrts_ai.passiveAI, microrts_ai.workerRushAI
+P, W, LR = microrts_ai.passiveAI, microrts_ai.workerRushAI, microrts_ai.lightRushAI
 RW = np.array([10.0, 1.0, 1.0, 0.2, 1.0, 4.0])
 
 CASES = {
@@ -24,6 +24,11 @@ CASES = {
     "cfg5_bloodbath64": (2, [W], MAP_64, False, 2000, 120, 0.05),
     "partial8_mixed": (4, [W, P], MAP_8, True, 120, 500, 0.1),
     "tiny4": (2, [P, W], MAP_4, False, 50, 300, 0.2),
+    # LightRush: builds a barracks, trains light units, every worker harvests
+    "lightrush16": (0, [LR, LR, W, LR], MAP_16, False, 700, 1000, 0.03),
+    "lightrush8_partial": (0, [LR, LR, P], MAP_8, True, 400, 600, 0.05),
+    "lightrush_barracks16": (0, [LR, LR], "maps/16x16/TwoBasesBarracks16x16.xml", False, 600, 700, 0.02),
+    "lightrush_nobase8": (0, [LR, LR], "maps/8x8/noBases8x8.xml", False, 300, 400, 0.05),
 }
 
 
