@@ -369,8 +369,8 @@ def e2e_run(args, env_dev, wl, rank, dist, dev):
     host_threads = env._lib.mrts_host_threads(env._h)
     env.close()
     return {"value": n * world * steps / dt, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "envs_per_gpu": n, "steps": steps,
-            "ms_per_step": 1e3 * dt / steps, "api": "MicroRTSGridModeVecEnv(host_transport=True).step/get_action_mask, NumPy int32 in/out; mrts_step_host moves 1 bit per element over PCIe and widens on %d host threads" % host_threads,
-            "host_bytes_written_per_step": int(obs.nbytes + m.nbytes)}
+            "ms_per_step": 1e3 * dt / steps, "api": "MicroRTSGridModeVecEnv(host_transport=True).step/get_action_mask, NumPy int32 in/out, two alternating result buffers; mrts_step_host_slot moves 1 bit per element over PCIe and %d host threads rewrite the cells of the arrays that changed" % host_threads,
+            "result_array_bytes_per_step": int(obs.nbytes + m.nbytes)}
 
 
 def main():

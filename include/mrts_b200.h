@@ -113,12 +113,26 @@ int mrts_sample_actions(mrts_env* env, int32_t* next_actions, uint64_t seed, voi
  * the library owns its own stream and pinned staging buffers for these calls. */
 int mrts_reset_host(mrts_env* env, void* obs, void* mask);
 int mrts_step_host(mrts_env* env, const void* actions, int action_elem_bytes, void* obs, void* mask, double* reward, uint8_t* done);
+/* Incremental forms for callers that alternate between a few result buffers (as vec envs usually do).
+ * `slot` (0 .. MRTS_HOST_SLOTS-1) names one (obs, mask) pair of caller arrays; the caller promises that the
+ * arrays it passes with a slot are the ones it passed with that slot before, NOT MODIFIED since.  The
+ * library keeps the words it last widened into them and rewrites only the cells whose value changed
+ * (between two steps most of a map does not change): the host then writes a few hundred bytes per
+ * env-step instead of ~110 KB at 16x16.  First use of a slot, or a different pointer, = full write;
+ * slot < 0 = the plain forms above.  mrts_host_forget_slot drops what is remembered about a slot. */
+#define MRTS_HOST_SLOTS 4
+int mrts_reset_host_slot(mrts_env* env, void* obs, void* mask, int slot);
+int mrts_step_host_slot(mrts_env* env, const void* actions, int action_elem_bytes, void* obs, void* mask, double* reward, uint8_t* done, int slot);
+int mrts_host_forget_slot(mrts_env* env, int slot);
 /* The transport codec alone, host arrays in and out (no device needed): observation words (n_env, hw) ->
  * one-hot (n_env, hw, planes); mask words (n_env, hw, 3) -> (n_env, hw, 78); action grid (n_env, hw, 7) ->
  * 16-bit rows at the cells whose mask word 0 has bit 0 set. */
 int mrts_host_expand_obs(const uint32_t* words, int64_t n_env, int hw, int planes, int elem_bytes, void* out);
 int mrts_host_expand_mask(const uint32_t* mask_words, int64_t n_env, int hw, int elem_bytes, void* out);
 int mrts_host_pack_actions(const void* actions, int action_elem_bytes, const uint32_t* mask_words, int64_t n_env, int hw, uint16_t* out);
+/* the incremental widening alone: `shadow` = the words `out` currently holds the expansion of (updated in place) */
+int mrts_host_expand_obs_delta(const uint32_t* words, uint32_t* shadow, int64_t n_env, int hw, int planes, int elem_bytes, void* out);
+int mrts_host_expand_mask_delta(const uint32_t* mask_words, uint32_t* shadow, int64_t n_env, int hw, int elem_bytes, void* out);
 int mrts_host_threads(const mrts_env* env); /* worker threads of the widening pool (0 before the first host call) */
 
 /* Introspection (synchronises the stream). */

@@ -160,6 +160,11 @@ SYMBOLS = [
     "mrts_sample_actions",
     "mrts_reset_host",
     "mrts_step_host",
+    "mrts_reset_host_slot",
+    "mrts_step_host_slot",
+    "mrts_host_forget_slot",
+    "mrts_host_expand_obs_delta",
+    "mrts_host_expand_mask_delta",
     "mrts_host_threads",
     "mrts_host_expand_obs",
     "mrts_host_expand_mask",
@@ -210,6 +215,11 @@ def lib():
         L.mrts_set_cycle_maps.argtypes = [vp, vp, C.c_int]
         L.mrts_reset_host.argtypes = [vp, vp, vp]
         L.mrts_step_host.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp]
+        L.mrts_reset_host_slot.argtypes = [vp, vp, vp, C.c_int]
+        L.mrts_step_host_slot.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int]
+        L.mrts_host_forget_slot.argtypes = [vp, C.c_int]
+        L.mrts_host_expand_obs_delta.argtypes = [vp, vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]
+        L.mrts_host_expand_mask_delta.argtypes = [vp, vp, C.c_int64, C.c_int, C.c_int, vp]
         L.mrts_host_threads.argtypes = [vp]
         L.mrts_host_expand_obs.argtypes = [vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]
         L.mrts_host_expand_mask.argtypes = [vp, C.c_int64, C.c_int, C.c_int, vp]

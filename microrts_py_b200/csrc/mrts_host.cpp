@@ -231,6 +231,125 @@ void expand_mask(Pool* p, const uint32_t* pmask, size_t n_env, int hw, int elem,
     });
 }
 
+// ------------------------------------------------------------------------------------------------ incremental forms
+static inline void obs_cell(uint32_t v, int planes, int elem, void* out) {
+    if (elem == 4) {
+        int32_t* o = (int32_t*)out;
+        for (int k = 0; k < planes; k++) o[k] = (int32_t)((v >> k) & 1u);
+    } else {
+        uint8_t* o = (uint8_t*)out;
+        for (int k = 0; k < planes; k++) o[k] = (uint8_t)((v >> k) & 1u);
+    }
+}
+static inline void mask_cell(const uint32_t* pm, int elem, void* out) {
+    if ((pm[0] | pm[1] | pm[2]) == 0) {
+        memset(out, 0, (size_t)78 * elem);
+        return;
+    }
+    for (int k = 0; k < 78; k++) {
+        const uint32_t bit = (pm[k >> 5] >> (k & 31)) & 1u;
+        if (elem == 4) ((int32_t*)out)[k] = (int32_t)bit;
+        else ((uint8_t*)out)[k] = (uint8_t)bit;
+    }
+}
+#if defined(__x86_64__)
+// one cell, int32, planes in 24..32: three aligned-to-cell stores and one overlapping the tail (no spill into the next cell)
+__attribute__((target("avx2"))) static inline void obs_cell_avx2_32(uint32_t w, int planes, int32_t* o) {
+    const __m256i one = _mm256_set1_epi32(1), v = _mm256_set1_epi32((int)w);
+    const __m256i s0 = _mm256_setr_epi32(0, 1, 2, 3, 4, 5, 6, 7);
+    _mm256_storeu_si256((__m256i*)(o), _mm256_and_si256(_mm256_srlv_epi32(v, s0), one));
+    _mm256_storeu_si256((__m256i*)(o + 8), _mm256_and_si256(_mm256_srlv_epi32(v, _mm256_add_epi32(s0, _mm256_set1_epi32(8))), one));
+    _mm256_storeu_si256((__m256i*)(o + 16), _mm256_and_si256(_mm256_srlv_epi32(v, _mm256_add_epi32(s0, _mm256_set1_epi32(16))), one));
+    _mm256_storeu_si256((__m256i*)(o + planes - 8), _mm256_and_si256(_mm256_srlv_epi32(v, _mm256_add_epi32(s0, _mm256_set1_epi32(planes - 8))), one));
+}
+__attribute__((target("avx2"))) static void obs_delta_avx2(const uint32_t* w, uint32_t* sh, size_t cells, int planes, int elem, uint8_t* out) {
+    const size_t cell_bytes = (size_t)planes * elem;
+    const bool wide = elem == 4 && planes >= 24 && planes <= 32;
+    size_t c = 0;
+    for (; c + 8 <= cells; c += 8) {
+        const __m256i a = _mm256_loadu_si256((const __m256i*)(w + c)), b = _mm256_loadu_si256((const __m256i*)(sh + c));
+        unsigned neq = ~(unsigned)_mm256_movemask_ps(_mm256_castsi256_ps(_mm256_cmpeq_epi32(a, b))) & 0xFFu;
+        if (!neq) continue;
+        _mm256_storeu_si256((__m256i*)(sh + c), a);
+        while (neq) {
+            const int k = __builtin_ctz(neq);
+            neq &= neq - 1;
+            if (wide) obs_cell_avx2_32(w[c + k], planes, (int32_t*)(out + (c + k) * cell_bytes));
+            else obs_cell(w[c + k], planes, elem, out + (c + k) * cell_bytes);
+        }
+    }
+    for (; c < cells; c++)
+        if (w[c] != sh[c]) {
+            sh[c] = w[c];
+            obs_cell(w[c], planes, elem, out + c * cell_bytes);
+        }
+}
+__attribute__((target("avx2"))) static void mask_delta_avx2(const uint32_t* pm, uint32_t* sh, size_t cells, int elem, uint8_t* out) {
+    const size_t cell_bytes = (size_t)78 * elem;
+    size_t c = 0;
+    for (; c + 8 <= cells; c += 8) {  // 8 cells = 24 words = three 256-bit compares
+        const __m256i* a = (const __m256i*)(pm + 3 * c);
+        const __m256i* b = (const __m256i*)(sh + 3 * c);
+        const __m256i d = _mm256_or_si256(_mm256_or_si256(_mm256_xor_si256(_mm256_loadu_si256(a), _mm256_loadu_si256(b)),
+                                                          _mm256_xor_si256(_mm256_loadu_si256(a + 1), _mm256_loadu_si256(b + 1))),
+                                          _mm256_xor_si256(_mm256_loadu_si256(a + 2), _mm256_loadu_si256(b + 2)));
+        if (_mm256_testz_si256(d, d)) continue;
+        for (size_t k = c; k < c + 8; k++) {
+            const uint32_t *n = pm + 3 * k;
+            uint32_t* o = sh + 3 * k;
+            if (n[0] == o[0] && n[1] == o[1] && n[2] == o[2]) continue;
+            o[0] = n[0], o[1] = n[1], o[2] = n[2];
+            mask_cell(n, elem, out + k * cell_bytes);
+        }
+    }
+    for (; c < cells; c++) {
+        const uint32_t* n = pm + 3 * c;
+        uint32_t* o = sh + 3 * c;
+        if (n[0] == o[0] && n[1] == o[1] && n[2] == o[2]) continue;
+        o[0] = n[0], o[1] = n[1], o[2] = n[2];
+        mask_cell(n, elem, out + c * cell_bytes);
+    }
+}
+#endif
+
+void expand_obs_delta(Pool* p, const uint32_t* words, uint32_t* shadow, size_t n_env, int hw, int planes, int elem, void* out) {
+    parallel_for(p, n_env, [=](size_t b, size_t e) {
+        const size_t c0 = b * (size_t)hw, cells = (e - b) * (size_t)hw;
+        uint8_t* o = (uint8_t*)out + c0 * (size_t)planes * elem;
+#if defined(__x86_64__)
+        if (has_avx2()) {
+            obs_delta_avx2(words + c0, shadow + c0, cells, planes, elem, o);
+            return;
+        }
+#endif
+        for (size_t c = 0; c < cells; c++)
+            if (words[c0 + c] != shadow[c0 + c]) {
+                shadow[c0 + c] = words[c0 + c];
+                obs_cell(words[c0 + c], planes, elem, o + c * (size_t)planes * elem);
+            }
+    });
+}
+
+void expand_mask_delta(Pool* p, const uint32_t* pmask, uint32_t* shadow, size_t n_env, int hw, int elem, void* out) {
+    parallel_for(p, n_env, [=](size_t b, size_t e) {
+        const size_t c0 = b * (size_t)hw, cells = (e - b) * (size_t)hw;
+        uint8_t* o = (uint8_t*)out + c0 * (size_t)78 * elem;
+#if defined(__x86_64__)
+        if (has_avx2()) {
+            mask_delta_avx2(pmask + 3 * c0, shadow + 3 * c0, cells, elem, o);
+            return;
+        }
+#endif
+        for (size_t c = 0; c < cells; c++) {
+            const uint32_t* n = pmask + 3 * (c0 + c);
+            uint32_t* s = shadow + 3 * (c0 + c);
+            if (n[0] == s[0] && n[1] == s[1] && n[2] == s[2]) continue;
+            s[0] = n[0], s[1] = n[1], s[2] = n[2];
+            mask_cell(n, elem, o + c * (size_t)78 * elem);
+        }
+    });
+}
+
 // same encoding as mrts::Sim::pack_action (mrts_core.h)
 template <class T>
 static inline uint16_t pack_row(const T* a) {

@@ -224,6 +224,11 @@ struct mrts_env {
         uint8_t *h_done = nullptr, *d_done = nullptr;
         mrts_host::Pool* pool = nullptr;
         bool ready = false, have_mask = false;
+        // result-array pairs the caller hands back unmodified (mrts_*_host_slot): the words last expanded into them
+        struct Slot {
+            void *obs = nullptr, *mask = nullptr;
+            std::vector<uint32_t> pobs, pmask;
+        } slots[MRTS_HOST_SLOTS];
     } hio;
     const uint16_t* cur_pact = nullptr;  // per-launch packed pointers (set by the host entry points)
     uint32_t *cur_pobs = nullptr, *cur_pmask = nullptr;
@@ -560,7 +565,7 @@ static int hostio_init(mrts_env* e) {
 }
 
 // device -> pinned staging -> the caller's arrays; the observation is widened while the mask words are still in flight
-static int hostio_finish(mrts_env* e, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done) {
+static int hostio_finish(mrts_env* e, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done, int slot = -1) {
     auto& h = e->hio;
     const size_t N = (size_t)e->N, HW = (size_t)e->P.HW;
     CK(cudaMemcpyAsync(h.h_pobs, h.d_pobs, N * HW * 4, cudaMemcpyDeviceToHost, h.stream));
@@ -569,28 +574,61 @@ static int hostio_finish(mrts_env* e, void* h_obs, void* h_mask, double* h_rewar
     if (h_reward) CK(cudaMemcpyAsync(h.h_rew, h.d_rew, N * 48, cudaMemcpyDeviceToHost, h.stream));
     if (h_done) CK(cudaMemcpyAsync(h.h_done, h.d_done, N, cudaMemcpyDeviceToHost, h.stream));
     CK(cudaEventSynchronize(h.ev_obs));
-    if (h_obs) mrts_host::expand_obs(h.pool, h.h_pobs, N, (int)HW, e->P.planes, e->P.elem, h_obs);
+    mrts_env::HostIO::Slot* S = slot >= 0 ? &h.slots[slot] : nullptr;
+    if (h_obs) {
+        if (S && S->obs == h_obs && S->pobs.size() == N * HW) {
+            mrts_host::expand_obs_delta(h.pool, h.h_pobs, S->pobs.data(), N, (int)HW, e->P.planes, e->P.elem, h_obs);
+        } else {
+            mrts_host::expand_obs(h.pool, h.h_pobs, N, (int)HW, e->P.planes, e->P.elem, h_obs);
+            if (S) {
+                S->pobs.assign(h.h_pobs, h.h_pobs + N * HW);
+                S->obs = h_obs;
+            }
+        }
+    }
     CK(cudaStreamSynchronize(h.stream));
     h.have_mask = true;
-    if (h_mask) mrts_host::expand_mask(h.pool, h.h_pmask, N, (int)HW, e->P.elem, h_mask);
+    if (h_mask) {
+        if (S && S->mask == h_mask && S->pmask.size() == N * HW * 3) {
+            mrts_host::expand_mask_delta(h.pool, h.h_pmask, S->pmask.data(), N, (int)HW, e->P.elem, h_mask);
+        } else {
+            mrts_host::expand_mask(h.pool, h.h_pmask, N, (int)HW, e->P.elem, h_mask);
+            if (S) {
+                S->pmask.assign(h.h_pmask, h.h_pmask + N * HW * 3);
+                S->mask = h_mask;
+            }
+        }
+    }
     if (h_reward) memcpy(h_reward, h.h_rew, N * 48);
     if (h_done) memcpy(h_done, h.h_done, N);
     return MRTS_OK;
 }
 
-int mrts_reset_host(mrts_env* e, void* h_obs, void* h_mask) {
+int mrts_reset_host(mrts_env* e, void* h_obs, void* h_mask) { return mrts_reset_host_slot(e, h_obs, h_mask, -1); }
+int mrts_step_host(mrts_env* e, const void* h_actions, int action_elem_bytes, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done) {
+    return mrts_step_host_slot(e, h_actions, action_elem_bytes, h_obs, h_mask, h_reward, h_done, -1);
+}
+int mrts_host_forget_slot(mrts_env* e, int slot) {
+    if (!e || slot < 0 || slot >= MRTS_HOST_SLOTS) return fail(MRTS_EINVAL, "bad slot");
+    e->hio.slots[slot] = mrts_env::HostIO::Slot();
+    return MRTS_OK;
+}
+
+int mrts_reset_host_slot(mrts_env* e, void* h_obs, void* h_mask, int slot) {
     if (!e) return fail(MRTS_EINVAL, "null env");
+    if (slot >= MRTS_HOST_SLOTS) return fail(MRTS_EINVAL, "bad slot");
     int rc = hostio_init(e);
     if (rc) return rc;
     e->cur_pobs = e->hio.d_pobs;
     e->cur_pmask = e->hio.d_pmask;
     rc = launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, e->hio.stream);
     if (rc) return rc;
-    return hostio_finish(e, h_obs, h_mask, nullptr, nullptr);
+    return hostio_finish(e, h_obs, h_mask, nullptr, nullptr, slot);
 }
 
-int mrts_step_host(mrts_env* e, const void* h_actions, int action_elem_bytes, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done) {
+int mrts_step_host_slot(mrts_env* e, const void* h_actions, int action_elem_bytes, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done, int slot) {
     if (!e || !h_actions) return fail(MRTS_EINVAL, "null argument");
+    if (slot >= MRTS_HOST_SLOTS) return fail(MRTS_EINVAL, "bad slot");
     if (action_elem_bytes != 4 && action_elem_bytes != 8) return fail(MRTS_EINVAL, "actions must be int32 or int64");
     int rc = hostio_init(e);
     if (rc) return rc;
@@ -612,7 +650,7 @@ int mrts_step_host(mrts_env* e, const void* h_actions, int action_elem_bytes, vo
     // `actions` is unused when the packed rows are given; pass a valid non-null pointer for the argument check
     rc = launch(e, MODE_STEP, (const int32_t*)h.d_pact, nullptr, nullptr, h.d_rew, h.d_done, h.stream);
     if (rc) return rc;
-    return hostio_finish(e, h_obs, h_mask, h_reward, h_done);
+    return hostio_finish(e, h_obs, h_mask, h_reward, h_done, slot);
 }
 
 int mrts_launches_per_step(const mrts_env* e) {
@@ -632,6 +670,20 @@ int mrts_host_expand_mask(const uint32_t* mask_words, int64_t n_env, int hw, int
     if (!mask_words || !out || (elem_bytes != 4 && elem_bytes != 1)) return fail(MRTS_EINVAL, "bad argument");
     mrts_host::Pool* p = mrts_host::pool_create(0);
     mrts_host::expand_mask(p, mask_words, (size_t)n_env, hw, elem_bytes, out);
+    mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
+int mrts_host_expand_obs_delta(const uint32_t* words, uint32_t* shadow, int64_t n_env, int hw, int planes, int elem_bytes, void* out) {
+    if (!words || !shadow || !out || (elem_bytes != 4 && elem_bytes != 1) || planes < 1 || planes > 31) return fail(MRTS_EINVAL, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    mrts_host::expand_obs_delta(p, words, shadow, (size_t)n_env, hw, planes, elem_bytes, out);
+    mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
+int mrts_host_expand_mask_delta(const uint32_t* mask_words, uint32_t* shadow, int64_t n_env, int hw, int elem_bytes, void* out) {
+    if (!mask_words || !shadow || !out || (elem_bytes != 4 && elem_bytes != 1)) return fail(MRTS_EINVAL, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    mrts_host::expand_mask_delta(p, mask_words, shadow, (size_t)n_env, hw, elem_bytes, out);
     mrts_host::pool_destroy(p);
     return MRTS_OK;
 }

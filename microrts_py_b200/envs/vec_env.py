@@ -18,7 +18,9 @@ Extra keyword-only arguments (all default to the reference's behaviour):
   host_transport NumPy mode only: use the library's host-buffer entry points (mrts_reset_host /
                 mrts_step_host): results cross PCIe as one bit per element and are widened into the
                 NumPy arrays by the library's thread pool; same values, shapes and dtypes.  Arrays are
-                two alternating buffers per output (as with ``zero_copy``)
+                two alternating buffers per output (as with ``zero_copy``), handed out READ-ONLY: the
+                library remembers what each buffer holds and rewrites only the cells that changed
+                (mrts_*_host_slot), so they must come back unmodified -- copy before editing
   fuse_mask     compute the action mask of the resulting state inside ``step`` (one launch,
                 the state is staged once); ``get_action_mask`` then only hands it out
 """
@@ -96,6 +98,10 @@ _DEFAULT_MICRORTS_PATHS = [os.environ.get("MICRORTS_PATH", ""), "/root/reference
 
 def _ptr(t: Optional[torch.Tensor]):
     return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _np_ptr(a: np.ndarray):
+    return C.c_void_p(a.ctypes.data)  # also for arrays handed out read-only
 
 
 class MicroRTSGridModeVecEnv:
@@ -256,6 +262,8 @@ class MicroRTSGridModeVecEnv:
                 "raw": [np.zeros((N, 6), np.float64) for _ in range(2)],
                 "done": [np.zeros((N,), np.uint8) for _ in range(2)],
             }
+            for a in self._hbuf["obs"] + self._hbuf["mask"]:
+                a.flags.writeable = False  # the library writes through the raw pointer; see host_transport above
             self._hcur = 0
             self._h_mask_np = None
 
@@ -299,7 +307,7 @@ class MicroRTSGridModeVecEnv:
         if self.host_transport:
             self._hcur ^= 1
             o, m = self._hbuf["obs"][self._hcur], self._hbuf["mask"][self._hcur]
-            _capi.check(self._lib.mrts_reset_host(self._h, o.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.c_void_p)))
+            _capi.check(self._lib.mrts_reset_host_slot(self._h, _np_ptr(o), _np_ptr(m), self._hcur))
             self._h_mask_np = m
             return o
         obs = self._new(self._shape_obs, self._t_dtype)
@@ -376,8 +384,8 @@ class MicroRTSGridModeVecEnv:
             k = self._hcur
             o, m, reward, d = self._hbuf["obs"][k], self._hbuf["mask"][k], self._hbuf["raw"][k], self._hbuf["done"][k]
             vp = C.c_void_p
-            _capi.check(self._lib.mrts_step_host(self._h, a.ctypes.data_as(vp), a.dtype.itemsize, o.ctypes.data_as(vp), m.ctypes.data_as(vp),
-                                                 reward.ctypes.data_as(vp), d.ctypes.data_as(vp)))
+            _capi.check(self._lib.mrts_step_host_slot(self._h, a.ctypes.data_as(vp), a.dtype.itemsize, _np_ptr(o), _np_ptr(m),
+                                                      reward.ctypes.data_as(vp), d.ctypes.data_as(vp), k))
             self._h_mask_np = m
             if not self.reward_shaping:
                 reward[:, 1:] = 0

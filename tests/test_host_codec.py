@@ -77,3 +77,37 @@ def test_action_rows_pack_only_at_source_cells(dtype):
     for e, c in zip(*np.nonzero(src)):
         want[e, c] = _pack_ref(a[e, c])
     np.testing.assert_array_equal(out, want)
+
+
+@pytest.mark.parametrize("hw,planes,dtype", [(256, 29, np.int32), (100, 31, np.int32), (64, 29, np.uint8), (3, 29, np.int32)])
+def test_incremental_widening_tracks_a_changing_state(hw, planes, dtype):
+    """mrts_*_host_slot: the shadow words say what the caller's array holds; after every update the array
+    must equal the full expansion, nothing outside it may be touched, and an unchanged state writes nothing."""
+    L = _capi.lib()
+    rng = np.random.default_rng(planes * hw)
+    n, elem = 23, np.dtype(dtype).itemsize
+    words = rng.integers(0, 2 ** planes, size=(n, hw), dtype=np.uint32)
+    pm = np.zeros((n, hw, 3), np.uint32)
+    buf_o = np.zeros(n * hw * planes + 64, dtype)
+    buf_m = np.zeros(n * hw * 78 + 64, dtype)
+    out_o = buf_o[1 : 1 + n * hw * planes].reshape(n, hw, planes)
+    out_m = buf_m[1 : 1 + n * hw * 78].reshape(n, hw, 78)
+    _capi.check(L.mrts_host_expand_obs(_p(words), n, hw, planes, elem, _p(out_o)))
+    _capi.check(L.mrts_host_expand_mask(_p(pm), n, hw, elem, _p(out_m)))
+    sh_o, sh_m = words.copy(), pm.copy()
+    for it in range(12):
+        if it != 5:  # iteration 5: nothing changes
+            k = rng.random((n, hw)) < (0.5 if it == 7 else 0.04)
+            words[k] = rng.integers(0, 2 ** planes, size=int(k.sum()), dtype=np.uint32)
+            pm[rng.random((n, hw)) < 0.03] = 0
+            k = rng.random((n, hw)) < 0.03
+            pm[k] = rng.integers(0, 2 ** 32, size=(int(k.sum()), 3), dtype=np.uint64).astype(np.uint32)
+            pm[:, :, 2] &= (1 << 14) - 1
+        _capi.check(L.mrts_host_expand_obs_delta(_p(words), _p(sh_o), n, hw, planes, elem, _p(out_o)))
+        _capi.check(L.mrts_host_expand_mask_delta(_p(pm), _p(sh_m), n, hw, elem, _p(out_m)))
+        np.testing.assert_array_equal(sh_o, words)
+        np.testing.assert_array_equal(sh_m, pm)
+        np.testing.assert_array_equal(out_o, ((words[:, :, None] >> np.arange(planes, dtype=np.uint32)) & 1).astype(dtype))
+        bits = np.concatenate([(pm[:, :, j : j + 1] >> np.arange(32, dtype=np.uint32)) & 1 for j in range(3)], axis=2)[:, :, :78]
+        np.testing.assert_array_equal(out_m, bits.astype(dtype))
+        assert not buf_o[0] and not buf_o[1 + n * hw * planes :].any() and not buf_m[0] and not buf_m[1 + n * hw * 78 :].any()
