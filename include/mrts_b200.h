@@ -58,6 +58,9 @@ typedef struct mrts_config {
     int32_t threads_per_game;  /* 0 = choose from the map size; n > 0 = n threads per game; n < 0 = one warp per game, -n games per block */
     int32_t staged_units;      /* 0 = choose; units per game staged in shared memory by the warp kernel (games that may
                                   outgrow it take the full-capacity launch); tuning / tests                          */
+    const int32_t* bot_ai1;    /* NULL, or num_bot_envs entries: MRTS_AI_* playing player 0 of that bot env (bot vs bot,
+                                  J/tests/JNIBotClient.java:108-134, MicroRTSBotVecEnv), -1 = the agent plays it.  The
+                                  action rows of such envs are ignored; both bots act on the full state             */
 } mrts_config;
 
 typedef struct mrts_env mrts_env;
@@ -70,7 +73,7 @@ void mrts_destroy(mrts_env* env);
 /* JNIGridnetVecClient.reset (:179-211): every game restarts from its map; obs / mask may be NULL. */
 int mrts_reset(mrts_env* env, void* obs, void* mask, void* stream);
 /* JNIGridnetVecClient.gameStep (:213-297) fused with getMasks (:307-316) of the resulting state:
- * any of obs / mask / reward / done may be NULL. */
+ * any of obs / mask / reward / done may be NULL; actions may be NULL when every env is bot vs bot (mrts_config::bot_ai1). */
 int mrts_step(mrts_env* env, const int32_t* actions, void* obs, void* mask, double* reward, uint8_t* done, void* stream);
 /* JNIGridnetVecClient.getMasks (:307-316) of the current state. */
 int mrts_get_masks(mrts_env* env, void* mask, void* stream);

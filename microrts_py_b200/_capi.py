@@ -50,6 +50,7 @@ class ConfigC(C.Structure):
         ("elem_bytes", C.c_int32),
         ("threads_per_game", C.c_int32),
         ("staged_units", C.c_int32),
+        ("bot_ai1", C.c_void_p),
     ]
 
 
@@ -78,6 +79,7 @@ def make_config(
     threads_per_game: int = 0,
     staged_units: int = 0,
     cycle_templates: Sequence[MapTemplate] = None,
+    bot_ai1: Sequence[int] = None,
 ):
     """Build an ``mrts_config``.  ``templates`` has one entry per env (as ``map_paths`` after
     broadcasting); identical templates are de-duplicated by object identity / name.
@@ -133,6 +135,12 @@ def make_config(
     cfg.elem_bytes = elem_bytes
     cfg.threads_per_game = threads_per_game
     cfg.staged_units = staged_units
+    if bot_ai1 is not None:  # bot vs bot (JNIBotClient): scripted player 0 per bot env, -1 = agent
+        if len(bot_ai1) != num_bot_envs:
+            raise ValueError("need one player-0 entry per bot env")
+        a1 = np.ascontiguousarray(np.asarray(list(bot_ai1), np.int32))
+        keep.append(a1)
+        cfg.bot_ai1 = a1.ctypes.data if len(a1) else None
     if cycle_templates is not None:
         return cfg, keep, cycle_idx
     return cfg, keep

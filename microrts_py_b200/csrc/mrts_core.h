@@ -110,6 +110,8 @@ struct Sim {
     int W, H, HW, cap;
     int none_mode, partial, max_steps;
     int ai;         // scripted opponent of a bot game (AI_*), AI_NONE for a self-play game
+    int ai1;        // bot-vs-bot game (JNIBotClient): the scripted player 0, AI_NONE when an agent plays
+    MRTS_HD bool plans() const { return ai_plans(ai) || ai_plans(ai1); }  // abstract-action table and path searches in use
     // ---- state staged for this step
     GameHdr* hdr;
     Unit* u;
@@ -918,6 +920,9 @@ struct Sim {
             k = hdr->n_aa++;
         }
         aa[k] = r;
+        // bot-vs-bot games keep both bots' tables in this one table: entries of player 0's bot carry AA_OWNER0
+        // (each bot only ever sees its own entries, in their insertion order -- two LinkedHashMaps)
+        if (u[i].player == 0) aa[k].kind = (uint8_t)(r.kind | AA_OWNER0);
         // UF_AA_ATTACK mirrors "this unit's table entry is an Attack" (see worker_rush)
         if (r.kind == AA_ATTACK) u[i].flags |= UF_AA_ATTACK;
         else u[i].flags &= (uint8_t)~UF_AA_ATTACK;
@@ -1504,6 +1509,12 @@ struct Sim {
 #pragma unroll 1
         for (int k = 0; k < na; k++) {
             AbstractAct r = aa[k];
+            const int owner0 = r.kind & AA_OWNER0;
+            if ((owner0 != 0) != (player == 0)) {  // the other bot's entry (bot-vs-bot games)
+                aa[keep++] = r;
+                continue;
+            }
+            r.kind &= AA_KIND_MASK;
             int i = find_uid(r.unit, vp);
             bool del = false;
             if (i < 0) del = true;
@@ -1521,7 +1532,10 @@ struct Sim {
                     }
                 }
             }
-            if (!del) aa[keep++] = r;  // r may carry Train's completed flag
+            if (!del) {
+                r.kind |= (uint8_t)owner0;
+                aa[keep++] = r;  // r may carry Train's completed flag
+            }
             else if (i >= 0) u[i].flags &= (uint8_t)~UF_AA_ATTACK;
         }
         hdr->n_aa = (uint16_t)keep;
@@ -1629,7 +1643,7 @@ struct Sim {
         kbase = wmin(kbase);
         const int cres = kres == NO_KEY ? -1 : (kres & 0xFFFF), cbase = kbase == NO_KEY ? -1 : (kbase & 0xFFFF);
         const int k = aa_find(u[w].uid);
-        const bool isharv = k >= 0 && aa[k].kind == AA_HARVEST;
+        const bool isharv = k >= 0 && (aa[k].kind & AA_KIND_MASK) == AA_HARVEST;
         if (u[w].res > 0) {
             if (cbase >= 0) {
                 if (!isharv || aa[k].base != u[cbase].uid) aa_harvest(w, -1, cbase);
@@ -1734,7 +1748,7 @@ struct Sim {
             const int harvester = want_base ? w1 : w0;
             if (builder >= 0) {  // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245
                 int k = aa_find(u[builder].uid);
-                if (k < 0 || aa[k].kind != AA_BUILD || aa[k].utype != UT_BASE) {
+                if (k < 0 || (aa[k].kind & AA_KIND_MASK) != AA_BUILD || aa[k].utype != UT_BASE) {
                     int pos = find_building_position(u[builder].x, u[builder].y, vp);
                     AbstractAct r;
                     r.unit = u[builder].uid;
@@ -1777,7 +1791,7 @@ struct Sim {
     // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245; returns the position it reserved, or `reserved` unchanged
     MRTS_HD int build_if_not_building(int i, int ut, int vp, int reserved) {
         const int k = aa_find(u[i].uid);
-        if (k >= 0 && aa[k].kind == AA_BUILD && aa[k].utype == ut) return reserved;
+        if (k >= 0 && (aa[k].kind & AA_KIND_MASK) == AA_BUILD && aa[k].utype == ut) return reserved;
         const int pos = find_building_position(u[i].x, u[i].y, vp, reserved);
         AbstractAct r;
         r.unit = u[i].uid;
@@ -1887,10 +1901,10 @@ struct Sim {
     }
 
     // the scripted opponent's PlayerAction for `player` -> pa2
-    MRTS_HD void bot_action(int player, int vp) {
+    MRTS_HD void bot_action(int which, int player, int vp) {
         st->npa2 = 0;
-        if (ai == AI_WORKER_RUSH) worker_rush(player, vp);
-        else if (ai == AI_LIGHT_RUSH) light_rush(player, vp);
+        if (which == AI_WORKER_RUSH) worker_rush(player, vp);
+        else if (which == AI_LIGHT_RUSH) light_rush(player, vp);
         else o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
     }
 
@@ -1914,6 +1928,18 @@ struct Sim {
                 o_decode_actions(self, p, vp);
                 o_issue_safe(self, pa, st->npa);
             }
+        } else if (ai1 != AI_NONE) {
+            // JNIBotClient.gameStep, J/tests/JNIBotClient.java:108-113: both bots act on the full state (the
+            // client ignores partialObs), player 0's action is issued first
+            bot_action(ai1, 0, -1);
+            wsync();
+            const int n0 = st->npa2;
+            for (int k = lane; k < n0; k += nl) pa[k] = pa2[k];
+            st->npa = n0;
+            wsync();
+            bot_action(ai, 1, -1);
+            o_issue_safe(self, pa, st->npa);
+            o_issue_safe(self, pa2, st->npa2);
         } else {
             // JNIGridnetClient.gameStep, :163-196
             int v0 = -1, v1 = -1;
@@ -1927,7 +1953,7 @@ struct Sim {
             o_decode_actions(self, 0, v0);
             int t1 = tick();
             st->tp[0] = t1 - t0;
-            bot_action(1, v1);
+            bot_action(ai, 1, v1);
             t0 = tick();
             o_issue_safe(self, pa, st->npa);
             t1 = tick();

@@ -240,6 +240,7 @@ struct mrts_env {
     uint8_t* d_ended = nullptr;
     int N = 0;
     int n_maps = 0;
+    bool all_scripted = false;  // every game is bot vs bot (mrts_config::bot_ai1): mrts_step takes no actions
     std::vector<void*> allocs;
     int* d_flag = nullptr;
     int32_t* d_rows = nullptr;
@@ -361,6 +362,8 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
     e->device = cfg->device;
     e->N = S.N;
     e->n_maps = cfg->n_maps;
+    e->all_scripted = S.N > 0;
+    for (int8_t a1 : S.game_ai1) e->all_scripted = e->all_scripted && a1 != AI_NONE;
     e->P = S.P;
     EnvParams& P = e->P;
     const int W = P.W, HW = P.HW, cap = P.cap;
@@ -370,7 +373,8 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         return fail(MRTS_ECUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(ce));
     }
     if ((rc = upload(e, S.tpls, &P.maps)) || (rc = upload(e, S.grids, &P.grid_pool)) || (rc = upload(e, S.units, &P.unit_pool)) ||
-        (rc = upload(e, S.game_map, &P.game_map)) || (rc = upload(e, S.game_ai, &P.game_ai))) {
+        (rc = upload(e, S.game_map, &P.game_map)) || (rc = upload(e, S.game_ai, &P.game_ai)) ||
+        (rc = upload(e, S.game_ai1, &P.game_ai1))) {
         mrts_destroy(e);
         return rc;
     }
@@ -523,7 +527,7 @@ void mrts_destroy(mrts_env* e) {
 int mrts_reset(mrts_env* e, void* obs, void* mask, void* stream) { return launch(e, MODE_RESET, nullptr, obs, mask, nullptr, nullptr, stream); }
 
 int mrts_step(mrts_env* e, const int32_t* actions, void* obs, void* mask, double* reward, uint8_t* done, void* stream) {
-    if (!actions) return fail(MRTS_EINVAL, "actions is null");
+    if (!actions && !(e && e->all_scripted)) return fail(MRTS_EINVAL, "actions is null");
     return launch(e, MODE_STEP, actions, obs, mask, reward, done, stream);
 }
 

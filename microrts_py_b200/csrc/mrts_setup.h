@@ -19,6 +19,7 @@ struct HostSetup {
     std::vector<Unit> units;
     std::vector<int32_t> game_map;
     std::vector<int8_t> game_ai;
+    std::vector<int8_t> game_ai1;
 };
 
 inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
@@ -122,6 +123,7 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
             return MRTS_EINVAL;
         }
         if (ai_plans(cfg->bot_ai[b])) P.has_bot = 1;
+        if (cfg->bot_ai1 && ai_plans(cfg->bot_ai1[b])) P.has_bot = 1;
     }
     P.game_stride = blob_bytes(cap, P.has_bot);
 
@@ -161,6 +163,7 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
     }
     S.game_map.assign(P.n_games, 0);
     S.game_ai.assign(P.n_games, (int8_t)AI_NONE);
+    S.game_ai1.assign(P.n_games, (int8_t)AI_NONE);
     const int nsp = P.num_selfplay / 2;
     for (int g = 0; g < P.n_games; g++) {
         const int env = g < nsp ? 2 * g : P.num_selfplay + (g - nsp);
@@ -171,6 +174,18 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
         }
         S.game_map[g] = m;
         S.game_ai[g] = g < nsp ? (int8_t)AI_NONE : (int8_t)cfg->bot_ai[g - nsp];
+        if (g >= nsp && cfg->bot_ai1 && cfg->bot_ai1[g - nsp] >= 0) {
+            const int a1 = cfg->bot_ai1[g - nsp];
+            if (a1 != MRTS_AI_PASSIVE && a1 != MRTS_AI_WORKER_RUSH && a1 != MRTS_AI_LIGHT_RUSH) {
+                err = "unsupported scripted player-0 id";
+                return MRTS_EINVAL;
+            }
+            if (cfg->partial_obs) {
+                err = "bot-vs-bot envs ignore partial_obs in the reference (JNIBotClient acts on the full state): create them with partial_obs = 0";
+                return MRTS_EINVAL;
+            }
+            S.game_ai1[g] = (int8_t)a1;
+        }
     }
     return MRTS_OK;
 }

@@ -30,6 +30,7 @@ struct EnvParams {
     const Unit* unit_pool;          // initial unit lists of all templates
     const int32_t* game_map;        // template id per game
     const int8_t* game_ai;          // AI_* per game (AI_NONE = self-play)
+    const int8_t* game_ai1;         // AI_* playing player 0 (bot-vs-bot games), AI_NONE = an agent; may be null
     // per-launch
     int32_t mode;
     int32_t elem;                   // bytes per obs/mask element: 4 (int32, reference dtype) or 1 (uint8)
@@ -103,6 +104,7 @@ MRTS_HD void bind_sim(Sim& s, const EnvParams& P, const Layout& L, uint8_t* mem,
     s.partial = P.partial;
     s.max_steps = P.max_steps;
     s.ai = P.game_ai[g];
+    s.ai1 = P.game_ai1 ? P.game_ai1[g] : AI_NONE;
     s.hdr = (GameHdr*)(mem + L.blob);
     s.u = (Unit*)(mem + L.blob + 32);
     s.aa = (AbstractAct*)(mem + L.blob + 32 + P.scap * 32);
@@ -223,7 +225,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         if (P.has_bot && naa > 0) copy16<Q16>(s.aa, gblob + 32 + P.cap * 32, align16(naa * 12), tid, nth);
         copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
     }
-    if (P.mode == MODE_STEP && ai_plans(s.ai)) s.astar_init(tid, nth);
+    if (P.mode == MODE_STEP && s.plans()) s.astar_init(tid, nth);
     if (tid == 0) {
         *(Sim*)(mem + L.sim) = s;
         St z;
@@ -251,9 +253,9 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     }
     scatter_grid();
     sync();
-    if (P.mode == MODE_STEP && ai_plans(s.ai) && !P.partial) s.flood_base_rows(-1, tid, nth);
+    if (P.mode == MODE_STEP && s.plans() && !P.partial) s.flood_base_rows(-1, tid, nth);
     // the agents' action rows of the units that may act, fetched by the whole group (the leader never waits on HBM)
-    if (P.mode == MODE_STEP)
+    if (P.mode == MODE_STEP && s.ai1 == AI_NONE)  // a scripted player 0 reads no action rows
         s.prefetch_actions(P.pact ? nullptr : P.actions + (size_t)env0 * P.HW * 7, P.pact ? P.pact + (size_t)env0 * P.HW : nullptr, tid, nth);
     sync();
 
@@ -324,14 +326,14 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         uint32_t* pm = P.pmask + (size_t)env0 * P.HW * 3;
         for (int k = tid; k < nviews * P.HW * 3; k += nth) pm[k] = 0;
     }
-    if (P.cost && ai_plans(s.ai)) {
+    if (P.cost && s.plans()) {
         const int n = s.hdr->nunits;
         int mine = 0;
         for (int i = tid; i < n; i += nth) mine += s.u[i].player == 1 && s.u[i].a_type < 0 && ut_can_move(s.u[i].type);
         if (mine) group_add(&s.st->nidle, mine);
     }
     sync();  // zero-fill before patches (and umask complete)
-    if (P.cost && tid == 0) P.cost[g] = ai_plans(s.ai) ? (uint32_t)((volatile St*)s.st)->nidle : 0u;
+    if (P.cost && tid == 0) P.cost[g] = s.plans() ? (uint32_t)((volatile St*)s.st)->nidle : 0u;
     if (P.next_actions)
         for (int v = 0; v < nviews; v++)
             sample_actions(s, v, umask, P.next_actions + (size_t)(env0 + v) * P.HW * 7, P.seed, P.counter, (uint32_t)(env0 + v), tid, nth);

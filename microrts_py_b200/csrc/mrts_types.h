@@ -83,7 +83,7 @@ enum { UF_DEAD = 1, UF_THIS_STEP = 2, UF_LISTED = 4 /* scratch mark of fill_with
        UF_AA_ATTACK = 8 /* scripted bot: the unit's abstract-action entry is an Attack */ };
 
 // abstract action of the scripted bots (J/ai/abstraction/{Train,Build,Harvest,Attack}.java)
-enum { AA_TRAIN = 0, AA_BUILD = 1, AA_HARVEST = 2, AA_ATTACK = 3 };
+enum { AA_TRAIN = 0, AA_BUILD = 1, AA_HARVEST = 2, AA_ATTACK = 3, AA_KIND_MASK = 15, AA_OWNER0 = 16 /* stored entries only */ };
 struct AbstractAct {  // 12 bytes; table order = LinkedHashMap insertion order (AbstractionLayerAI.java:36)
     uint16_t unit;    // uid
     uint8_t kind;

@@ -1,1 +1,1 @@
-from .vec_env import MicroRTSGridModeVecEnv, unit_type_table  # noqa: F401
+from .vec_env import MicroRTSBotVecEnv, MicroRTSGridModeVecEnv, unit_type_table  # noqa: F401

@@ -21,6 +21,8 @@ Extra keyword-only arguments (all default to the reference's behaviour):
                 two alternating buffers per output (as with ``zero_copy``), handed out READ-ONLY: the
                 library remembers what each buffer holds and rewrites only the cells that changed
                 (mrts_*_host_slot), so they must come back unmodified -- copy before editing
+  ai1s          scripted player 0 per bot env (``microrts_ai`` factories, ``None`` = the agent): bot vs bot as in
+                the reference's JNIBotClient; the action rows of those envs are ignored
   fuse_mask     compute the action mask of the resulting state inside ``step`` (one launch,
                 the state is staged once); ``get_action_mask`` then only hands it out
 """
@@ -37,7 +39,7 @@ import torch
 from .. import _capi
 from ..maps import MapTemplate, load_map
 from ..microrts_ai import DeviceAI
-from ..spaces import Box, MultiDiscrete
+from ..spaces import Box, Discrete, MultiDiscrete
 
 # ---------------------------------------------------------------------------------------------
 # UnitTypeTable() = VERSION_ORIGINAL + MOVE_CONFLICT_RESOLUTION_CANCEL_BOTH (J/rts/units/
@@ -139,6 +141,7 @@ class MicroRTSGridModeVecEnv:
         microrts_path=None,
         threads_per_game=0,
         staged_units=0,
+        ai1s=None,
     ):
         self.num_selfplay_envs = num_selfplay_envs
         self.num_bot_envs = num_bot_envs
@@ -190,6 +193,16 @@ class MicroRTSGridModeVecEnv:
             if not isinstance(a, DeviceAI):
                 raise NotImplementedError(f"ai2s entry {ai2!r} has no device implementation (use microrts_py_b200.microrts_ai)")
             ai_ids.append(a.ai_id)
+        # bot vs bot (JNIBotClient, MicroRTSBotVecEnv): scripted player 0 per bot env; its action rows are ignored
+        ai1_ids = None
+        if ai1s is not None:
+            assert len(ai1s) == num_bot_envs, "for each bot environment, a player-0 ai (or None for the agent) should be provided"
+            ai1_ids = []
+            for ai1 in ai1s:
+                a = ai1(None) if callable(ai1) else ai1
+                if a is not None and not isinstance(a, DeviceAI):
+                    raise NotImplementedError(f"ai1s entry {ai1!r} has no device implementation (use microrts_py_b200.microrts_ai)")
+                ai1_ids.append(-1 if a is None else a.ai_id)
 
         # ---- device
         if not torch.cuda.is_available():
@@ -212,7 +225,7 @@ class MicroRTSGridModeVecEnv:
         cfg, self._keep, cycle_idx = _capi.make_config(
             num_selfplay_envs, num_bot_envs, max_steps, partial_obs, templates, ai_ids,
             none_mode=_capi.NONE_FORK, device=dev_index, elem_bytes=self._np_dtype.itemsize, threads_per_game=threads_per_game, staged_units=staged_units,
-            cycle_templates=cycle_templates,
+            cycle_templates=cycle_templates, bot_ai1=ai1_ids,
         )  # fmt: skip
         h = C.c_void_p()
         _capi.check(self._lib.mrts_create(C.byref(cfg), C.byref(h)))
@@ -420,6 +433,38 @@ class MicroRTSGridModeVecEnv:
             _capi.check(self._lib.mrts_sample_actions(self._h, _ptr(self._d_actions), C.c_uint64(self._sample_seed if seed is None else seed), self._stream()))
         return self._d_actions
 
+    def step_into(self, actions, obs, mask=None, raw_rewards=None, done=None, next_actions=None, seed: Optional[int] = None):
+        """gameStep + getMasks of the resulting state written straight into the caller's device tensors --
+        e.g. ``step_into(a, buf.obs[t + 1], buf.mask[t + 1], buf.raw[t], buf.done[t])`` for a PPO rollout
+        buffer (the consumer loop of experiments/ppo_gridnet.py:459-480 without a host hop or an extra copy).
+        ``obs`` (N,H,W,P) and ``mask`` (N,H*W,78) have the env's dtype, ``raw_rewards`` (N,6) float64, ``done``
+        (N,) uint8, ``next_actions`` (N,H*W,7) int32 receives a masked-uniform random action grid for the
+        new state (mrts_step_ex).  All contiguous, on the env's device; nothing is returned or synchronised."""
+        self._check_open()
+
+        def chk(t, shape, dtype, name):
+            if t is None:
+                return None
+            if not isinstance(t, torch.Tensor) or t.device != self.device or t.dtype != dtype or tuple(t.shape) != tuple(shape) or not t.is_contiguous():
+                raise ValueError(f"{name}: need a contiguous {dtype} tensor of shape {tuple(shape)} on {self.device}")
+            return t
+
+        N = self.num_envs
+        a = chk(actions, self._shape_act, torch.int32, "actions")
+        if a is None:
+            raise ValueError("actions is required")
+        io = _capi.StepIOC()
+        io.actions = a.data_ptr()
+        io.obs = chk(obs, self._shape_obs, self._t_dtype, "obs").data_ptr() if obs is not None else None
+        io.mask = chk(mask, self._shape_mask, self._t_dtype, "mask").data_ptr() if mask is not None else None
+        io.reward = chk(raw_rewards, (N, 6), torch.float64, "raw_rewards").data_ptr() if raw_rewards is not None else None
+        io.done = chk(done, (N,), torch.uint8, "done").data_ptr() if done is not None else None
+        io.next_actions = chk(next_actions, self._shape_act, torch.int32, "next_actions").data_ptr() if next_actions is not None else None
+        io.seed = self._sample_seed if seed is None else seed
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.mrts_step_ex(self._h, C.byref(io), self._stream()))
+        self._d_mask, self._mask_valid = (mask, True) if mask is not None else (None, False)
+
     def getattr_depth_check(self, name, already_found):
         if hasattr(self, name) and already_found:
             return "{0}.{1}".format(type(self).__module__, type(self).__name__)
@@ -450,6 +495,52 @@ class MicroRTSGridModeVecEnv:
         rows = np.zeros((cap, 12), np.int32)
         n = _capi.check(self._lib.mrts_export_state(self._h, game, hdr.ctypes.data_as(C.c_void_p), rows.ctypes.data_as(C.c_void_p), cap, self._stream()))
         return hdr, rows[:n].copy()
+
+
+class MicroRTSBotVecEnv(MicroRTSGridModeVecEnv):
+    """Bot-vs-bot games, rewards and dones only (gym_microrts/envs/vec_env.py:1104-1236 over
+    J/tests/JNIBotClient.java:108-134): ``ai1s[i]`` plays player 0 and ``ai2s[i]`` player 1 of env i, both on
+    the full state; ``step`` ignores its argument and returns ``np.ones((N, 2))`` as the observation, the
+    weighted reward of player 0, done and ``[{"raw_rewards": ...}]`` exactly like the reference."""
+
+    def __init__(self, ai1s=[], ai2s=[], partial_obs=False, max_steps=2000, render_theme=2, map_paths="maps/10x10/basesTwoWorkers10x10.xml",
+                 reward_weight=np.array([0.0, 1.0, 0.0, 0.0, 0.0, 5.0]), autobuild=False, jvm_args=[], *, device=None, microrts_path=None):
+        assert len(ai1s) == len(ai2s), "for each environment, a microrts ai should be provided"
+        paths = [map_paths] if isinstance(map_paths, str) else list(map_paths)
+        if len(paths) != 1 and len(paths) != len(ai1s):  # the Java client reads mapPaths[i] per env (JNIGridnetVecClient.java:168)
+            raise ValueError("map_paths: one path, or one per environment")
+        super().__init__(0, len(ai2s), partial_obs=False, max_steps=max_steps, render_theme=render_theme, ai2s=list(ai2s), map_paths=paths,
+                         reward_weight=reward_weight, device=device, microrts_path=microrts_path, ai1s=list(ai1s), fuse_mask=False)
+        self.ai1s = ai1s
+        self.partial_obs = partial_obs  # JNIBotClient ignores it: both bots see the whole state
+        if partial_obs:
+            self.num_planes = [5, 5, 3, len(self.utt["unitTypes"]) + 1, 6, 2, 2]
+        self.observation_space = Discrete(2)
+        self.action_space = Discrete(2)
+        N = self.num_envs
+        self._raw = torch.empty((N, 6), dtype=torch.float64, device=self.device)
+        self._done = torch.empty((N,), dtype=torch.uint8, device=self.device)
+
+    def reset(self):
+        self._check_open()
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.mrts_reset(self._h, None, None, self._stream()))
+        return np.ones((self.num_envs, 2))
+
+    def step_async(self, actions):
+        self.actions = actions
+
+    def step_wait(self):
+        self._check_open()
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.mrts_step(self._h, None, None, None, _ptr(self._raw), _ptr(self._done), self._stream()))
+        reward = self._raw.cpu().numpy()
+        done = self._done.cpu().numpy().astype(np.bool_)
+        infos = [{"raw_rewards": item} for item in reward]
+        return np.ones((self.num_envs, 2)), reward @ self.reward_weight, done, infos
+
+    def get_action_mask(self):
+        raise NotImplementedError("MicroRTSBotVecEnv has no agent: the reference's inherited get_action_mask() fails in getMasks (no clients)")
 
 
 class _LazyInfos(Sequence):

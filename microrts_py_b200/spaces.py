@@ -10,7 +10,7 @@ from __future__ import annotations
 import numpy as np
 
 try:  # pragma: no cover - gym is absent in the build image
-    from gym.spaces import Box, MultiDiscrete  # type: ignore
+    from gym.spaces import Box, Discrete, MultiDiscrete  # type: ignore
 except Exception:  # noqa: BLE001
 
     class _Space:
@@ -55,3 +55,17 @@ except Exception:  # noqa: BLE001
 
         def __repr__(self):
             return f"MultiDiscrete({self.nvec})"
+
+    class Discrete(_Space):
+        def __init__(self, n):
+            self.n = int(n)
+            super().__init__((), np.int64)
+
+        def sample(self):
+            return int(self._rng.integers(0, self.n))
+
+        def contains(self, x):
+            return 0 <= int(x) < self.n
+
+        def __repr__(self):
+            return f"Discrete({self.n})"

@@ -185,9 +185,11 @@ struct VecEnv {
     int planes = 29;
     std::vector<MapTemplate> maps;  // one per env (self-play uses maps[2g])
     std::vector<int> ai_ids;
+    std::vector<int> ai1_ids;  // JNIBotClient games (bot vs bot): the scripted player 0 per bot env, -1 = the agent plays
     struct Game {
         GameState gs;
         std::unique_ptr<BotAI> bot;  // bot envs only
+        std::unique_ptr<BotAI> bot1; // JNIBotClient games only: ai1
         long long next_id = 0;
     };
     std::vector<Game> selfplay;  // num_selfplay/2
@@ -199,6 +201,7 @@ struct VecEnv {
     int threads = 1;
 
     void init();
+    int ai1_of(int b) const { return b < (int)ai1_ids.size() ? ai1_ids[b] : -1; }
     void reset(int32_t* obs);
     void get_masks(int32_t* mask78, int32_t* source_unit_mask);
     void step(const int32_t* actions, int32_t* obs, double* rewards, uint8_t* done);
@@ -209,7 +212,7 @@ struct VecEnv {
 
    private:
     void observe(const GameState& view, const GameState& truth, int player, int32_t* obs_out) const;
-    void reset_game(Game& g, const MapTemplate& m, int ai_id);
+    void reset_game(Game& g, const MapTemplate& m, int ai_id, int ai1_id = -1);
     void step_selfplay(int g, const int32_t* actions, int32_t* obs, double* rewards, uint8_t* done);
     void step_bot(int b, const int32_t* actions, int32_t* obs, double* rewards, uint8_t* done);
     std::vector<int32_t> gather_actions(int env, const int32_t* actions, const GameState& view, int player) const;

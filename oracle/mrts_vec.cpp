@@ -23,13 +23,17 @@ void VecEnv::init() {
     // JNIGridnetClient / SelfPlay constructors only load the map; gs exists after reset().
 }
 
-void VecEnv::reset_game(Game& g, const MapTemplate& m, int ai_id) {
+void VecEnv::reset_game(Game& g, const MapTemplate& m, int ai_id, int ai1_id) {
     // PhysicalGameState.load + new GameState (JNIGridnetClient.java:232-233); Unit.next_ID is a
     // JVM-wide static in the reference but never observable -- kept per game here.
     g.gs = make_game(m, none_mode, &g.next_id);
     if (ai_id >= 0) {
         g.bot = make_bot(ai_id);  // ai2 = ai2.clone(); ai2.reset()  (JNIGridnetClient.java:230-231)
         g.bot->reset();
+    }
+    if (ai1_id >= 0) {  // JNIBotClient.reset, JNIBotClient.java:146-150
+        g.bot1 = make_bot(ai1_id);
+        g.bot1->reset();
     }
 }
 
@@ -70,7 +74,7 @@ void VecEnv::reset(int32_t* obs) {
         }
     }
     for (int b = 0; b < num_bot; b++) {
-        reset_game(botgames[b], maps[num_selfplay + b], ai_ids[b]);
+        reset_game(botgames[b], maps[num_selfplay + b], ai_ids[b], ai1_of(b));
         const GameState& gs = botgames[b].gs;
         if (partial_obs) observe(gs.pogs(0), gs, 0, obs + (num_selfplay + b) * stride);
         else observe(gs, gs, 0, obs + (num_selfplay + b) * stride);
@@ -91,7 +95,7 @@ void VecEnv::swap_map_and_reset(int env, const MapTemplate& m, int32_t* obs) {
     } else {  // clients[b].mapPath = ...; reset(0)  (JNIGridnetClient.java:228-247)
         const int b = env - num_selfplay;
         maps[env] = m;
-        reset_game(botgames[b], maps[env], ai_ids[b]);
+        reset_game(botgames[b], maps[env], ai_ids[b], ai1_of(b));
         const GameState& gs = botgames[b].gs;
         if (partial_obs) observe(gs.pogs(0), gs, 0, obs + env * stride);
         else observe(gs, gs, 0, obs + env * stride);
@@ -210,10 +214,16 @@ void VecEnv::step_bot(int b, const int32_t* actions, int32_t* obs, double* rewar
     }
     const GameState& p1gs = partial_obs ? v1 : gs;
     const GameState& p2gs = partial_obs ? v2 : gs;
-    std::vector<int32_t> rows = gather_actions(env, actions, p1gs, 0);
-    PlayerAction pa1 = from_vector_action(p1gs, rows.data(), (int)rows.size() / 8, 0);
-    p1gs.fill_with_nones(pa1, 0, 1);
-    PlayerAction pa2 = game.bot->get_action(1, p2gs);
+    PlayerAction pa1, pa2;
+    if (game.bot1) {  // JNIBotClient.gameStep, JNIBotClient.java:108-111: both bots act on the full state
+        pa1 = game.bot1->get_action(0, gs);
+        pa2 = game.bot->get_action(1, gs);
+    } else {
+        std::vector<int32_t> rows = gather_actions(env, actions, p1gs, 0);
+        pa1 = from_vector_action(p1gs, rows.data(), (int)rows.size() / 8, 0);
+        p1gs.fill_with_nones(pa1, 0, 1);
+        pa2 = game.bot->get_action(1, p2gs);
+    }
     gs.issue_safe(pa1);
     gs.issue_safe(pa2);
     TraceSnapshot te;
@@ -227,7 +237,7 @@ void VecEnv::step_bot(int b, const int32_t* actions, int32_t* obs, double* rewar
     observe(p1gs, gs, 0, obs + env * stride);
     // JNIGridnetVecClient.gameStep, :268-286
     if (dn[0] || env_steps[env] >= max_steps) {
-        reset_game(game, maps[env], ai_ids[b]);
+        reset_game(game, maps[env], ai_ids[b], ai1_of(b));
         if (partial_obs) observe(gs.pogs(0), gs, 0, obs + env * stride);
         else observe(gs, gs, 0, obs + env * stride);
         dn[0] = true;

@@ -95,6 +95,12 @@ void orc_vec_add_env(void* h, int W, int H, const uint8_t* terrain, int res0, in
     v->maps.push_back(make_template(W, H, terrain, res0, res1, nunits, units7));
     if (ai_id >= 0) v->ai_ids.push_back(ai_id);
 }
+// JNIBotClient games: scripted player 0 of bot env b (call before orc_vec_init)
+void orc_vec_set_ai1(void* h, int b, int ai1_id) {
+    VecEnv* v = (VecEnv*)h;
+    if ((int)v->ai1_ids.size() <= b) v->ai1_ids.resize(b + 1, -1);
+    v->ai1_ids[b] = ai1_id;
+}
 void orc_vec_init(void* h) { ((VecEnv*)h)->init(); }
 void orc_vec_reset(void* h, int32_t* obs) { ((VecEnv*)h)->reset(obs); }
 void orc_vec_masks(void* h, int32_t* mask78, int32_t* source) { ((VecEnv*)h)->get_masks(mask78, source); }

@@ -37,6 +37,7 @@ def lib():
         L.orc_vec_create.argtypes = [C.c_int] * 6
         L.orc_vec_add_env.argtypes = [vp, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.orc_vec_init.argtypes = [vp]
+        L.orc_vec_set_ai1.argtypes = [vp, C.c_int, C.c_int]
         L.orc_vec_reset.argtypes = [vp, C.c_void_p]
         L.orc_vec_masks.argtypes = [vp, C.c_void_p, C.c_void_p]
         L.orc_vec_step.argtypes = [vp, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -128,7 +129,7 @@ class OracleBot:
 class OracleVecEnv:
     """JNIGridnetVecClient-level oracle: raw int32 obs, (N,HW,78) masks, (N,6) rewards, (N,) done."""
 
-    def __init__(self, num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=NONE_FORK, threads=1):
+    def __init__(self, num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=NONE_FORK, threads=1, ai1_ids=None):
         self.L = lib()
         self.N = num_selfplay + num_bot
         assert len(templates) == self.N and len(ai_ids) == num_bot
@@ -138,6 +139,8 @@ class OracleVecEnv:
             units = np.ascontiguousarray(t.units, np.int32)
             ai = ai_ids[e - num_selfplay] if e >= num_selfplay else -1
             self.L.orc_vec_add_env(self.h, t.width, t.height, _p(terr), t.resources[0], t.resources[1], len(units), _p(units), ai)
+        for b, a1 in enumerate(ai1_ids or ()):  # JNIBotClient games (MicroRTSBotVecEnv): scripted player 0
+            self.L.orc_vec_set_ai1(self.h, b, a1)
         self.L.orc_vec_init(self.h)
         self.H, self.W = templates[0].height, templates[0].width
         self.P = self.L.orc_vec_planes(self.h)

@@ -51,26 +51,27 @@ class _HostEnv:
         pass
 
 
-def make_env(backend, num_selfplay_envs=0, num_bot_envs=0, partial_obs=False, max_steps=2000, ai2s=(), map_paths=(), reward_weight=(0.0, 1.0, 0.0, 0.0, 0.0, 5.0), cycle_maps=(), **kw):
+def make_env(backend, num_selfplay_envs=0, num_bot_envs=0, partial_obs=False, max_steps=2000, ai2s=(), map_paths=(), reward_weight=(0.0, 1.0, 0.0, 0.0, 0.0, 5.0), cycle_maps=(), ai1s=None, **kw):
     n = num_selfplay_envs + num_bot_envs
     paths = list(map_paths) * n if len(map_paths) == 1 else list(map_paths)
     if backend == "cuda":
         from microrts_py_b200.envs import MicroRTSGridModeVecEnv
 
         return MicroRTSGridModeVecEnv(
-            num_selfplay_envs, num_bot_envs, partial_obs=partial_obs, max_steps=max_steps, ai2s=list(ai2s), map_paths=paths, reward_weight=np.asarray(reward_weight), cycle_maps=list(cycle_maps), **kw
+            num_selfplay_envs, num_bot_envs, partial_obs=partial_obs, max_steps=max_steps, ai2s=list(ai2s), map_paths=paths, reward_weight=np.asarray(reward_weight), cycle_maps=list(cycle_maps), ai1s=ai1s, **kw
         )
     t = templates_for(paths)
     ids = [AI_IDS[a] for a in ai2s]
+    ids1 = [AI_IDS[a] for a in ai1s] if ai1s is not None else None  # bot vs bot (JNIBotClient)
     if backend == "oracle":
         from oracle.oracle_py import OracleVecEnv
 
-        eng = OracleVecEnv(num_selfplay_envs, num_bot_envs, max_steps, partial_obs, t, ids)
+        eng = OracleVecEnv(num_selfplay_envs, num_bot_envs, max_steps, partial_obs, t, ids, ai1_ids=ids1)
         return _HostEnv(eng, n, t[0].height, t[0].width, reward_weight, num_bot_envs=num_bot_envs, cycle_templates=templates_for(list(cycle_maps)))
     elif backend == "hostsim":
         from tests.hostsim import HostSimVecEnv
 
-        eng = HostSimVecEnv(num_selfplay_envs, num_bot_envs, max_steps, partial_obs, t, ids, cycle_templates=templates_for(list(cycle_maps)))
+        eng = HostSimVecEnv(num_selfplay_envs, num_bot_envs, max_steps, partial_obs, t, ids, cycle_templates=templates_for(list(cycle_maps)), ai1_ids=ids1)
     else:
         raise ValueError(backend)
     return _HostEnv(eng, n, t[0].height, t[0].width, reward_weight)

@@ -44,10 +44,10 @@ def _p(a):
 class HostSimVecEnv:
     """Same call surface as oracle.oracle_py.OracleVecEnv."""
 
-    def __init__(self, num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=1, elem_bytes=4, cycle_templates=()):
+    def __init__(self, num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=1, elem_bytes=4, cycle_templates=(), ai1_ids=None):
         self.L = lib()
         cfg, self._keep, cyc = make_config(
-            num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=none_mode, elem_bytes=elem_bytes, cycle_templates=list(cycle_templates)
+            num_selfplay, num_bot, max_steps, partial_obs, templates, ai_ids, none_mode=none_mode, elem_bytes=elem_bytes, cycle_templates=list(cycle_templates), bot_ai1=ai1_ids
         )
         h = C.c_void_p()
         rc = self.L.hs_create(C.byref(cfg), C.byref(h))

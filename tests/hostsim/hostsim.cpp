@@ -35,6 +35,7 @@ static void pass(hs_env* e, int mode, const int32_t* actions, void* obs, void* m
     P.unit_pool = e->S.units.data();
     P.game_map = e->S.game_map.data();
     P.game_ai = e->S.game_ai.data();
+    P.game_ai1 = e->S.game_ai1.data();
     P.mode = mode;
     P.actions = actions;
     P.obs = obs;

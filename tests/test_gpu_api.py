@@ -10,7 +10,7 @@ from microrts_py_b200 import microrts_ai
 from tests.common import GROUPS, MAP_8, MAP_16, MAP_32, sample_actions, templates_for
 
 pytestmark = pytest.mark.gpu
-P, W = microrts_ai.passiveAI, microrts_ai.workerRushAI
+P, W, LR = microrts_ai.passiveAI, microrts_ai.workerRushAI, microrts_ai.lightRushAI
 
 
 def _env(*a, **k):
@@ -229,4 +229,64 @@ def test_cycle_maps_on_a_large_slab_follow_the_reference_order(mode):
         np.testing.assert_array_equal(r, r2)
         ended += int(d.sum())
     assert ended >= 2 * n
+    env.close()
+
+
+def test_step_into_writes_a_rollout_buffer_in_place():
+    """step + masks written straight into slices of a preallocated rollout buffer
+    (no intermediate tensors), next actions drawn on the device; every slice equals the oracle."""
+    import torch
+
+    ais = [W, P, W, LR]
+    n, T = len(ais), 40
+    env = _env(0, n, max_steps=25, ai2s=ais, map_paths=[MAP_8], return_torch=True, seed=4)
+    ref = _oracle(0, ais, MAP_8, max_steps=25)
+    dev = env.device
+    obs = torch.zeros((T + 1, n, 8, 8, 29), dtype=torch.int32, device=dev)
+    mask = torch.zeros((T + 1, n, 64, 78), dtype=torch.int32, device=dev)
+    raw = torch.zeros((T, n, 6), dtype=torch.float64, device=dev)
+    done = torch.zeros((T, n), dtype=torch.uint8, device=dev)
+    act = torch.zeros((T + 1, n, 64, 7), dtype=torch.int32, device=dev)
+    obs[0].copy_(env.reset())
+    mask[0].copy_(env.get_action_mask())
+    act[0].copy_(env.sample_actions())
+    for t in range(T):
+        env.step_into(act[t], obs[t + 1], mask[t + 1], raw[t], done[t], next_actions=act[t + 1])
+    with pytest.raises(ValueError):
+        env.step_into(act[0], obs[1][:, :4])  # wrong shape
+    o, m, r, d, a = (x.cpu().numpy() for x in (obs, mask, raw, done, act))
+    np.testing.assert_array_equal(o[0], ref.reset())
+    for t in range(T):
+        np.testing.assert_array_equal(m[t], ref.get_masks()[0], err_msg=f"mask {t}")
+        o2, r2, d2 = ref.step(a[t])
+        np.testing.assert_array_equal(o[t + 1], o2, err_msg=f"obs {t}")
+        np.testing.assert_array_equal(r[t], r2)
+        np.testing.assert_array_equal(d[t], d2)
+    assert d.sum() >= n
+    env.close()
+
+
+def test_bot_vec_env_returns_rewards_and_dones_like_the_reference():
+    """MicroRTSBotVecEnv (vec_env.py:1104-1236): np.ones observations, player 0's weighted reward, done,
+    raw rewards in infos; the argument of step() is ignored."""
+    from microrts_py_b200.envs import MicroRTSBotVecEnv
+    from tests.backends import make_env
+
+    ai1s, ai2s = [W, LR, P, LR], [LR, W, W, LR]
+    rw = np.array([10.0, 1.0, 1.0, 0.2, 1.0, 4.0])
+    env = MicroRTSBotVecEnv(ai1s=ai1s, ai2s=ai2s, max_steps=300, map_paths=[MAP_8], reward_weight=rw)
+    ref = make_env("oracle", 0, 4, max_steps=300, ai2s=ai2s, ai1s=ai1s, map_paths=[MAP_8], reward_weight=rw)
+    assert env.reset().shape == (4, 2) and env.observation_space.n == 2
+    ref.reset()
+    a = np.zeros((4, 64, 7), np.int32)
+    ended = 0
+    for t in range(700):
+        o, r, d, infos = env.step(None)
+        _, r2, d2, infos2 = ref.step(a)
+        assert o.shape == (4, 2) and (o == 1).all()
+        np.testing.assert_array_equal(r, r2, err_msg=f"reward {t}")
+        np.testing.assert_array_equal(d, d2, err_msg=f"done {t}")
+        np.testing.assert_array_equal(np.stack([i["raw_rewards"] for i in infos]), np.stack([i["raw_rewards"] for i in infos2]))
+        ended += int(d.sum())
+    assert ended >= 4
     env.close()

@@ -104,3 +104,67 @@ def test_cycle_maps_match_the_reference_rotation(engine, case):
 def test_cycle_maps_with_both_env_kinds_are_refused():
     with pytest.raises((NotImplementedError, ValueError)):
         make_env("hostsim", 2, 1, ai2s=[P], map_paths=[MAP_8], cycle_maps=[MAP_8])
+
+
+# Long scripted-bot games (many path searches, full-length episodes, several resets), hostsim only: the
+# CUDA build runs the same cases through the shorter table above and test_gpu_api's large slabs.
+STRESS = {
+    # name: (map, num_selfplay, ai2s, partial_obs, max_steps, steps, eps, seed)
+    "wrush16_long": (MAP_16, 0, [W] * 12, False, 2000, 2300, 0.02, 1),
+    "wrush8_long": (MAP_8, 0, [W] * 16, False, 600, 1300, 0.05, 2),
+    "wrush16_partial_long": (MAP_16, 0, [W] * 8, True, 1000, 1200, 0.02, 3),
+    "mix10_long": ("maps/10x10/basesWorkers10x10.xml", 4, [W, LR] * 5, False, 800, 1200, 0.05, 4),
+    "lrush16_long": (MAP_16, 0, [LR] * 8, False, 2000, 2300, 0.02, 5),
+}
+
+
+@pytest.mark.parametrize("case", list(STRESS))
+def test_long_scripted_bot_games_match_oracle(case):
+    mp, nsp, ais, partial, max_steps, steps, eps, seed = STRESS[case]
+    kw = dict(num_selfplay_envs=nsp, num_bot_envs=len(ais), partial_obs=partial, max_steps=max_steps, ai2s=ais, map_paths=[mp], reward_weight=RW)
+    ref = make_env("oracle", **kw)
+    env = make_env("hostsim", **kw)
+    rng = np.random.default_rng(seed)
+    np.testing.assert_array_equal(env.reset(), ref.reset())
+    for t in range(steps):
+        m_ref = ref.get_action_mask()
+        np.testing.assert_array_equal(env.get_action_mask(), m_ref, err_msg=f"{case}: mask at step {t}")
+        a = sample_actions(m_ref, rng, eps)
+        o, r, d, _ = env.step(a)
+        o2, r2, d2, _ = ref.step(a)
+        np.testing.assert_array_equal(o, o2, err_msg=f"{case}: observation at step {t}")
+        np.testing.assert_array_equal(r, r2, err_msg=f"{case}: reward at step {t}")
+        np.testing.assert_array_equal(d, d2, err_msg=f"{case}: done at step {t}")
+
+
+# Bot vs bot (J/tests/JNIBotClient.java:108-134 under MicroRTSBotVecEnv): both players
+# scripted, both acting on the full state, player 0's action issued first.  The reference returns only
+# rewards / dones; the observation of the same state is compared as well (it exposes every unit).
+BOTVBOT = {
+    # name: (map, ai1s, ai2s, max_steps, steps)
+    "wr_vs_wr16": (MAP_16, [W, W], [W, W], 600, 700),
+    "mixed8": (MAP_8, [W, LR, P, W, LR, LR], [LR, W, W, P, LR, P], 300, 700),
+    "lr_vs_wr16": (MAP_16, [LR, W, LR], [W, LR, LR], 1500, 1700),
+    "nobase8": ("maps/8x8/noBases8x8.xml", [LR, W], [W, LR], 250, 400),
+}
+
+
+@pytest.mark.parametrize("engine", _engines())
+@pytest.mark.parametrize("case", list(BOTVBOT))
+def test_bot_vs_bot_games_match_oracle(engine, case):
+    mp, ai1s, ai2s, max_steps, steps = BOTVBOT[case]
+    kw = dict(num_selfplay_envs=0, num_bot_envs=len(ai2s), max_steps=max_steps, ai2s=ai2s, ai1s=ai1s, map_paths=[mp], reward_weight=RW)
+    ref = make_env("oracle", **kw)
+    env = make_env(engine, **kw)
+    np.testing.assert_array_equal(env.reset(), ref.reset())
+    n_done = 0
+    a = np.zeros((len(ai2s), ref.height * ref.width, 7), np.int32)  # ignored by both
+    for t in range(steps):
+        o, r, d, info = env.step(a)
+        o2, r2, d2, info2 = ref.step(a)
+        np.testing.assert_array_equal(np.stack([i["raw_rewards"] for i in info]), np.stack([i["raw_rewards"] for i in info2]), err_msg=f"{case}: raw rewards at step {t}")
+        np.testing.assert_array_equal(d, d2, err_msg=f"{case}: done at step {t}")
+        np.testing.assert_array_equal(o, o2, err_msg=f"{case}: observation at step {t}")
+        n_done += int(d.sum())
+    assert n_done > 0
+    env.close()

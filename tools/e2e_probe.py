@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Where an end-to-end step (bench.py e2e loop) spends its time: policy stand-in, its action grid
+device->host, env.step (mrts_step_host_slot).  Usage: python tools/e2e_probe.py [workload] [envs]"""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+from microrts_py_b200 import microrts_ai  # noqa: E402
+from microrts_py_b200.envs import MicroRTSGridModeVecEnv  # noqa: E402
+
+name = sys.argv[1] if len(sys.argv) > 1 else "cfg2_rollout16"
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
+wl = bench.workload_setup(name, None)
+nsp = int(n * (wl["nsp"] / wl["n"])) // 2 * 2
+nbot = n - nsp
+ai2s = [getattr(microrts_ai, wl["bot_names"][i * wl["nbot"] // nbot]) for i in range(nbot)] if nbot else []
+env = MicroRTSGridModeVecEnv(nsp, nbot, partial_obs=wl["partial"], max_steps=wl["max_steps"], ai2s=ai2s, map_paths=[wl["map"]], host_transport=True, seed=3)
+a_host = torch.zeros((n, env.height * env.width, 7), dtype=torch.int32).pin_memory()
+env.reset()
+T = {"sample": 0.0, "actions_d2h": 0.0, "step": 0.0}
+K = 40
+for it in range(K + 5):
+    if it == 5:
+        T = dict.fromkeys(T, 0.0)
+    t0 = time.perf_counter()
+    a = env.sample_actions()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    a_host.copy_(a, non_blocking=True)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    env.step(a_host.numpy())
+    env.get_action_mask()
+    t3 = time.perf_counter()
+    T["sample"] += t1 - t0
+    T["actions_d2h"] += t2 - t1
+    T["step"] += t3 - t2
+tot = sum(T.values())
+print(f"{name} {n} envs: " + " | ".join(f"{k} {1e3 * v / K:.2f} ms" for k, v in T.items()) + f" | total {1e3 * tot / K:.2f} ms = {n * K / tot / 1e6:.2f} M env-steps/s")
