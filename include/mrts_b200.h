@@ -32,6 +32,8 @@ extern "C" {
 #define MRTS_AI_PASSIVE 0     /* ai.PassiveAI      (gym_microrts/microrts_ai.py:13-16) */
 #define MRTS_AI_WORKER_RUSH 1 /* ai.abstraction.WorkerRush (microrts_ai.py:19-22)      */
 #define MRTS_AI_LIGHT_RUSH 2  /* ai.abstraction.LightRush  (microrts_ai.py:25-28)      */
+#define MRTS_AI_PO_WORKER_RUSH 3 /* ai.abstraction.partialobservability.POWorkerRush (microrts_ai.py:37-40) */
+#define MRTS_AI_PO_LIGHT_RUSH 4  /* ai.abstraction.partialobservability.POLightRush  (microrts_ai.py:31-34) */
 
 /* One parsed map: what PhysicalGameState.load returns (J/rts/PhysicalGameState.java:54-65,685-711). */
 typedef struct mrts_map_template {

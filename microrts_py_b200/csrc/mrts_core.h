@@ -89,6 +89,8 @@ struct St {
     int rows_ready;  // the enterable-cell rows of this bot call are built (see astar_rows)
     int nidle;       // idle mobile units of the scripted bot after this step (launch-order hint)
     int nprod;       // pending PRODUCE assignments at load (capacity check)
+    int explore;     // the bot acting now is a PO* variant (bot_action)
+    int unobs_ready; // bitsC holds this bot call's not-observable cell bitmap (bot_melee)
     int timing_on;   // profiling aid (mrts_debug_timing): fill tp[]
     int tp[8];       // cycles: decode, bot census/puts, bot translate, issue agent, issue bot, cycle; then #searches, #expansions
     int rew[2][6];   // integer reward terms per player view (exact small integers)
@@ -1461,6 +1463,15 @@ struct Sim {
                 out.param = (int16_t)d;
                 return true;
             }
+            case AA_MOVE: {  // Move.java:53-59: findPath = findPathToPositionInRange(.., 0, ..)
+                int mv = o_astar(self, i, r.x + r.y * W, 0, vp);
+                if (mv >= 0 && action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
+                    out.type = T_MOVE;
+                    out.param = (int16_t)mv;
+                    return true;
+                }
+                return false;
+            }
             case AA_ATTACK: {  // Attack.java:50-65
                 int ti = find_uid(r.target, vp);
                 if (ti < 0) return false;
@@ -1493,6 +1504,7 @@ struct Sim {
                 if (u[i].res > 0) return find_uid(r.base, vp) < 0;
                 return find_uid(r.target, vp) < 0;
             case AA_ATTACK: return find_uid(r.target, vp) < 0;                     // Attack.java:30-33
+            case AA_MOVE: return u[i].x == r.x && u[i].y == r.y;                   // Move.java:32-34
         }
         return true;
     }
@@ -1608,6 +1620,58 @@ struct Sim {
             r.target = u[closest].uid;
             r.base = NO_UID;
             aa_put(r, i);
+        } else if (st->explore && vp >= 0) {
+            // PO*.meleeUnitBehavior (partialobservability/POWorkerRush.java:56-76): the state is a
+            // PartiallyObservableGameState (vp >= 0) and shows no enemy -> Move to the nearest cell that is not
+            // observable (row-major scan with strict <: lowest cell index among equal distances)
+            if (!st->unobs_ready) {  // bitsC (free until translate_actions): bit c = cell c is NOT within sight of an own unit
+#pragma unroll 1
+                for (int base = 0; base < HW; base += nl) {
+                    const int c = base + lane;
+                    bool seen = true;
+                    if (c < HW) {
+                        const int cx = c % W, cy = c / W;
+                        seen = false;
+#pragma unroll 1
+                        for (int j = 0; j < n && !seen; j++) {
+                            const Unit& o = u[j];
+                            if (o.player != player) continue;
+                            const int dx = o.x - cx, dy = o.y - cy, rr = ut_sight(o.type);
+                            seen = dx * dx + dy * dy <= rr * rr;
+                        }
+                    }
+#if defined(__CUDA_ARCH__)
+                    const unsigned word = wballot(!seen);
+                    if (lane == 0) bitsC[base >> 5] = word;
+#else
+                    if ((c & 31) == 0) bitsC[c >> 5] = 0;
+                    if (!seen) bitsC[c >> 5] |= 1u << (c & 31);
+#endif
+                }
+                st->unobs_ready = 1;
+                wsync();
+            }
+            int bestc = NO_KEY;
+#pragma unroll 1
+            for (int c = lane; c < HW; c += nl) {
+                if (!((bitsC[c >> 5] >> (c & 31)) & 1u)) continue;
+                const int dx = ux - c % W, dy = uy - c / W;
+                const int key = ((dx * dx + dy * dy) << 14) | c;
+                if (key < bestc) bestc = key;
+            }
+            bestc = wmin(bestc);
+            if (bestc != NO_KEY) {
+                const int c = bestc & 0x3FFF;
+                AbstractAct r;
+                r.unit = u[i].uid;
+                r.kind = AA_MOVE;
+                r.utype = -1;
+                r.x = (int16_t)(c % W);
+                r.y = (int16_t)(c / W);
+                r.target = NO_UID;
+                r.base = NO_UID;
+                aa_put(r, i);
+            }
         }
     }
     MRTS_HD void aa_harvest(int i, int target, int base) {
@@ -1903,8 +1967,11 @@ struct Sim {
     // the scripted opponent's PlayerAction for `player` -> pa2
     MRTS_HD void bot_action(int which, int player, int vp) {
         st->npa2 = 0;
-        if (which == AI_WORKER_RUSH) worker_rush(player, vp);
-        else if (which == AI_LIGHT_RUSH) light_rush(player, vp);
+        st->explore = ai_explores(which);
+        st->unobs_ready = 0;
+        wsync();
+        if (which == AI_WORKER_RUSH || which == AI_PO_WORKER_RUSH) worker_rush(player, vp);
+        else if (which == AI_LIGHT_RUSH || which == AI_PO_LIGHT_RUSH) light_rush(player, vp);
         else o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
     }
 

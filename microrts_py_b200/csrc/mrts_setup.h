@@ -118,7 +118,7 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
     P.elem = cfg->elem_bytes;
     P.has_bot = 0;
     for (int b = 0; b < cfg->num_bot_envs; b++) {
-        if (cfg->bot_ai[b] != MRTS_AI_PASSIVE && cfg->bot_ai[b] != MRTS_AI_WORKER_RUSH && cfg->bot_ai[b] != MRTS_AI_LIGHT_RUSH) {
+        if (cfg->bot_ai[b] < 0 || cfg->bot_ai[b] >= AI_COUNT) {
             err = "unsupported scripted opponent id";
             return MRTS_EINVAL;
         }
@@ -176,7 +176,7 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
         S.game_ai[g] = g < nsp ? (int8_t)AI_NONE : (int8_t)cfg->bot_ai[g - nsp];
         if (g >= nsp && cfg->bot_ai1 && cfg->bot_ai1[g - nsp] >= 0) {
             const int a1 = cfg->bot_ai1[g - nsp];
-            if (a1 != MRTS_AI_PASSIVE && a1 != MRTS_AI_WORKER_RUSH && a1 != MRTS_AI_LIGHT_RUSH) {
+            if (a1 >= AI_COUNT) {
                 err = "unsupported scripted player-0 id";
                 return MRTS_EINVAL;
             }

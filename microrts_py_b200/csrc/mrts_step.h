@@ -229,7 +229,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (tid == 0) {
         *(Sim*)(mem + L.sim) = s;
         St z;
-        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.rows_ready = z.nidle = 0;
+        z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.rows_ready = z.nidle = z.explore = z.unobs_ready = 0;
         z.winner = -1;
         z.timing_on = P.timing != nullptr;
         for (int k = 0; k < 8; k++) z.tp[k] = 0;

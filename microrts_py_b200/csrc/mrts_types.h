@@ -22,9 +22,11 @@ enum { D_UP = 0, D_RIGHT = 1, D_DOWN = 2, D_LEFT = 3 };
 enum { UT_RESOURCE = 0, UT_BASE = 1, UT_BARRACKS = 2, UT_WORKER = 3, UT_LIGHT = 4, UT_HEAVY = 5, UT_RANGED = 6, N_UTYPES = 7 };
 // how `new UnitAction(TYPE_NONE, d)` behaves: the fork forces parameter -1 (J/rts/UnitAction.java:149-154)
 enum { NONE_UPSTREAM = 0, NONE_FORK = 1 };
-enum { AI_NONE = -1, AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2 };
+enum { AI_NONE = -1, AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2, AI_PO_WORKER_RUSH = 3, AI_PO_LIGHT_RUSH = 4, AI_COUNT = 5 };
 // scripted opponents built on AbstractionLayerAI: abstract-action table in the blob, path searches
-MRTS_HD bool ai_plans(int ai) { return ai == AI_WORKER_RUSH || ai == AI_LIGHT_RUSH; }
+MRTS_HD bool ai_plans(int ai) { return ai >= AI_WORKER_RUSH && ai < AI_COUNT; }
+// the PO* variants (ai/abstraction/partialobservability/): same bot, melee units explore when no enemy is in view
+MRTS_HD bool ai_explores(int ai) { return ai == AI_PO_WORKER_RUSH || ai == AI_PO_LIGHT_RUSH; }
 
 MRTS_HD int dir_dx(int d) { return d == D_RIGHT ? 1 : (d == D_LEFT ? -1 : 0); }
 MRTS_HD int dir_dy(int d) { return d == D_DOWN ? 1 : (d == D_UP ? -1 : 0); }
@@ -83,7 +85,7 @@ enum { UF_DEAD = 1, UF_THIS_STEP = 2, UF_LISTED = 4 /* scratch mark of fill_with
        UF_AA_ATTACK = 8 /* scripted bot: the unit's abstract-action entry is an Attack */ };
 
 // abstract action of the scripted bots (J/ai/abstraction/{Train,Build,Harvest,Attack}.java)
-enum { AA_TRAIN = 0, AA_BUILD = 1, AA_HARVEST = 2, AA_ATTACK = 3, AA_KIND_MASK = 15, AA_OWNER0 = 16 /* stored entries only */ };
+enum { AA_TRAIN = 0, AA_BUILD = 1, AA_HARVEST = 2, AA_ATTACK = 3, AA_MOVE = 4, AA_KIND_MASK = 15, AA_OWNER0 = 16 /* stored entries only */ };
 struct AbstractAct {  // 12 bytes; table order = LinkedHashMap insertion order (AbstractionLayerAI.java:36)
     uint16_t unit;    // uid
     uint8_t kind;

@@ -8,6 +8,8 @@ returning the opponent.  In the reference the result is a Java ``ai.core.AI`` ob
   passiveAI     ai.PassiveAI             (J/ai/PassiveAI.java:41-45)
   workerRushAI  ai.abstraction.WorkerRush (J/ai/abstraction/WorkerRush.java:63-204)
   lightRushAI   ai.abstraction.LightRush  (J/ai/abstraction/LightRush.java:77-254)
+  POWorkerRush / POLightRush  the same two with the exploring melee behaviour of
+                J/ai/abstraction/partialobservability/PO{Worker,Light}Rush.java:42-78
 
 Every other factory of the reference (random, search-based or closed-jar bots) raises
 ``NotImplementedError`` with the reason.
@@ -36,6 +38,14 @@ def lightRushAI(utt=None):
     return DeviceAI("LightRush", 2)
 
 
+def POWorkerRush(utt=None):
+    return DeviceAI("POWorkerRush", 3)
+
+
+def POLightRush(utt=None):
+    return DeviceAI("POLightRush", 4)
+
+
 def _unsupported(name, why):
     def f(utt=None):
         raise NotImplementedError(f"{name}: {why}")
@@ -48,8 +58,6 @@ _RANDOM = "draws from an unseeded java.util.Random; not reproducible, outside th
 _SEARCH = "wall-clock-budgeted search / closed competition jar; outside the device hot path"
 randomBiasedAI = _unsupported("randomBiasedAI", _RANDOM)
 randomAI = _unsupported("randomAI", _RANDOM)
-POLightRush = _unsupported("POLightRush", "not built yet")
-POWorkerRush = _unsupported("POWorkerRush", "not built yet")
 for _n in ("naiveMCTSAI", "mixedBot", "rojo", "izanagi", "tiamat", "droplet", "guidedRojoA3N", "coacAI", "mayari"):
     globals()[_n] = _unsupported(_n, _SEARCH)
 del _n

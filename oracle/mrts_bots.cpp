@@ -107,19 +107,20 @@ struct AStar {
 };
 
 // ---------------------------------------------------------------- abstract actions
-enum { AA_TRAIN, AA_BUILD, AA_HARVEST, AA_ATTACK };
+enum { AA_TRAIN, AA_BUILD, AA_HARVEST, AA_ATTACK, AA_MOVE };
 struct AbstractAction {
     int kind;
     UnitP unit;
     int utype = -1;          // Train / Build
     bool completed_flag = false;  // Train
-    int x = 0, y = 0;        // Build
+    int x = 0, y = 0;        // Build / Move
     UnitP target, base;      // Harvest (target may be null) / Attack (target)
 };
 using AAP = std::shared_ptr<AbstractAction>;
 
 struct AbstractionLayerAI : BotAI {
     std::vector<AAP> actions;  // LinkedHashMap<Unit, AbstractAction>: insertion order, re-put keeps slot
+    bool explore = false;      // the PO* subclasses (ai/abstraction/partialobservability/): their meleeUnitBehavior override
     AStar pf;
 
     void reset() override { actions.clear(); }  // AbstractionLayerAI.java:53-55
@@ -161,6 +162,14 @@ struct AbstractionLayerAI : BotAI {
         a->base = base;
         put(a);
     }
+    void move(const UnitP& u, int x, int y) {  // AbstractionLayerAI.java:119-121
+        auto a = std::make_shared<AbstractAction>();
+        a->kind = AA_MOVE;
+        a->unit = u;
+        a->x = x;
+        a->y = y;
+        put(a);
+    }
     void attack(const UnitP& u, const UnitP& target) {
         auto a = std::make_shared<AbstractAction>();
         a->kind = AA_ATTACK;
@@ -177,6 +186,7 @@ struct AbstractionLayerAI : BotAI {
                 if (aa.unit->res > 0) return !gs.contains(aa.base.get());
                 return !gs.contains(aa.target.get());  // contains(null) is false
             case AA_ATTACK: return !gs.contains(aa.target.get());         // Attack.java:30-33
+            case AA_MOVE: return aa.unit->x == aa.x && aa.unit->y == aa.y; // Move.java:32-34
         }
         return true;
     }
@@ -273,6 +283,14 @@ struct AbstractionLayerAI : BotAI {
                 if (tgt->x == unit.x + 1 && tgt->y == unit.y) { out = act_dir(ty, D_RIGHT); return true; }
                 if (tgt->x == unit.x && tgt->y == unit.y + 1) { out = act_dir(ty, D_DOWN); return true; }
                 if (tgt->x == unit.x - 1 && tgt->y == unit.y) { out = act_dir(ty, D_LEFT); return true; }
+                return false;
+            }
+            case AA_MOVE: {  // Move.java:53-59: findPath = findPathToPositionInRange(..., 0, ...)
+                Action mv;
+                if (pf.find_path(unit, aa.x + aa.y * gs.W, 0, gs, &ru, mv) && gs.action_allowed(unit, mv)) {
+                    out = mv;
+                    return true;
+                }
                 return false;
             }
             case AA_ATTACK: {  // Attack.java:50-65
@@ -401,7 +419,24 @@ struct AbstractionLayerAI : BotAI {
                     cd = d;
                 }
             }
-        if (closest) attack(u, closest);
+        if (closest) {
+            attack(u, closest);
+        } else if (explore && gs.pogs_player >= 0) {
+            // POWorkerRush / POLightRush.meleeUnitBehavior (partialobservability/POWorkerRush.java:56-76): no enemy
+            // in view -> walk to the nearest cell that is not observable (row-major scan, strict <)
+            int cx = 0, cy = 0, best = -1;
+            for (int i = 0; i < gs.H; i++)
+                for (int j = 0; j < gs.W; j++)
+                    if (!gs.observable(j, i)) {
+                        int d = (u->x - j) * (u->x - j) + (u->y - i) * (u->y - i);
+                        if (best == -1 || d < best) {
+                            cx = j;
+                            cy = i;
+                            best = d;
+                        }
+                    }
+            if (best != -1) move(u, cx, cy);
+        }
     }
 
     // shared tail of WorkerRush.workersBehavior:148-197 / LightRush.workersBehavior:201-244.
@@ -566,6 +601,16 @@ std::unique_ptr<BotAI> make_bot(int ai_id) {
         case AI_PASSIVE: return std::unique_ptr<BotAI>(new PassiveAI());
         case AI_WORKER_RUSH: return std::unique_ptr<BotAI>(new WorkerRush());
         case AI_LIGHT_RUSH: return std::unique_ptr<BotAI>(new LightRush());
+        case AI_PO_WORKER_RUSH: {
+            auto* b = new WorkerRush();
+            b->explore = true;
+            return std::unique_ptr<BotAI>(b);
+        }
+        case AI_PO_LIGHT_RUSH: {
+            auto* b = new LightRush();
+            b->explore = true;
+            return std::unique_ptr<BotAI>(b);
+        }
     }
     return nullptr;
 }

@@ -497,7 +497,17 @@ GameState GameState::pogs(int player) const {
         }
     }
     for (auto* u : del) v.remove_unit(u);
+    v.pogs_player = player;
     return v;
+}
+
+bool GameState::observable(int x, int y) const {
+    for (auto& u : units)
+        if (u->player == pogs_player) {
+            int dx = u->x - x, dy = u->y - y, r = utype(u->type).sightRadius;
+            if (dx * dx + dy * dy <= r * r) return true;  // sqrt(d2) <= r, exact on integers
+        }
+    return false;
 }
 
 GameState make_game(const MapTemplate& m, int none_mode, long long* next_id) {

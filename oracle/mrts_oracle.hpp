@@ -117,6 +117,8 @@ struct GameState {
     int time = 0;
     int none_mode = NONE_FORK;
     long long* next_id = nullptr;  // Unit.next_ID stand-in (never observable)
+    int pogs_player = -1;          // >= 0: this state is a PartiallyObservableGameState of that player (`instanceof` test of the PO bots)
+    bool observable(int x, int y) const;  // PartiallyObservableGameState.observable, PartiallyObservableGameState.java:48-58
 
     int terrain_at(int x, int y) const { return (*terrain)[x + y * W]; }
     Unit* unit_at(int x, int y) const;            // PhysicalGameState.java:248-255 (first match)
@@ -173,7 +175,7 @@ struct BotAI {
     virtual PlayerAction get_action(int player, const GameState& gs) = 0;
     virtual void reset() = 0;
 };
-enum { AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2 };
+enum { AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2, AI_PO_WORKER_RUSH = 3, AI_PO_LIGHT_RUSH = 4 };
 std::unique_ptr<BotAI> make_bot(int ai_id);
 
 // ---------------------------------------------------------------- vectorised client

@@ -13,6 +13,7 @@ from tests.backends import make_env
 from tests.common import MAP_4, MAP_8, MAP_16, MAP_32, MAP_64, sample_actions
 
 P, W, LR = microrts_ai.passiveAI, microrts_ai.workerRushAI, microrts_ai.lightRushAI
+POW, POL = microrts_ai.POWorkerRush, microrts_ai.POLightRush
 RW = np.array([10.0, 1.0, 1.0, 0.2, 1.0, 4.0])
 
 CASES = {
@@ -29,6 +30,10 @@ CASES = {
     "lightrush8_partial": (0, [LR, LR, P], MAP_8, True, 400, 600, 0.05),
     "lightrush_barracks16": (0, [LR, LR], "maps/16x16/TwoBasesBarracks16x16.xml", False, 600, 700, 0.02),
     "lightrush_nobase8": (0, [LR, LR], "maps/8x8/noBases8x8.xml", False, 300, 400, 0.05),
+    # the partially observable variants: melee units explore (Move to the nearest unobservable cell) while no enemy is in view
+    "po_bots16_partial": (0, [POW, POL, POW, POL], MAP_16, True, 500, 800, 0.03),
+    "po_bots32_partial": (0, [POW, POL], MAP_32, True, 400, 450, 0.03),
+    "po_bots8_full_obs": (0, [POW, POL, W], MAP_8, False, 300, 500, 0.05),
 }
 
 
