@@ -34,6 +34,8 @@ extern "C" {
 #define MRTS_AI_LIGHT_RUSH 2  /* ai.abstraction.LightRush  (microrts_ai.py:25-28)      */
 #define MRTS_AI_PO_WORKER_RUSH 3 /* ai.abstraction.partialobservability.POWorkerRush (microrts_ai.py:37-40) */
 #define MRTS_AI_PO_LIGHT_RUSH 4  /* ai.abstraction.partialobservability.POLightRush  (microrts_ai.py:31-34) */
+#define MRTS_AI_PO_HEAVY_RUSH 5  /* ai.abstraction.partialobservability.POHeavyRush  (microrts_ai.py:43-46) */
+#define MRTS_AI_PO_RANGED_RUSH 6 /* ai.abstraction.partialobservability.PORangedRush (microrts_ai.py:49-52) */
 
 /* One parsed map: what PhysicalGameState.load returns (J/rts/PhysicalGameState.java:54-65,685-711). */
 typedef struct mrts_map_template {

@@ -22,11 +22,15 @@ enum { D_UP = 0, D_RIGHT = 1, D_DOWN = 2, D_LEFT = 3 };
 enum { UT_RESOURCE = 0, UT_BASE = 1, UT_BARRACKS = 2, UT_WORKER = 3, UT_LIGHT = 4, UT_HEAVY = 5, UT_RANGED = 6, N_UTYPES = 7 };
 // how `new UnitAction(TYPE_NONE, d)` behaves: the fork forces parameter -1 (J/rts/UnitAction.java:149-154)
 enum { NONE_UPSTREAM = 0, NONE_FORK = 1 };
-enum { AI_NONE = -1, AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2, AI_PO_WORKER_RUSH = 3, AI_PO_LIGHT_RUSH = 4, AI_COUNT = 5 };
+enum { AI_NONE = -1, AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2, AI_PO_WORKER_RUSH = 3, AI_PO_LIGHT_RUSH = 4, AI_PO_HEAVY_RUSH = 5, AI_PO_RANGED_RUSH = 6, AI_COUNT = 7 };
 // scripted opponents built on AbstractionLayerAI: abstract-action table in the blob, path searches
 MRTS_HD bool ai_plans(int ai) { return ai >= AI_WORKER_RUSH && ai < AI_COUNT; }
 // the PO* variants (ai/abstraction/partialobservability/): same bot, melee units explore when no enemy is in view
-MRTS_HD bool ai_explores(int ai) { return ai == AI_PO_WORKER_RUSH || ai == AI_PO_LIGHT_RUSH; }
+MRTS_HD bool ai_explores(int ai) { return ai >= AI_PO_WORKER_RUSH && ai <= AI_PO_RANGED_RUSH; }
+// LightRush / HeavyRush / RangedRush (ai/abstraction/{Light,Heavy,Ranged}Rush.java) are one bot that differs in the
+// unit type its barracks train (LightRush.java:137-138, HeavyRush.java:136-137, RangedRush.java:124-125)
+MRTS_HD bool ai_barracks_rush(int ai) { return ai == AI_LIGHT_RUSH || (ai >= AI_PO_LIGHT_RUSH && ai <= AI_PO_RANGED_RUSH); }
+MRTS_HD int ai_rush_unit(int ai) { return ai == AI_PO_HEAVY_RUSH ? UT_HEAVY : (ai == AI_PO_RANGED_RUSH ? UT_RANGED : UT_LIGHT); }
 
 MRTS_HD int dir_dx(int d) { return d == D_RIGHT ? 1 : (d == D_LEFT ? -1 : 0); }
 MRTS_HD int dir_dy(int d) { return d == D_DOWN ? 1 : (d == D_UP ? -1 : 0); }

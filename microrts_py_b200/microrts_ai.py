@@ -10,6 +10,8 @@ returning the opponent.  In the reference the result is a Java ``ai.core.AI`` ob
   lightRushAI   ai.abstraction.LightRush  (J/ai/abstraction/LightRush.java:77-254)
   POWorkerRush / POLightRush  the same two with the exploring melee behaviour of
                 J/ai/abstraction/partialobservability/PO{Worker,Light}Rush.java:42-78
+  POHeavyRush / PORangedRush  POLightRush training heavy / ranged units (J/ai/abstraction/HeavyRush.java:136-137,
+                RangedRush.java:124-125 are the only lines that differ from LightRush.java)
 
 Every other factory of the reference (random, search-based or closed-jar bots) raises
 ``NotImplementedError`` with the reason.
@@ -44,6 +46,14 @@ def POWorkerRush(utt=None):
 
 def POLightRush(utt=None):
     return DeviceAI("POLightRush", 4)
+
+
+def POHeavyRush(utt=None):
+    return DeviceAI("POHeavyRush", 5)
+
+
+def PORangedRush(utt=None):
+    return DeviceAI("PORangedRush", 6)
 
 
 def _unsupported(name, why):

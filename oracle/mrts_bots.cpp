@@ -541,7 +541,11 @@ struct WorkerRush : AbstractionLayerAI {
 };
 
 // ---------------------------------------------------------------- LightRush (J/ai/abstraction/LightRush.java:77-254)
+// HeavyRush.java / RangedRush.java are the same class with heavyType / rangedType in barracksBehavior
+// (HeavyRush.java:136-137, RangedRush.java:124-125; RangedRush.java:181-183 only reorders the && of the
+// barracks-building test): rush_type names the unit the barracks train.
 struct LightRush : AbstractionLayerAI {
+    int rush_type = UT_LIGHT;
     PlayerAction get_action(int player, const GameState& gs) override {
         const int pres = gs.players->res[player];
         for (auto& u : gs.units)
@@ -553,7 +557,7 @@ struct LightRush : AbstractionLayerAI {
             }
         for (auto& u : gs.units)
             if (u->type == UT_BARRACKS && u->player == player && !gs.assignment(u.get()))
-                if (pres >= utype(UT_LIGHT).cost) train(u, UT_LIGHT);
+                if (pres >= utype(rush_type).cost) train(u, rush_type);
         for (auto& u : gs.units)
             if (utype(u->type).canAttack && !utype(u->type).canHarvest && u->player == player && !gs.assignment(u.get()))
                 melee_behavior(u, player, gs);
@@ -606,9 +610,12 @@ std::unique_ptr<BotAI> make_bot(int ai_id) {
             b->explore = true;
             return std::unique_ptr<BotAI>(b);
         }
-        case AI_PO_LIGHT_RUSH: {
+        case AI_PO_LIGHT_RUSH:
+        case AI_PO_HEAVY_RUSH:
+        case AI_PO_RANGED_RUSH: {  // partialobservability/PO{Light,Heavy,Ranged}Rush.java:23-78
             auto* b = new LightRush();
             b->explore = true;
+            b->rush_type = ai_id == AI_PO_HEAVY_RUSH ? UT_HEAVY : (ai_id == AI_PO_RANGED_RUSH ? UT_RANGED : UT_LIGHT);
             return std::unique_ptr<BotAI>(b);
         }
     }

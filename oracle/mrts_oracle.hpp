@@ -175,7 +175,7 @@ struct BotAI {
     virtual PlayerAction get_action(int player, const GameState& gs) = 0;
     virtual void reset() = 0;
 };
-enum { AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2, AI_PO_WORKER_RUSH = 3, AI_PO_LIGHT_RUSH = 4 };
+enum { AI_PASSIVE = 0, AI_WORKER_RUSH = 1, AI_LIGHT_RUSH = 2, AI_PO_WORKER_RUSH = 3, AI_PO_LIGHT_RUSH = 4, AI_PO_HEAVY_RUSH = 5, AI_PO_RANGED_RUSH = 6 };
 std::unique_ptr<BotAI> make_bot(int ai_id);
 
 // ---------------------------------------------------------------- vectorised client

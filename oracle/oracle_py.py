@@ -17,7 +17,7 @@ _LIB_PATH = os.path.join(_HERE, "libmrts_oracle.so")
 _lib = None
 
 NONE_UPSTREAM, NONE_FORK = 0, 1
-AI_PASSIVE, AI_WORKER_RUSH, AI_LIGHT_RUSH, AI_PO_WORKER_RUSH, AI_PO_LIGHT_RUSH = 0, 1, 2, 3, 4
+AI_PASSIVE, AI_WORKER_RUSH, AI_LIGHT_RUSH, AI_PO_WORKER_RUSH, AI_PO_LIGHT_RUSH, AI_PO_HEAVY_RUSH, AI_PO_RANGED_RUSH = 0, 1, 2, 3, 4, 5, 6
 
 
 def build(force: bool = False) -> str:

@@ -14,7 +14,8 @@ import numpy as np
 from microrts_py_b200 import microrts_ai
 from tests.common import templates_for
 
-AI_IDS = {microrts_ai.passiveAI: 0, microrts_ai.workerRushAI: 1, microrts_ai.lightRushAI: 2, microrts_ai.POWorkerRush: 3, microrts_ai.POLightRush: 4}
+AI_IDS = {microrts_ai.passiveAI: 0, microrts_ai.workerRushAI: 1, microrts_ai.lightRushAI: 2, microrts_ai.POWorkerRush: 3, microrts_ai.POLightRush: 4,
+          microrts_ai.POHeavyRush: 5, microrts_ai.PORangedRush: 6}
 
 
 class _HostEnv:

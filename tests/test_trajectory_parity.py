@@ -14,6 +14,7 @@ from tests.common import MAP_4, MAP_8, MAP_16, MAP_32, MAP_64, sample_actions
 
 P, W, LR = microrts_ai.passiveAI, microrts_ai.workerRushAI, microrts_ai.lightRushAI
 POW, POL = microrts_ai.POWorkerRush, microrts_ai.POLightRush
+POH, POR = microrts_ai.POHeavyRush, microrts_ai.PORangedRush
 RW = np.array([10.0, 1.0, 1.0, 0.2, 1.0, 4.0])
 
 CASES = {
@@ -34,6 +35,10 @@ CASES = {
     "po_bots16_partial": (0, [POW, POL, POW, POL], MAP_16, True, 500, 800, 0.03),
     "po_bots32_partial": (0, [POW, POL], MAP_32, True, 400, 450, 0.03),
     "po_bots8_full_obs": (0, [POW, POL, W], MAP_8, False, 300, 500, 0.05),
+    # POHeavyRush / PORangedRush (microrts_ai.py:43-52): the LightRush bot training heavy / ranged units (range-3 attacks)
+    "po_heavy_ranged16_partial": (0, [POH, POR, POH, POR], MAP_16, True, 900, 1100, 0.02),
+    "po_heavy_ranged_barracks16": (0, [POH, POR, POR], "maps/16x16/TwoBasesBarracks16x16.xml", False, 700, 800, 0.02),
+    "po_heavy_ranged8_partial": (0, [POR, POH], MAP_8, True, 500, 700, 0.03),
 }
 
 
@@ -150,6 +155,7 @@ BOTVBOT = {
     "wr_vs_wr16": (MAP_16, [W, W], [W, W], 600, 700),
     "mixed8": (MAP_8, [W, LR, P, W, LR, LR], [LR, W, W, P, LR, P], 300, 700),
     "lr_vs_wr16": (MAP_16, [LR, W, LR], [W, LR, LR], 1500, 1700),
+    "heavy_ranged16": (MAP_16, [POH, POR, POL, W], [POR, POH, POR, POH], 1500, 1700),
     "nobase8": ("maps/8x8/noBases8x8.xml", [LR, W], [W, LR], 250, 400),
 }
 
