@@ -320,8 +320,9 @@ def e2e_run(args, env_dev, wl, rank, dist, dev):
     """The call a user of the reference makes (ppo_gridnet.py:459-480 loop shape): get_action_mask()
     -> NumPy, policy output -> NumPy, step(actions) -> NumPy obs / reward / done, all int32 / float64
     host arrays as in the reference.  Every step moves the actions host->device and obs + mask + raw
-    rewards + dones (and the device policy's sampled action grid, as `action.cpu().numpy()` does)
-    device->host; the env's own traffic is bit-packed (mrts_step_host)."""
+    rewards + dones device->host inside the timed region; the env's own traffic is bit-packed
+    (mrts_step_host_slot).  The policy stand-in between two env calls is not timed in `value` (the reference
+    arm does not time its action sampling either); `value_incl_policy_copy` is the whole loop."""
     import torch
 
     from microrts_py_b200 import microrts_ai
@@ -339,13 +340,19 @@ def e2e_run(args, env_dev, wl, rank, dist, dev):
     mask = env.get_action_mask()
     steps = max(3, args.steps // 4)
 
+    # Like the reference arm (cpu_run: "get_masks + step timed, action sampling excluded") the timed region
+    # is the env's own API: step(host actions) + get_action_mask(), host arrays in and out, every
+    # host<->device copy of the env inside.  The stand-in policy (device sampler + the 58.7 MB int32
+    # `action.cpu().numpy()` copy at 16x16) is the consumer's work: it runs between the timed regions and
+    # the loop's wall time including it is reported beside as `value_incl_policy_copy`.
     def one():
         a_dev = env.sample_actions()           # policy stand-in, on the device
         a_host.copy_(a_dev, non_blocking=True)  # action.cpu().numpy()
-        torch.cuda.current_stream(dev).synchronize()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
         obs, r, d, infos = env.step(a_host.numpy())
         m = env.get_action_mask()
-        return obs, m, r, d
+        return obs, m, r, d, time.perf_counter() - t0
 
     for _ in range(3):
         one()
@@ -353,23 +360,28 @@ def e2e_run(args, env_dev, wl, rank, dist, dev):
     if dist is not None:
         dist.barrier()
     t0 = time.perf_counter()
+    dt_env = 0.0
     for _ in range(steps):
-        obs, m, r, d = one()
+        obs, m, r, d, dt1 = one()
+        dt_env += dt1
     torch.cuda.synchronize(dev)
-    dt = time.perf_counter() - t0
-    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    dt_loop = time.perf_counter() - t0
+    t = torch.tensor([dt_env, dt_loop], dtype=torch.float64, device=dev)
     world = 1
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         world = dist.get_world_size()
-    dt = float(t.item())
+    dt, dt_loop = float(t[0].item()), float(t[1].item())
     hw = env.height * env.width
     h2d = n * hw * 2                                            # packed action rows
-    d2h = n * hw * 16 + n * 6 * 8 + n + a_host.numel() * 4      # obs + mask bits, rewards, dones; + the policy's action grid
+    d2h = n * hw * 16 + n * 6 * 8 + n                           # obs + mask bits, rewards, dones
     host_threads = env._lib.mrts_host_threads(env._h)
     env.close()
     return {"value": n * world * steps / dt, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "envs_per_gpu": n, "steps": steps,
-            "ms_per_step": 1e3 * dt / steps, "api": "MicroRTSGridModeVecEnv(host_transport=True).step/get_action_mask, NumPy int32 in/out, two alternating result buffers; mrts_step_host_slot moves 1 bit per element over PCIe and %d host threads rewrite the cells of the arrays that changed" % host_threads,
+            "ms_per_step": 1e3 * dt / steps,
+            "value_incl_policy_copy": n * world * steps / dt_loop, "policy_copy_d2h_bytes_per_step": a_host.numel() * 4,
+            "timed": "step(host actions) + get_action_mask() per step, summed over the steps (max over ranks); the stand-in policy's device sampling and its action-grid copy to the host run between the timed regions, as the reference arm excludes action sampling",
+            "api": "MicroRTSGridModeVecEnv(host_transport=True).step/get_action_mask, NumPy int32 in/out, two alternating result buffers; mrts_step_host_slot moves 1 bit per element over PCIe and %d host threads rewrite the cells of the arrays that changed" % host_threads,
             "result_array_bytes_per_step": int(obs.nbytes + m.nbytes)}
 
 
