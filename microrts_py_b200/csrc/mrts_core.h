@@ -127,8 +127,6 @@ struct Sim {
     uint32_t* bitsC;
     int nbits_words;
     int16_t* astar;  // bot games: A* scratch (astar_bytes)
-    int ws, a_nc, a_core;  // constants of the map (bind_sim): ceil_log2(W), astar_cells, astar_core_bytes
-    uint32_t winv;         // ceil(2^32 / W), 0 when W == 1: c / W == umulhi(c, winv) for 0 <= c < 65536 (div_w)
     St* st;          // per-step mutable scalars
     int lane, nl;    // the rules run on the game's first warp, every lane executing the same (uniform) code on the
                      // shared state; lane / lane count (32 on the device, 1 in the host build) drive the per-unit scans
@@ -182,13 +180,6 @@ struct Sim {
         return (int)(threadIdx.x & 31);
 #else
         return 0;
-#endif
-    }
-    MRTS_HD int div_w(int c) const {  // c / W for a cell index, without the integer-division sequence
-#ifdef __CUDA_ARCH__
-        return winv ? (int)__umulhi((unsigned)c, winv) : c;
-#else
-        return winv ? (int)(((uint64_t)(uint32_t)c * winv) >> 32) : c;
 #endif
     }
     MRTS_HD int nunits() const { return hdr->nunits; }
@@ -995,7 +986,7 @@ struct Sim {
     MRTS_HD int astar_nf() const { return HW + W + H + 2; }
     MRTS_HD AStarBuf astar_buf() const {
         AStarBuf b;
-        const int nc = a_nc;
+        const int nc = astar_cells(W, HW);
         b.cost = astar;
         b.parent = b.cost + nc;
         b.next = b.parent + nc;
@@ -1007,7 +998,7 @@ struct Sim {
     // of the units the bot sees (constant during a step), F = cells a search may enter during this
     // bot call (F0 minus pending MOVE/PRODUCE targets, bitsB, minus the desires accepted so far,
     // bitsC), V = cells pushed by the current search, R = flood-fill scratch
-    MRTS_HD uint64_t* rows_F0() const { return (uint64_t*)((uint8_t*)astar + a_core); }
+    MRTS_HD uint64_t* rows_F0() const { return (uint64_t*)((uint8_t*)astar + astar_core_bytes(W, HW)); }
     MRTS_HD uint64_t* rows_F() const { return rows_F0() + H; }
     MRTS_HD uint64_t* rows_V() const { return rows_F0() + 2 * H; }
     MRTS_HD uint64_t* rows_R() const { return rows_F0() + 3 * H; }
@@ -1058,8 +1049,7 @@ struct Sim {
     // a desire was accepted (its target is now in bitsC): later searches of this call may not enter it
     MRTS_HD void rows_reserve(int pos) const {
         if (W > 64 || !st->rows_ready || pos < 0 || pos >= HW) return;
-        const int py = div_w(pos);
-        rows_F()[py] &= ~(1ull << (pos - py * W));
+        rows_F()[pos / W] &= ~(1ull << (pos % W));
     }
     static MRTS_HD uint64_t brev64(uint64_t v) {
 #if defined(__CUDA_ARCH__)
@@ -1133,7 +1123,7 @@ struct Sim {
     MRTS_HD int astar_rows(int i, int targetpos, int range, int vp) {
         const AStarBuf b = astar_buf();
         const Unit& su = u[i];
-        const int ws = this->ws, WP = 1 << ws;
+        const int ws = ceil_log2(W), WP = 1 << ws;
         const int tx = targetpos % W, ty = targetpos / W;
         const int sq = range * range;
         const int sx = su.x, sy = su.y;

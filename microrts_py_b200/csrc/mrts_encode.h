@@ -43,7 +43,7 @@ MRTS_HD void obs_words_cells(const Sim& s, int viewer, int vp, const uint16_t* g
         if (s.partial) {
             // README-literal visibility planes: is this cell within sight of any unit
             // of the viewer's opponent in the TRUE post-step state
-            const int y = s.div_w(c), x = c - y * s.W;
+            const int x = c % s.W, y = c / s.W;
             bool seen = false;
             for (int j = 0; j < n && !seen; j++) {
                 const Unit& o = s.u[j];

@@ -116,10 +116,6 @@ MRTS_HD void bind_sim(Sim& s, const EnvParams& P, const Layout& L, uint8_t* mem,
     s.bitsB = s.bitsA + L.nbits_words;
     s.bitsC = s.bitsB + L.nbits_words;
     s.astar = (int16_t*)(mem + L.astar);
-    s.ws = ceil_log2(P.W);
-    s.a_nc = astar_cells(P.W, P.HW);
-    s.a_core = astar_core_bytes(P.W, P.HW);
-    s.winv = P.W > 1 ? (uint32_t)((0x100000000ull + (uint32_t)P.W - 1) / (uint32_t)P.W) : 0u;
     s.lane = 0;
     s.nl = 1;
     s.st = (St*)(mem + L.misc);

@@ -24,10 +24,15 @@ def line_table(kernel):
     subprocess.check_call(["cuobjdump", "-xelf", "all", LIB], cwd=d, stdout=subprocess.DEVNULL)
     cubin = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
     txt = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, cubin)], capture_output=True, text=True).stdout
-    table, cur, active = {}, ("?", 0), False
+    table, cur, active, first = {}, ("?", 0), False, None
     for ln in txt.splitlines():
         if ln.startswith(".text."):
-            active = kernel in ln
+            # one instantiation only: a substring that matches several template instances would merge their
+            # offset tables -- give the mangled arguments too (e.g. mrts_pass_warp_kernelILi4ELi29ELi5E)
+            active = kernel in ln and first in (None, ln)
+            if active and first is None:
+                first = ln
+                print("section", ln.strip(), file=sys.stderr)
         if not active:
             continue
         m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
