@@ -311,7 +311,7 @@ def gpu_arm(args):
         }
         if cpu_v is not None:
             line["cpu_baseline"] = {"value": cpu_v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                                    "sample": f"{args.cpu_envs} envs of the workload, {cpu_k} steps ({cpu_spent:.1f} s timed inside a 25 s leg), get_masks + step timed, action sampling excluded"}
+                                    "sample": f"{args.cpu_envs} envs of the workload, {cpu_k} steps ({cpu_spent:.1f} s timed inside a {args.cpu_budget:.0f} s leg), get_masks + step timed, action sampling excluded"}
         emit(line)
     env.close()
     if dist is not None:
