@@ -285,7 +285,7 @@ def gpu_arm(args):
     units_mean = float(mask[:, :, 0].sum().item()) / N  # units that may act per view, end state
 
     # ---------------- end to end: the reference-facing class with HOST buffers
-    e2e = e2e_run(args, env, wl, rank, dist, dev)
+    e2e = e2e_run(args, env, wl, rank, dist, dev) if args.e2e_envs > 0 else None
 
     if rank == 0:
         B = algorithmic_bytes(HW, Pn, elem)
@@ -303,9 +303,10 @@ def gpu_arm(args):
                        "partial_obs": wl["partial"], "max_steps": wl["max_steps"], "prewarm_steps": args.prewarm, "l2": "outputs per step (%.2f GB) exceed the 126 MB L2; no flush needed" % (B * N / 1e9),
                        "mean_acting_units_per_view": units_mean, "threads_per_game": L.mrts_threads_per_game(env._h), "smem_per_game": L.mrts_smem_bytes(env._h),
                        "staged_units_per_game": L.mrts_staged_units(env._h), "unit_capacity": L.mrts_unit_capacity(env._h),
-                       "kernels_per_step": L.mrts_launches_per_step(env._h)},
+                       "kernels_per_step": L.mrts_launches_per_step(env._h), "pipeline": {1: "direct", 2: "split"}.get(L.mrts_pipeline(env._h)), "chunks": L.mrts_chunks(env._h),
+                       "rules_kernels": kernel_info(L, env._h)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC.get((args.workload, args.dtype)),
-                         "kernel": "mrts_pass_warp_kernel" if L.mrts_threads_per_game(env._h) == 32 else "mrts_pass_kernel",
+                         "kernel": "mrts_expand_kernel (bulk-store half of the step; mrts_rules_warp_kernel feeds it)" if L.mrts_pipeline(env._h) == 2 else ("mrts_rules_warp_kernel" if L.mrts_threads_per_game(env._h) == 32 else "mrts_rules_block_kernel"),
                          "kernel_ms_note": "CUDA events around each step on the launching stream (includes the tiny launch-order / overflow kernels of bot slabs)", "bytes_per_env_step": B, "env_steps_per_launch": N, "kernel_ms": kern_ms, "peak_source": peak_src},
             "e2e": e2e, "gpu_launches": args.steps * L.mrts_launches_per_step(env._h), "clocks": clk,
         }
@@ -316,6 +317,17 @@ def gpu_arm(args):
     env.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def kernel_info(L, h):
+    import ctypes as C
+
+    out = {}
+    for name, k in (("light", 0), ("heavy", 1)):
+        r, g, sm = C.c_int(), C.c_int(), C.c_int()
+        L.mrts_kernel_info(h, k, C.byref(r), C.byref(g), C.byref(sm))
+        out[name] = {"regs": r.value, "games_per_block": g.value, "smem_per_game": sm.value}
+    return out
 
 
 def e2e_run(args, env_dev, wl, rank, dist, dev):

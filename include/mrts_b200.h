@@ -37,6 +37,13 @@ extern "C" {
 #define MRTS_AI_PO_HEAVY_RUSH 5  /* ai.abstraction.partialobservability.POHeavyRush  (microrts_ai.py:43-46) */
 #define MRTS_AI_PO_RANGED_RUSH 6 /* ai.abstraction.partialobservability.PORangedRush (microrts_ai.py:49-52) */
 
+/* How mrts_step produces the tensors (mrts_config::pipeline); see DESIGN.md section 4.  SPLIT: the rules kernels write a
+ * packed form (one word per cell, one entry per acting unit) and an expansion kernel streams it into the tensors with bulk
+ * async stores, the slab cut into `chunks` so that the two overlap.  DIRECT: the rules pass writes the tensors itself. */
+#define MRTS_PIPELINE_AUTO 0
+#define MRTS_PIPELINE_DIRECT 1
+#define MRTS_PIPELINE_SPLIT 2
+
 /* One parsed map: what PhysicalGameState.load returns (J/rts/PhysicalGameState.java:54-65,685-711). */
 typedef struct mrts_map_template {
     int32_t width, height;
@@ -65,6 +72,8 @@ typedef struct mrts_config {
     const int32_t* bot_ai1;    /* NULL, or num_bot_envs entries: MRTS_AI_* playing player 0 of that bot env (bot vs bot,
                                   J/tests/JNIBotClient.java:108-134, MicroRTSBotVecEnv), -1 = the agent plays it.  The
                                   action rows of such envs are ignored; both bots act on the full state             */
+    int32_t pipeline;          /* MRTS_PIPELINE_*: 0 = choose from the slab size                                      */
+    int32_t chunks;            /* slab chunks of the split pipeline, 0 = choose                                       */
 } mrts_config;
 
 typedef struct mrts_env mrts_env;
@@ -110,6 +119,27 @@ int mrts_step_ex(mrts_env* env, const mrts_step_io* io, void* stream);
 /* The same sampler on the current state (e.g. after mrts_reset). */
 int mrts_sample_actions(mrts_env* env, int32_t* next_actions, uint64_t seed, void* stream);
 
+/* The packed form of the same outputs -- what the rules kernels produce before the expansion, ~1.4 KB per 16x16 view
+ * instead of 110 KB -- for consumers that unpack on the fly (or not at all):
+ *   obs_words    (N, H*W) uint32         bit k of a cell's word = plane k of the observation
+ *   mask_entries (N, 1 + cap, 4) uint32  row 0 = {n, 0, 0, 0}; rows 1..n = {cell, bits 0-31, bits 32-63, bits 64-77} of the
+ *                                        mask rows that are not all zero, in ascending cell order; cap = mrts_unit_capacity
+ * mrts_packed_sizes gives the element counts of the two arrays.  mrts_expand turns them into the obs / mask tensors of
+ * mrts_step (either may be NULL); it needs H*W*element_bytes to be a multiple of 16. */
+typedef struct mrts_packed_io {
+    const int32_t* actions;  /* (N, H*W, 7) int32; NULL only when every env is bot vs bot */
+    uint32_t* obs_words;     /* nullable */
+    uint32_t* mask_entries;  /* nullable */
+    double* reward;          /* (N, 6), nullable */
+    uint8_t* done;           /* (N,), nullable */
+    int32_t* next_actions;   /* nullable */
+    uint64_t seed;
+} mrts_packed_io;
+int mrts_packed_sizes(const mrts_env* env, int64_t* obs_words, int64_t* mask_entry_words);
+int mrts_reset_packed(mrts_env* env, uint32_t* obs_words, uint32_t* mask_entries, void* stream);
+int mrts_step_packed(mrts_env* env, const mrts_packed_io* io, void* stream);
+int mrts_expand(mrts_env* env, const uint32_t* obs_words, const uint32_t* mask_entries, void* obs, void* mask, void* stream);
+
 /* Host-buffer forms of reset / gameStep + getMasks: every pointer is a HOST pointer (pageable is fine),
  * the call returns when the arrays are filled -- what the reference's NumPy-returning methods do
  * (gym_microrts/envs/vec_env.py:278-282, 968-1061, 1091-1101).  obs (N,H,W,P) and mask (N,H*W,78) have
@@ -150,12 +180,21 @@ int mrts_unit_capacity(const mrts_env* env);
 int mrts_threads_per_game(const mrts_env* env);
 int mrts_smem_bytes(const mrts_env* env);
 int mrts_staged_units(const mrts_env* env);     /* units per game the warp kernel stages in shared memory */
-int mrts_launches_per_step(const mrts_env* env); /* kernels one mrts_step enqueues: the pass itself, + the launch-order kernel of
-                                                    large bot slabs, + the full-capacity overflow launch when staged < capacity */
+int mrts_launches_per_step(const mrts_env* env); /* kernels the last launch enqueued: rules per game class and slab chunk, the
+                                                    full-capacity launch when staged < capacity, the expansion per chunk, map rotation */
+int mrts_pipeline(const mrts_env* env);          /* MRTS_PIPELINE_DIRECT or MRTS_PIPELINE_SPLIT */
+int mrts_chunks(const mrts_env* env);            /* slab chunks of the split pipeline */
+/* registers per thread, games per block and shared memory per game of the light (0) / heavy (1) rules kernel in use */
+int mrts_kernel_info(const mrts_env* env, int heavy, int* regs, int* games_per_block, int* smem_per_game);
 /* State of one game for cross-checks against the oracle: hdr5 = time, res0, res1, steps, nunits;
  * rows12 = per unit: type, player, x, y, res, hp, a_type (-1 idle), a_param, a_x, a_y, a_utype, a_time.
  * Returns the number of units (or a negative error); host pointers. */
 int mrts_export_state(mrts_env* env, int game, int32_t* hdr5, int32_t* rows12, int cap_rows, void* stream);
+/* The inverse (GameState.fromXML, J/rts/GameState.java:763-915): game `game` continues from the given state; n = rows
+ * (units, in pgs.units order).  The pending assignments are taken to have been issued in ascending issue_order[i]
+ * (n entries, one per row; NULL = by time of issue, then row).  The scripted bot of the game starts with an empty
+ * abstract-action table, as after a reset.  Synchronises the device. */
+int mrts_import_state(mrts_env* env, int game, const int32_t* hdr5, const int32_t* rows12, int n, const int32_t* issue_order, void* stream);
 
 /* Raw engine access for replaying recorded games (J/test/microrts/TestTracesIntegrity.java:72-126):
  * GameState.issueSafe of one player's actions on one game, rows7 = ux, uy, type, param, ax, ay, utype (host). */

@@ -51,7 +51,24 @@ class ConfigC(C.Structure):
         ("threads_per_game", C.c_int32),
         ("staged_units", C.c_int32),
         ("bot_ai1", C.c_void_p),
+        ("pipeline", C.c_int32),
+        ("chunks", C.c_int32),
     ]
+
+
+class PackedIOC(C.Structure):
+    _fields_ = [
+        ("actions", C.c_void_p),
+        ("obs_words", C.c_void_p),
+        ("mask_entries", C.c_void_p),
+        ("reward", C.c_void_p),
+        ("done", C.c_void_p),
+        ("next_actions", C.c_void_p),
+        ("seed", C.c_uint64),
+    ]
+
+
+PIPELINE_AUTO, PIPELINE_DIRECT, PIPELINE_SPLIT = 0, 1, 2
 
 
 class StepIOC(C.Structure):
@@ -80,6 +97,8 @@ def make_config(
     staged_units: int = 0,
     cycle_templates: Sequence[MapTemplate] = None,
     bot_ai1: Sequence[int] = None,
+    pipeline: int = 0,
+    chunks: int = 0,
 ):
     """Build an ``mrts_config``.  ``templates`` has one entry per env (as ``map_paths`` after
     broadcasting); identical templates are de-duplicated by object identity / name.
@@ -135,6 +154,8 @@ def make_config(
     cfg.elem_bytes = elem_bytes
     cfg.threads_per_game = threads_per_game
     cfg.staged_units = staged_units
+    cfg.pipeline = pipeline
+    cfg.chunks = chunks
     if bot_ai1 is not None:  # bot vs bot (JNIBotClient): scripted player 0 per bot env, -1 = agent
         if len(bot_ai1) != num_bot_envs:
             raise ValueError("need one player-0 entry per bot env")
@@ -148,11 +169,11 @@ def make_config(
 
 def build_library(force: bool = False) -> str:
     """Compile libmrts_b200.so for sm_100a with nvcc (cross-compiles without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".h"))]
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h", ".cpp"))]
     srcs.append(os.path.join(_HERE, "..", "include", "mrts_b200.h"))
     stale = not os.path.exists(LIB_PATH) or any(os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in srcs if os.path.exists(s))
     if force or stale:
-        subprocess.check_call(["make", "-C", CSRC, "-B", "libmrts_b200.so"], stdout=subprocess.DEVNULL)
+        subprocess.check_call(["make", "-C", CSRC, "-j", "8", "libmrts_b200.so"], stdout=subprocess.DEVNULL)
     return LIB_PATH
 
 
@@ -186,6 +207,14 @@ SYMBOLS = [
     "mrts_staged_units",
     "mrts_launches_per_step",
     "mrts_export_state",
+    "mrts_import_state",
+    "mrts_packed_sizes",
+    "mrts_reset_packed",
+    "mrts_step_packed",
+    "mrts_expand",
+    "mrts_pipeline",
+    "mrts_chunks",
+    "mrts_kernel_info",
     "mrts_debug_issue",
     "mrts_debug_cycle",
     "mrts_debug_timing",
@@ -217,6 +246,14 @@ def lib():
         for f in ("mrts_num_envs", "mrts_num_games", "mrts_planes", "mrts_unit_capacity", "mrts_threads_per_game", "mrts_smem_bytes", "mrts_staged_units", "mrts_launches_per_step"):
             getattr(L, f).argtypes = [vp]
         L.mrts_export_state.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
+        L.mrts_import_state.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp]
+        L.mrts_packed_sizes.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.mrts_reset_packed.argtypes = [vp, vp, vp, vp]
+        L.mrts_step_packed.argtypes = [vp, C.POINTER(PackedIOC), vp]
+        L.mrts_expand.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.mrts_pipeline.argtypes = [vp]
+        L.mrts_chunks.argtypes = [vp]
+        L.mrts_kernel_info.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.mrts_debug_issue.argtypes = [vp, C.c_int, vp, C.c_int, vp]
         L.mrts_debug_cycle.argtypes = [vp, C.c_int, C.POINTER(C.c_int), vp]
         L.mrts_debug_timing.argtypes = [vp, vp]

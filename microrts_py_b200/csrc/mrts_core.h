@@ -96,17 +96,6 @@ struct St {
     int rew[2][6];   // integer reward terms per player view (exact small integers)
 };
 
-struct Sim;
-// Out-of-line entry points of the big rule functions (one copy of each in the kernel image instead
-// of one per call site: the rules phase is instruction-fetch bound).  `sp` is the game's Sim in
-// shared memory; each copies it into registers first.
-MRTS_HDN int o_astar(const Sim* sp, int i, int targetpos, int range, int vp);
-MRTS_HDN void o_issue_safe(const Sim* sp, PAct* list, int cnt);
-MRTS_HDN void o_decode_actions(const Sim* sp, int player, int vp);
-MRTS_HDN void o_make_view(const Sim* sp, int p);
-MRTS_HDN void o_bot_melee(const Sim* sp, int i, int player, int vp);
-MRTS_HDN void o_fill_with_nones(const Sim* sp, PAct* list, int* cnt, int player, int duration, int vp);
-
 struct Sim {
     // ---- configuration
     int W, H, HW, cap;
@@ -130,7 +119,6 @@ struct Sim {
     St* st;          // per-step mutable scalars
     int lane, nl;    // the rules run on the game's first warp, every lane executing the same (uniform) code on the
                      // shared state; lane / lane count (32 on the device, 1 in the host build) drive the per-unit scans
-    const Sim* self; // where this view is stored for the out-of-line entry points
 
     // ------------------------------------------------------------------ small helpers
     // ---- warp primitives of the rules phase (no-ops / identities with one lane)
@@ -524,8 +512,8 @@ struct Sim {
                 pa[kept++] = e;  // kept <= k: never overwrites an unread candidate
             }
         }
+        fill_with_nones(pa, kept, player, 1, vp);
         st->npa = kept;
-        o_fill_with_nones(self, pa, &st->npa, player, 1, vp);
     }
 
     // PlayerAction.fillWithNones: idle own units not yet in the action, in unit order
@@ -915,19 +903,20 @@ struct Sim {
     // equal values the lowest index wins -- what a strict `<` scan in unit order keeps.  -1 if no candidate.
     static MRTS_HD int argmin_key(int value, int index) { return (value << 16) | index; }
     enum { NO_KEY = 0x7FFFFFFF };
-    MRTS_HD void aa_put(const AbstractAct& r, int i) {  // LinkedHashMap.put: re-put keeps the slot; i = the unit's index
-        int k = aa_find(r.unit);
+    MRTS_HD void aa_put(const AbstractAct& r, int i, int k) {  // LinkedHashMap.put: re-put keeps the slot; i = the unit's index, k = aa_find(r.unit)
         if (k < 0) {
             if (hdr->n_aa >= cap) return;
             k = hdr->n_aa++;
         }
+        wsync();
         aa[k] = r;
         // bot-vs-bot games keep both bots' tables in this one table: entries of player 0's bot carry AA_OWNER0
         // (each bot only ever sees its own entries, in their insertion order -- two LinkedHashMaps)
         if (u[i].player == 0) aa[k].kind = (uint8_t)(r.kind | AA_OWNER0);
-        // UF_AA_ATTACK mirrors "this unit's table entry is an Attack" (see worker_rush)
+        // UF_AA_ATTACK mirrors "this unit's table entry is an Attack" (see worker_rush_jobs)
         if (r.kind == AA_ATTACK) u[i].flags |= UF_AA_ATTACK;
         else u[i].flags &= (uint8_t)~UF_AA_ATTACK;
+        wsync();
     }
     // The unit array is in creation order and uids are handed out in creation order (template
     // index, then next_uid++), compaction is stable: the array is sorted by uid.
@@ -1385,18 +1374,25 @@ struct Sim {
         return best == NO_KEY ? 0 : -best;
     }
 
-    // AbstractAction.execute: true + primitive action in `out`, or false (null)
-    MRTS_HD bool aa_execute(AbstractAct& r, int i, int vp, const int* costB, PAct& out) {
+    // AbstractAction.execute: true + primitive action in `out`, or false (null).  ti = index of the entry's
+    // target unit in the bot's view (Harvest: the resource, or the base when carrying; Attack: the target), -1 = gone.
+    // Every kind that walks first decides (target cell, range); the ONE path search below serves them all
+    // (the rules are instruction-fetch bound: each big function is inlined exactly once).
+    MRTS_HD bool aa_execute(AbstractAct& r, int i, int ti, int vp, const int* costB, PAct& out) {
         const Unit& un = u[i];
         out.unit = (uint16_t)i;
         out.utype = -1;
         out.param = -1;
         out.x = out.y = 0;
         out.pad = 0;
-        switch (r.kind) {
+        const int kind = r.kind;
+        int tpos = 0, range = 0, tx = 0, ty = 0;
+        bool search = false;
+        switch (kind) {
             case AA_TRAIN: {  // Train.java:48-96
                 const int x = un.x, y = un.y;
                 int best_dir = -1, best_score = -1;
+#pragma unroll 1
                 for (int d = 0; d < 4; d++) {
                     int nx = x + dir_dx(d), ny = y + dir_dy(d);
                     if (nx < 0 || ny < 0 || nx >= W || ny >= H) continue;
@@ -1408,105 +1404,63 @@ struct Sim {
                     }
                 }
                 r.target = 1;  // completed = true
-                if (best_dir != -1 && action_allowed(i, T_PRODUCE, best_dir, r.utype, vp, costB)) {
-                    out.type = T_PRODUCE;
-                    out.param = (int16_t)best_dir;
-                    out.utype = r.utype;
-                    return true;
-                }
-                return false;
+                if (best_dir == -1) return false;
+                out.type = T_PRODUCE;
+                out.param = (int16_t)best_dir;
+                out.utype = r.utype;
+                break;
             }
-            case AA_BUILD: {  // Build.java:56-78
-                int mv = o_astar(self, i, r.x + r.y * W, 1, vp);
-                if (mv >= 0) {
-                    if (action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
-                        out.type = T_MOVE;
-                        out.param = (int16_t)mv;
-                        return true;
-                    }
-                    return false;
-                }
-                int d = -1;
-                if (r.x == un.x && r.y == un.y - 1) d = D_UP;
-                if (r.x == un.x + 1 && r.y == un.y) d = D_RIGHT;
-                if (r.x == un.x && r.y == un.y + 1) d = D_DOWN;
-                if (r.x == un.x - 1 && r.y == un.y) d = D_LEFT;
-                if (d >= 0 && action_allowed(i, T_PRODUCE, d, r.utype, vp, costB)) {
-                    out.type = T_PRODUCE;
-                    out.param = (int16_t)d;
-                    out.utype = r.utype;
-                    return true;
-                }
-                return false;
-            }
-            case AA_HARVEST: {  // Harvest.java:71-114
-                const bool carrying = un.res != 0;
-                int ti = find_uid(carrying ? r.base : r.target, vp);
+            case AA_BUILD:  // Build.java:56-78
+                tx = r.x, ty = r.y, range = 1, search = true;
+                break;
+            case AA_MOVE:  // Move.java:53-59: findPath = findPathToPositionInRange(.., 0, ..)
+                tx = r.x, ty = r.y, range = 0, search = true;
+                break;
+            case AA_HARVEST:  // Harvest.java:71-114
                 if (ti < 0) return false;
-                const Unit& tg = u[ti];
-                int mv = o_astar(self, i, tg.x + tg.y * W, 1, vp);
-                if (mv >= 0) {
-                    if (action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
-                        out.type = T_MOVE;
-                        out.param = (int16_t)mv;
-                        return true;
-                    }
-                    return false;
-                }
-                int d = -1;
-                if (tg.x == un.x && tg.y == un.y - 1) d = D_UP;
-                else if (tg.x == un.x + 1 && tg.y == un.y) d = D_RIGHT;
-                else if (tg.x == un.x && tg.y == un.y + 1) d = D_DOWN;
-                else if (tg.x == un.x - 1 && tg.y == un.y) d = D_LEFT;
-                if (d < 0) return false;
-                out.type = carrying ? T_RETURN : T_HARVEST;
-                out.param = (int16_t)d;
-                return true;
-            }
-            case AA_MOVE: {  // Move.java:53-59: findPath = findPathToPositionInRange(.., 0, ..)
-                int mv = o_astar(self, i, r.x + r.y * W, 0, vp);
-                if (mv >= 0 && action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
-                    out.type = T_MOVE;
-                    out.param = (int16_t)mv;
-                    return true;
-                }
-                return false;
-            }
+                tx = u[ti].x, ty = u[ti].y, range = 1, search = true;
+                break;
             case AA_ATTACK: {  // Attack.java:50-65
-                int ti = find_uid(r.target, vp);
                 if (ti < 0) return false;
-                const Unit& tg = u[ti];
-                int dx = tg.x - un.x, dy = tg.y - un.y;
-                int rg = ut_range(un.type);
-                if (dx * dx + dy * dy <= rg * rg) {
+                tx = u[ti].x, ty = u[ti].y;
+                const int dx = tx - un.x, dy = ty - un.y;
+                range = ut_range(un.type);
+                if (dx * dx + dy * dy <= range * range) {
                     out.type = T_ATTACK;
-                    out.x = tg.x;
-                    out.y = tg.y;
+                    out.x = (int16_t)tx;
+                    out.y = (int16_t)ty;
                     return true;
                 }
-                int mv = o_astar(self, i, tg.x + tg.y * W, rg, vp);
-                if (mv >= 0 && action_allowed(i, T_MOVE, mv, -1, vp, costB)) {
-                    out.type = T_MOVE;
-                    out.param = (int16_t)mv;
+                search = true;
+                break;
+            }
+            default: return false;
+        }
+        if (search) {
+            tpos = tx + ty * W;
+            const int mv = astar_first_move(i, tpos, range, vp);
+            if (mv >= 0) {
+                out.type = T_MOVE;
+                out.param = (int16_t)mv;
+            } else {
+                if (kind == AA_MOVE || kind == AA_ATTACK) return false;
+                // Build / Harvest: act on the adjacent target
+                int d = -1;
+                if (tx == un.x && ty == un.y - 1) d = D_UP;
+                else if (tx == un.x + 1 && ty == un.y) d = D_RIGHT;
+                else if (tx == un.x && ty == un.y + 1) d = D_DOWN;
+                else if (tx == un.x - 1 && ty == un.y) d = D_LEFT;
+                if (d < 0) return false;
+                out.param = (int16_t)d;
+                if (kind == AA_HARVEST) {  // Harvest.java:97-113: no isUnitActionAllowed test
+                    out.type = un.res != 0 ? T_RETURN : T_HARVEST;
                     return true;
                 }
-                return false;
+                out.type = T_PRODUCE;
+                out.utype = r.utype;
             }
         }
-        return false;
-    }
-
-    MRTS_HD bool aa_completed(const AbstractAct& r, int i, int vp) const {
-        switch (r.kind) {
-            case AA_TRAIN: return r.target != 0;                                   // Train.java:30-32
-            case AA_BUILD: return unit_at_v(r.x, r.y, vp) >= 0;                    // Build.java:33-37
-            case AA_HARVEST:                                                       // Harvest.java:42-48
-                if (u[i].res > 0) return find_uid(r.base, vp) < 0;
-                return find_uid(r.target, vp) < 0;
-            case AA_ATTACK: return find_uid(r.target, vp) < 0;                     // Attack.java:30-33
-            case AA_MOVE: return u[i].x == r.x && u[i].y == r.y;                   // Move.java:32-34
-        }
-        return true;
+        return action_allowed(i, out.type, out.param, out.utype, vp, costB);
     }
 
     // AbstractionLayerAI.translateActions, AbstractionLayerAI.java:58-113 -> pa2
@@ -1527,20 +1481,35 @@ struct Sim {
                 continue;
             }
             r.kind &= AA_KIND_MASK;
-            int i = find_uid(r.unit, vp);
+            const int i = find_uid(r.unit, vp);
             bool del = false;
             if (i < 0) del = true;
             else if (enemy_seen && u[i].a_type >= 0 && (u[i].flags & UF_AA_ATTACK) && ut_can_harvest(u[i].type)) {
                 // busy worker with an Attack entry: the reference's per-frame re-put keeps it alive (see worker_rush)
-            } else if (aa_completed(r, i, vp)) del = true;
-            else if (u[i].a_type < 0) {
-                PAct out;
-                if (aa_execute(r, i, vp, costB, out)) {
-                    pa2[st->npa2++] = out;
-                    int pos = usage_pos(u[i], out.type, out.param);
-                    if (pos != -0x7fff) {
-                        bit_set(bitsC, pos);
-                        rows_reserve(pos);
+            } else {
+                // the unit the entry refers to (Harvest.java:42-48, Attack.java:30-33): gone from the view = completed
+                int ti = -1;
+                if (r.kind == AA_HARVEST) ti = find_uid(u[i].res > 0 ? r.base : r.target, vp);
+                else if (r.kind == AA_ATTACK) ti = find_uid(r.target, vp);
+                bool completed;
+                switch (r.kind) {
+                    case AA_TRAIN: completed = r.target != 0; break;                 // Train.java:30-32
+                    case AA_BUILD: completed = unit_at_v(r.x, r.y, vp) >= 0; break;  // Build.java:33-37
+                    case AA_HARVEST:
+                    case AA_ATTACK: completed = ti < 0; break;
+                    case AA_MOVE: completed = u[i].x == r.x && u[i].y == r.y; break;  // Move.java:32-34
+                    default: completed = true;
+                }
+                if (completed) del = true;
+                else if (u[i].a_type < 0) {
+                    PAct out;
+                    if (aa_execute(r, i, ti, vp, costB, out)) {
+                        pa2[st->npa2++] = out;
+                        int pos = usage_pos(u[i], out.type, out.param);
+                        if (pos != -0x7fff) {
+                            bit_set(bitsC, pos);
+                            rows_reserve(pos);
+                        }
                     }
                 }
             }
@@ -1569,8 +1538,8 @@ struct Sim {
                 pa2[kept++] = d;
             }
         }
+        fill_with_nones(pa2, kept, player, 10, vp);
         st->npa2 = kept;
-        o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);
     }
 
     // AbstractionLayerAI.findBuildingPosition, AbstractionLayerAI.java:143-228.  `reserved` = the one position an
@@ -1596,7 +1565,34 @@ struct Sim {
         return -1;
     }
 
-    MRTS_HD void bot_melee(int i, int player, int vp) {  // WorkerRush.meleeUnitBehavior, WorkerRush.java:106-122
+    // ---- the puts of one getAction call.  A bot's getAction makes its puts in a fixed order (the table's insertion
+    // order decides who wins a resource conflict in translateActions); here the call first QUEUES them as jobs in
+    // that order (worker_rush_jobs / light_rush_jobs) and one loop (bot_jobs) executes the queue, so that each
+    // decision routine below is inlined exactly once.  The queue lives in pa2 (free until translate_actions):
+    // at most two jobs per unit (build or harvest, then attack when it stays free), 4 bytes each.
+    enum { JOB_TRAIN = 0, JOB_MELEE = 1, JOB_BUILD = 2, JOB_HARVEST = 3 };
+    struct Job {
+        uint16_t unit;  // unit index
+        uint8_t kind;
+        int8_t utype;   // Train / Build
+    };
+    static MRTS_HD Job make_job(int unit, int kind, int utype) {
+        Job j;
+        j.unit = (uint16_t)unit;
+        j.kind = (uint8_t)kind;
+        j.utype = (int8_t)utype;
+        return j;
+    }
+    // one unit per lane: the picked ones join the queue in unit order
+    MRTS_HD void jobs_append(Job* q, int& nq, bool pick, int i, int kind, int utype) const {
+        const unsigned m = wballot(pick);
+        if (pick) q[nq + popc(m & lanes_below())] = make_job(i, kind, utype);
+        nq += popc(m);
+    }
+
+    // WorkerRush.meleeUnitBehavior, WorkerRush.java:106-122: Attack(closest enemy); the PO* variants explore when
+    // none is in view.  true = `r` holds the put.
+    MRTS_HD bool melee_target(int i, int player, int vp, AbstractAct& r) {
         const int n = nunits();
         const int ux = u[i].x, uy = u[i].y;
         int best = NO_KEY;
@@ -1612,80 +1608,60 @@ struct Sim {
         best = wmin(best);
         const int closest = best == NO_KEY ? -1 : (best & 0xFFFF);
         if (closest >= 0) {
-            AbstractAct r;
-            r.unit = u[i].uid;
             r.kind = AA_ATTACK;
-            r.utype = -1;
-            r.x = r.y = 0;
             r.target = u[closest].uid;
-            r.base = NO_UID;
-            aa_put(r, i);
-        } else if (st->explore && vp >= 0) {
-            // PO*.meleeUnitBehavior (partialobservability/POWorkerRush.java:56-76): the state is a
-            // PartiallyObservableGameState (vp >= 0) and shows no enemy -> Move to the nearest cell that is not
-            // observable (row-major scan with strict <: lowest cell index among equal distances)
-            if (!st->unobs_ready) {  // bitsC (free until translate_actions): bit c = cell c is NOT within sight of an own unit
-#pragma unroll 1
-                for (int base = 0; base < HW; base += nl) {
-                    const int c = base + lane;
-                    bool seen = true;
-                    if (c < HW) {
-                        const int cx = c % W, cy = c / W;
-                        seen = false;
-#pragma unroll 1
-                        for (int j = 0; j < n && !seen; j++) {
-                            const Unit& o = u[j];
-                            if (o.player != player) continue;
-                            const int dx = o.x - cx, dy = o.y - cy, rr = ut_sight(o.type);
-                            seen = dx * dx + dy * dy <= rr * rr;
-                        }
-                    }
-#if defined(__CUDA_ARCH__)
-                    const unsigned word = wballot(!seen);
-                    if (lane == 0) bitsC[base >> 5] = word;
-#else
-                    if ((c & 31) == 0) bitsC[c >> 5] = 0;
-                    if (!seen) bitsC[c >> 5] |= 1u << (c & 31);
-#endif
-                }
-                st->unobs_ready = 1;
-                wsync();
-            }
-            int bestc = NO_KEY;
-#pragma unroll 1
-            for (int c = lane; c < HW; c += nl) {
-                if (!((bitsC[c >> 5] >> (c & 31)) & 1u)) continue;
-                const int dx = ux - c % W, dy = uy - c / W;
-                const int key = ((dx * dx + dy * dy) << 14) | c;
-                if (key < bestc) bestc = key;
-            }
-            bestc = wmin(bestc);
-            if (bestc != NO_KEY) {
-                const int c = bestc & 0x3FFF;
-                AbstractAct r;
-                r.unit = u[i].uid;
-                r.kind = AA_MOVE;
-                r.utype = -1;
-                r.x = (int16_t)(c % W);
-                r.y = (int16_t)(c / W);
-                r.target = NO_UID;
-                r.base = NO_UID;
-                aa_put(r, i);
-            }
+            return true;
         }
+        if (!(st->explore && vp >= 0)) return false;
+        // PO*.meleeUnitBehavior (partialobservability/POWorkerRush.java:56-76): the state is a
+        // PartiallyObservableGameState (vp >= 0) and shows no enemy -> Move to the nearest cell that is not
+        // observable (row-major scan with strict <: lowest cell index among equal distances)
+        if (!st->unobs_ready) {  // bitsC (free until translate_actions): bit c = cell c is NOT within sight of an own unit
+#pragma unroll 1
+            for (int base = 0; base < HW; base += nl) {
+                const int c = base + lane;
+                bool seen = true;
+                if (c < HW) {
+                    const int cx = c % W, cy = c / W;
+                    seen = false;
+#pragma unroll 1
+                    for (int j = 0; j < n && !seen; j++) {
+                        const Unit& o = u[j];
+                        if (o.player != player) continue;
+                        const int dx = o.x - cx, dy = o.y - cy, rr = ut_sight(o.type);
+                        seen = dx * dx + dy * dy <= rr * rr;
+                    }
+                }
+#if defined(__CUDA_ARCH__)
+                const unsigned word = wballot(!seen);
+                if (lane == 0) bitsC[base >> 5] = word;
+#else
+                if ((c & 31) == 0) bitsC[c >> 5] = 0;
+                if (!seen) bitsC[c >> 5] |= 1u << (c & 31);
+#endif
+            }
+            st->unobs_ready = 1;
+            wsync();
+        }
+        int bestc = NO_KEY;
+#pragma unroll 1
+        for (int c = lane; c < HW; c += nl) {
+            if (!((bitsC[c >> 5] >> (c & 31)) & 1u)) continue;
+            const int dx = ux - c % W, dy = uy - c / W;
+            const int key = ((dx * dx + dy * dy) << 14) | c;
+            if (key < bestc) bestc = key;
+        }
+        bestc = wmin(bestc);
+        if (bestc == NO_KEY) return false;
+        const int c = bestc & 0x3FFF;
+        r.kind = AA_MOVE;
+        r.x = (int16_t)(c % W);
+        r.y = (int16_t)(c / W);
+        return true;
     }
-    MRTS_HD void aa_harvest(int i, int target, int base) {
-        AbstractAct r;
-        r.unit = u[i].uid;
-        r.kind = AA_HARVEST;
-        r.utype = -1;
-        r.x = r.y = 0;
-        r.target = target >= 0 ? u[target].uid : (uint16_t)NO_UID;
-        r.base = base >= 0 ? u[base].uid : (uint16_t)NO_UID;
-        aa_put(r, i);
-    }
-    // WorkerRush.workersBehavior tail, WorkerRush.java:148-197: true = the worker stays free
-    MRTS_HD bool bot_harvest(int w, int player, int vp) {
+    // WorkerRush.workersBehavior tail, WorkerRush.java:148-197 (LightRush.java:213-244): nearest resource / own
+    // stockpile; `put` = (re)assign Harvest in `r`; returns true when the worker stays free.  ke = its table entry.
+    MRTS_HD bool harvest_target(int w, int player, int vp, int ke, AbstractAct& r, bool& put) {
         const int n = nunits();
         const int wx = u[w].x, wy = u[w].y;
         int kres = NO_KEY, kbase = NO_KEY;
@@ -1706,23 +1682,26 @@ struct Sim {
         kres = wmin(kres);
         kbase = wmin(kbase);
         const int cres = kres == NO_KEY ? -1 : (kres & 0xFFFF), cbase = kbase == NO_KEY ? -1 : (kbase & 0xFFFF);
-        const int k = aa_find(u[w].uid);
-        const bool isharv = k >= 0 && (aa[k].kind & AA_KIND_MASK) == AA_HARVEST;
+        const bool isharv = ke >= 0 && (aa[ke].kind & AA_KIND_MASK) == AA_HARVEST;
+        r.kind = AA_HARVEST;
         if (u[w].res > 0) {
-            if (cbase >= 0) {
-                if (!isharv || aa[k].base != u[cbase].uid) aa_harvest(w, -1, cbase);
-                return false;
+            if (cbase < 0) return true;
+            if (!isharv || aa[ke].base != u[cbase].uid) {
+                r.base = u[cbase].uid;  // Harvest(null, base)
+                put = true;
             }
-        } else {
-            if (cres >= 0 && cbase >= 0) {
-                if (!isharv || aa[k].target != u[cres].uid || aa[k].base != u[cbase].uid) aa_harvest(w, cres, cbase);
-                return false;
-            }
+            return false;
         }
-        return true;
+        if (cres < 0 || cbase < 0) return true;
+        if (!isharv || aa[ke].target != u[cres].uid || aa[ke].base != u[cbase].uid) {
+            r.target = u[cres].uid;
+            r.base = u[cbase].uid;
+            put = true;
+        }
+        return false;
     }
 
-    // WorkerRush.getAction, J/ai/abstraction/WorkerRush.java:63-104 -> pa2
+    // WorkerRush.getAction, J/ai/abstraction/WorkerRush.java:63-204 -> job queue.
     //
     // The reference re-puts Attack(closest enemy) for EVERY free worker on every frame, busy or not
     // (workersBehavior, :198-203).  For a worker that is busy and whose table entry already is an
@@ -1731,15 +1710,13 @@ struct Sim {
     // target is a unit of this frame's view the entry is never "completed" in translateActions.  So
     // such workers are skipped and translate_actions keeps their entry -- provided an enemy is in
     // view at all (otherwise the reference puts nothing and the stale entry is checked as usual).
-    MRTS_HD void worker_rush(int player, int vp) {
+    MRTS_HD int worker_rush_jobs(int player, int vp, Job* q, bool& enemy_seen_out) {
         wsync();
-        const int t_wr = tick();
         const int n = nunits();
         const int pres = hdr->res[player];
-        // census (:124-137) + is any enemy in view + which units need a put this frame: one unit per lane
+        // census (:124-137) + is any enemy in view: one unit per lane
         int nbases = 0, nworkers = 0, kw0 = NO_KEY, kw1 = NO_KEY;
         bool enemy_seen = false;
-        wsync();
 #pragma unroll 1
         for (int base = 0; base < n; base += nl) {
             const int i = base + lane;
@@ -1768,67 +1745,30 @@ struct Sim {
             }
             nworkers += popc(mw);
         }
+        enemy_seen_out = enemy_seen;
         const int w0 = kw0 == NO_KEY ? -1 : kw0, w1 = kw1 == NO_KEY ? -1 : kw1;
+        int nq = 0;
 #pragma unroll 1
-        for (int base = 0; base < n; base += nl) {  // idle bases train (:102-104), idle melee units attack (:106-122)
+        for (int base = 0; base < n; base += nl) {  // idle bases train (:102-104)
             const int i = base + lane;
-            bool train = false, melee = false;
-            if (i < n) {
-                const Unit& un = u[i];
-                train = un.type == UT_BASE && un.player == player && un.a_type < 0 && pres >= ut_cost(UT_WORKER);
-                melee = ut_can_attack(un.type) && !ut_can_harvest(un.type) && un.player == player && un.a_type < 0;
-            }
-            unsigned mt = wballot(train);
-#pragma unroll 1
-            while (mt) {
-                const int j = base + ffs32(mt) - 1;
-                mt &= mt - 1;
-                AbstractAct r;
-                r.unit = u[j].uid;
-                r.kind = AA_TRAIN;
-                r.utype = UT_WORKER;
-                r.x = r.y = 0;
-                r.target = 0;
-                r.base = NO_UID;
-                aa_put(r, j);
-            }
-            wsync();
+            jobs_append(q, nq, i < n && u[i].type == UT_BASE && u[i].player == player && u[i].a_type < 0 && pres >= ut_cost(UT_WORKER), i, JOB_TRAIN, UT_WORKER);
         }
 #pragma unroll 1
-        for (int base = 0; base < n; base += nl) {
+        for (int base = 0; base < n; base += nl) {  // idle melee units attack (:106-122)
             const int i = base + lane;
-            unsigned mm = wballot(i < n && ut_can_attack(u[i].type) && !ut_can_harvest(u[i].type) && u[i].player == player && u[i].a_type < 0);
-#pragma unroll 1
-            while (mm) {
-                const int j = base + ffs32(mm) - 1;
-                mm &= mm - 1;
-                o_bot_melee(self, j, player, vp);
-            }
+            jobs_append(q, nq, i < n && ut_can_attack(u[i].type) && !ut_can_harvest(u[i].type) && u[i].player == player && u[i].a_type < 0, i, JOB_MELEE, -1);
         }
         // workersBehavior, WorkerRush.java:124-204
         if (nworkers > 0) {
             const bool want_base = nbases == 0 && pres >= ut_cost(UT_BASE);
             const int builder = want_base ? w0 : -1;
             const int harvester = want_base ? w1 : w0;
-            if (builder >= 0) {  // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245
-                int k = aa_find(u[builder].uid);
-                if (k < 0 || (aa[k].kind & AA_KIND_MASK) != AA_BUILD || aa[k].utype != UT_BASE) {
-                    int pos = find_building_position(u[builder].x, u[builder].y, vp);
-                    AbstractAct r;
-                    r.unit = u[builder].uid;
-                    r.kind = AA_BUILD;
-                    r.utype = UT_BASE;
-                    r.x = (int16_t)(pos % W);  // pos == -1 -> (-1, 0): Java % and / truncate like C++
-                    r.y = (int16_t)(pos / W);
-                    r.target = NO_UID;
-                    r.base = NO_UID;
-                    aa_put(r, builder);
-                }
-            }
-            bool hfree = false;
-            if (harvester >= 0) hfree = bot_harvest(harvester, player, vp);
+            wsync();
+            if (builder >= 0) q[nq++] = make_job(builder, JOB_BUILD, UT_BASE);      // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245
+            if (harvester >= 0) q[nq++] = make_job(harvester, JOB_HARVEST, -1);     // a harvester that stays free attacks last (bot_jobs)
+            wsync();
 #pragma unroll 1
-            for (int base = 0; base < n; base += nl) {  // one unit per lane picks the workers that need a put, in unit order
+            for (int base = 0; base < n; base += nl) {  // every other worker attacks, in unit order
                 const int i = base + lane;
                 bool need = false;
                 if (i < n) {
@@ -1836,58 +1776,20 @@ struct Sim {
                     need = un.player == player && ut_can_harvest(un.type) && i != builder && i != harvester &&
                            !(enemy_seen && un.a_type >= 0 && (un.flags & UF_AA_ATTACK));  // unobservable re-put, see above
                 }
-                unsigned mn = wballot(need);
-#pragma unroll 1
-                while (mn) {
-                    const int j = base + ffs32(mn) - 1;
-                    mn &= mn - 1;
-                    o_bot_melee(self, j, player, vp);
-                }
+                jobs_append(q, nq, need, i, JOB_MELEE, -1);
             }
-            if (hfree) o_bot_melee(self, harvester, player, vp);
         }
-        st->tp[1] = tick() - t_wr;
-        const int t_tr = tick();
-        translate_actions(player, vp, enemy_seen);
-        st->tp[2] = tick() - t_tr;
-    }
-
-    // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245; returns the position it reserved, or `reserved` unchanged
-    MRTS_HD int build_if_not_building(int i, int ut, int vp, int reserved) {
-        const int k = aa_find(u[i].uid);
-        if (k >= 0 && (aa[k].kind & AA_KIND_MASK) == AA_BUILD && aa[k].utype == ut) return reserved;
-        const int pos = find_building_position(u[i].x, u[i].y, vp, reserved);
-        AbstractAct r;
-        r.unit = u[i].uid;
-        r.kind = AA_BUILD;
-        r.utype = (int8_t)ut;
-        r.x = (int16_t)(pos % W);  // pos == -1 -> (-1, 0): Java % and / truncate like C++
-        r.y = (int16_t)(pos / W);
-        r.target = NO_UID;
-        r.base = NO_UID;
-        aa_put(r, i);
-        return pos;  // reservedPositions.add(pos), also when it is -1
-    }
-    MRTS_HD void aa_train(int i, int ut) {
-        AbstractAct r;
-        r.unit = u[i].uid;
-        r.kind = AA_TRAIN;
-        r.utype = (int8_t)ut;
-        r.x = r.y = 0;
-        r.target = 0;
-        r.base = NO_UID;
-        aa_put(r, i);
-    }
-
-    // LightRush.getAction, J/ai/abstraction/LightRush.java:77-254 -> pa2.  Every put of the reference is made,
-    // in its order: bases, barracks, melee units, then the workers (builders, harvesters, the rest attack).
-    MRTS_HD void light_rush(int player, int vp, int rush_ut) {  // rush_ut: what the barracks train (UT_LIGHT / UT_HEAVY / UT_RANGED)
         wsync();
-        const int t_lr = tick();
+        return nq;
+    }
+
+    // LightRush.getAction, J/ai/abstraction/LightRush.java:77-254 -> job queue.  Every put of the reference is made,
+    // in its order: bases, barracks, melee units, then the workers (builders, harvesters, the rest attack).
+    MRTS_HD int light_rush_jobs(int player, int vp, int rush_ut, Job* q) {  // rush_ut: what the barracks train (UT_LIGHT / UT_HEAVY / UT_RANGED)
+        wsync();
         const int n = nunits();
         const int pres = hdr->res[player];
         int nbases = 0, nbarracks = 0, nworkers = 0;
-        wsync();
 #pragma unroll 1
         for (int base = 0; base < n; base += nl) {  // census, one unit per lane (a bot sees only its view)
             const int i = base + lane;
@@ -1896,6 +1798,7 @@ struct Sim {
             nbarracks += popc(wballot(mine && u[i].type == UT_BARRACKS));
             nworkers += popc(wballot(mine && u[i].type == UT_WORKER));
         }
+        int nq = 0;
         // three passes in the reference's order (:93-119): idle bases, idle barracks, idle melee units
 #pragma unroll 1
         for (int pass = 0; pass < 3; pass++) {
@@ -1909,22 +1812,14 @@ struct Sim {
                     const int t = u[i].type;
                     pick = pass == 0 ? t == UT_BASE : pass == 1 ? t == UT_BARRACKS : (ut_can_attack(t) && !ut_can_harvest(t));
                 }
-                unsigned m = wballot(pick);
-#pragma unroll 1
-                while (m) {
-                    const int j = base + ffs32(m) - 1;
-                    m &= m - 1;
-                    if (pass == 0) aa_train(j, UT_WORKER);
-                    else if (pass == 1) aa_train(j, rush_ut);
-                    else o_bot_melee(self, j, player, vp);
-                }
-                wsync();
+                jobs_append(q, nq, pick, i, pass == 2 ? JOB_MELEE : JOB_TRAIN, pass == 0 ? UT_WORKER : rush_ut);
             }
         }
-        // workersBehavior, :160-254: the workers in unit order; the first may build a base, the next a barracks
-        uint16_t* still_free = (uint16_t*)pa2;  // pa2 is only filled by translate_actions below
-        int nfree = 0, used = 0, reserved = NO_POS, taken = 0;
+        // workersBehavior, :160-254: the workers in unit order; the first may build a base, the next a barracks,
+        // every other one harvests (and attacks when it stays free: queued by bot_jobs behind all of these)
+        int used = 0, taken = 0;
         const bool want_base = nbases == 0 && pres >= ut_cost(UT_BASE);
+        wsync();
 #pragma unroll 1
         for (int base = 0; base < n; base += nl) {
             const int i = base + lane;
@@ -1934,45 +1829,94 @@ struct Sim {
                 const int j = base + ffs32(m) - 1;
                 m &= m - 1;
                 if (taken == 0 && want_base) {
-                    reserved = build_if_not_building(j, UT_BASE, vp, reserved);
+                    q[nq++] = make_job(j, JOB_BUILD, UT_BASE);
                     used += ut_cost(UT_BASE);
                     taken = 1;
                     continue;
                 }
                 if (taken <= 1 && nbarracks == 0 && pres >= ut_cost(UT_BARRACKS) + used) {
                     if (taken == 0 || want_base) {  // at most one barracks builder: the first worker left after the base builder
-                        reserved = build_if_not_building(j, UT_BARRACKS, vp, reserved);
+                        q[nq++] = make_job(j, JOB_BUILD, UT_BARRACKS);
                         used += ut_cost(UT_BARRACKS);
                         taken = 2;
                         continue;
                     }
                 }
                 if (taken < 2) taken = 2;  // the builder slots are decided by the first workers only
-                if (bot_harvest(j, player, vp)) {
-                    if (lane == 0) still_free[nfree] = (uint16_t)j;
-                    nfree++;
-                }
+                q[nq++] = make_job(j, JOB_HARVEST, -1);
             }
         }
         wsync();
-#pragma unroll 1
-        for (int k = 0; k < nfree; k++) o_bot_melee(self, still_free[k], player, vp);
-        wsync();
-        st->tp[1] = tick() - t_lr;
-        const int t_tr = tick();
-        translate_actions(player, vp, false);
-        st->tp[2] = tick() - t_tr;
+        return nq;
     }
 
-    // the scripted opponent's PlayerAction for `player` -> pa2
+    // executes the queue; a harvester that stays free joins its tail as an attacker (WorkerRush.java:198-203,
+    // LightRush.java:246-253).  `reserved` = the position an earlier build of this frame took (LightRush: base, then barracks).
+    MRTS_HD void bot_jobs(Job* q, int nq, int player, int vp) {
+        int reserved = NO_POS;
+#pragma unroll 1
+        for (int k = 0; k < nq; k++) {
+            wsync();
+            const Job jb = q[k];
+            const int j = jb.unit;
+            const int ke = aa_find(u[j].uid);  // the unit's entry in the table, -1 = none
+            AbstractAct r;
+            r.unit = u[j].uid;
+            r.kind = AA_TRAIN;
+            r.utype = -1;
+            r.x = r.y = 0;
+            r.target = NO_UID;
+            r.base = NO_UID;
+            bool put = false;
+            switch (jb.kind) {
+                case JOB_TRAIN:
+                    r.utype = jb.utype;
+                    r.target = 0;  // Train's `completed` flag
+                    put = true;
+                    break;
+                case JOB_MELEE: put = melee_target(j, player, vp, r); break;
+                case JOB_BUILD: {  // buildIfNotAlreadyBuilding, AbstractionLayerAI.java:230-245
+                    if (ke >= 0 && (aa[ke].kind & AA_KIND_MASK) == AA_BUILD && aa[ke].utype == jb.utype) break;
+                    const int pos = find_building_position(u[j].x, u[j].y, vp, reserved);
+                    r.kind = AA_BUILD;
+                    r.utype = jb.utype;
+                    r.x = (int16_t)(pos % W);  // pos == -1 -> (-1, 0): Java % and / truncate like C++
+                    r.y = (int16_t)(pos / W);
+                    reserved = pos;  // reservedPositions.add(pos), also when it is -1
+                    put = true;
+                    break;
+                }
+                case JOB_HARVEST:
+                    if (harvest_target(j, player, vp, ke, r, put)) {
+                        wsync();
+                        q[nq++] = make_job(j, JOB_MELEE, -1);
+                        wsync();
+                    }
+                    break;
+            }
+            if (put) aa_put(r, j, ke);
+        }
+        wsync();
+    }
+
+    // the scripted opponent's PlayerAction for `player` -> pa2 (heavy kernels only; PassiveAI.getAction,
+    // J/ai/PassiveAI.java:41-45, has no table entries: translate_actions then only fills NONE(10))
     MRTS_HD void bot_action(int which, int player, int vp) {
         st->npa2 = 0;
         st->explore = ai_explores(which);
         st->unobs_ready = 0;
         wsync();
-        if (which == AI_WORKER_RUSH || which == AI_PO_WORKER_RUSH) worker_rush(player, vp);
-        else if (ai_barracks_rush(which)) light_rush(player, vp, ai_rush_unit(which));
-        else o_fill_with_nones(self, pa2, &st->npa2, player, 10, vp);  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
+        const int t_puts = tick();
+        Job* const q = (Job*)pa2;
+        int nq = 0;
+        bool enemy_seen = false;
+        if (which == AI_WORKER_RUSH || which == AI_PO_WORKER_RUSH) nq = worker_rush_jobs(player, vp, q, enemy_seen);
+        else if (ai_barracks_rush(which)) nq = light_rush_jobs(player, vp, ai_rush_unit(which), q);
+        bot_jobs(q, nq, player, vp);
+        const int t_tr = tick();
+        st->tp[1] = t_tr - t_puts;
+        translate_actions(player, vp, enemy_seen);
+        st->tp[2] = tick() - t_tr;
     }
 
     // ================================================================== one environment step
@@ -1980,53 +1924,57 @@ struct Sim {
     // On return: st->rew[][] holds the six reward terms per view, st->gameover/st->winner are set, the unit
     // array still contains units killed this cycle (flagged) so that stale partially observable
     // views can be encoded; the caller then runs compact() or reloads the map template.
+    //
+    // HEAVY = the game has a scripted player built on AbstractionLayerAI (table + path searches); light kernels
+    // (self-play, PassiveAI) are compiled without that code.  The three clients of the reference differ only in
+    // the order of four operations -- {player 0, player 1} x {make the PlayerAction, issueSafe it} -- so one loop
+    // runs them and every rule function below has a single call site:
+    //   JNIGridnetClientSelfPlay.gameStep (:159-189)   act 0, issue 0, act 1, issue 1  (player 1 decodes after player 0's issue)
+    //   JNIGridnetClient.gameStep (:163-196)           act 0, act 1, issue 0, issue 1  (views of both taken before any issue)
+    //   JNIBotClient.gameStep (JNIBotClient.java:108-113)   same order, both players scripted, full state
+    template <int HEAVY>
     MRTS_HD bool step_game() {
         wsync();
-        for (int p = 0; p < 2; p++)
-            for (int k = 0; k < 6; k++) st->rew[p][k] = 0;
-        if (ai == AI_NONE) {
-            // JNIGridnetClientSelfPlay.gameStep, :159-189
-            for (int p = 0; p < 2; p++) {
-                int vp = -1;
-                if (partial) {
-                    o_make_view(self, p);
-                    vp = p;
+        const bool selfplay = ai == AI_NONE;
+        const bool views = partial && ai1 == AI_NONE;  // bot-vs-bot clients ignore partialObs
+#pragma unroll 1
+        for (int k = 0; k < 4; k++) {
+            const int p = selfplay ? (k >> 1) : (k & 1);
+            const bool act = selfplay ? (k & 1) == 0 : k < 2;
+            const bool first_list = selfplay || p == 0;  // self-play games reuse pa for player 1 (pa2 belongs to bot games)
+            PAct* const list = first_list ? pa : pa2;
+            const int t0 = tick();
+            if (act) {
+                if (views && (selfplay || k == 0)) {
+                    const int vlast = selfplay ? p : 1;
+#pragma unroll 1
+                    for (int v = selfplay ? p : 0; v <= vlast; v++) make_view(v);
                 }
-                o_decode_actions(self, p, vp);
-                o_issue_safe(self, pa, st->npa);
+                const int vp = views ? p : -1;
+                const int which = p == 0 ? ai1 : ai;
+                if (which == AI_NONE) {
+                    decode_actions(p, vp);  // -> pa
+                    st->tp[0] = tick() - t0;
+                } else if (HEAVY) {
+                    bot_action(which, p, vp);  // -> pa2
+                    if (p == 0) {              // a scripted player 0: its action is issued first, from pa
+                        wsync();
+                        const int n0 = st->npa2;
+#pragma unroll 1
+                        for (int e = lane; e < n0; e += nl) pa[e] = pa2[e];
+                        st->npa = n0;
+                        wsync();
+                    }
+                } else {  // PassiveAI.getAction, J/ai/PassiveAI.java:41-45
+                    int cnt = 0;
+                    fill_with_nones(list, cnt, p, 10, vp);
+                    if (first_list) st->npa = cnt;
+                    else st->npa2 = cnt;
+                }
+            } else {
+                issue_safe(list, first_list ? st->npa : st->npa2);
+                st->tp[3 + p] = tick() - t0;
             }
-        } else if (ai1 != AI_NONE) {
-            // JNIBotClient.gameStep, J/tests/JNIBotClient.java:108-113: both bots act on the full state (the
-            // client ignores partialObs), player 0's action is issued first
-            bot_action(ai1, 0, -1);
-            wsync();
-            const int n0 = st->npa2;
-            for (int k = lane; k < n0; k += nl) pa[k] = pa2[k];
-            st->npa = n0;
-            wsync();
-            bot_action(ai, 1, -1);
-            o_issue_safe(self, pa, st->npa);
-            o_issue_safe(self, pa2, st->npa2);
-        } else {
-            // JNIGridnetClient.gameStep, :163-196
-            int v0 = -1, v1 = -1;
-            if (partial) {
-                o_make_view(self, 0);
-                o_make_view(self, 1);
-                v0 = 0;
-                v1 = 1;
-            }
-            int t0 = tick();
-            o_decode_actions(self, 0, v0);
-            int t1 = tick();
-            st->tp[0] = t1 - t0;
-            bot_action(ai, 1, v1);
-            t0 = tick();
-            o_issue_safe(self, pa, st->npa);
-            t1 = tick();
-            st->tp[3] = t1 - t0;
-            o_issue_safe(self, pa2, st->npa2);
-            st->tp[4] = tick() - t1;
         }
         const int tc = tick();
         cycle();
@@ -2040,39 +1988,5 @@ struct Sim {
         return st->gameover || hdr->steps >= max_steps;  // JNIGridnetVecClient.java:245-266 / :270-286
     }
 };
-
-// ---- out-of-line entry points (see the declarations above Sim)
-MRTS_HDN int o_astar(const Sim* sp, int i, int targetpos, int range, int vp) {
-    Sim s = *sp;
-    s.lane = Sim::lane_now();
-    return s.astar_first_move(i, targetpos, range, vp);
-}
-MRTS_HDN void o_issue_safe(const Sim* sp, PAct* list, int cnt) {
-    Sim s = *sp;
-    s.lane = Sim::lane_now();
-    s.issue_safe(list, cnt);
-}
-MRTS_HDN void o_decode_actions(const Sim* sp, int player, int vp) {
-    Sim s = *sp;
-    s.lane = Sim::lane_now();
-    s.decode_actions(player, vp);
-}
-MRTS_HDN void o_make_view(const Sim* sp, int p) {
-    Sim s = *sp;
-    s.lane = Sim::lane_now();
-    s.make_view(p);
-}
-MRTS_HDN void o_bot_melee(const Sim* sp, int i, int player, int vp) {
-    Sim s = *sp;
-    s.lane = Sim::lane_now();
-    s.bot_melee(i, player, vp);
-}
-MRTS_HDN void o_fill_with_nones(const Sim* sp, PAct* list, int* cnt, int player, int duration, int vp) {
-    Sim s = *sp;
-    s.lane = Sim::lane_now();
-    int c = *cnt;
-    s.fill_with_nones(list, c, player, duration, vp);
-    *cnt = c;
-}
 
 }  // namespace mrts

@@ -170,6 +170,79 @@ MRTS_HD void patch_mask(const Sim& s, int player, const uint32_t* umask, void* o
     }
 }
 
+// ---- run-time choice of the element size / plane count (the pass itself is not templated on them:
+// the store loops are a small part of its code, the rules are not)
+MRTS_HD void store_obs_rt(int elem, int planes, const uint32_t* words, int HW, void* out, int tid, int nth) {
+    if (elem == 4) {
+        if (planes == 29) store_obs<4, 29>(words, HW, out, tid, nth);
+        else store_obs<4, 31>(words, HW, out, tid, nth);
+    } else {
+        if (planes == 29) store_obs<1, 29>(words, HW, out, tid, nth);
+        else store_obs<1, 31>(words, HW, out, tid, nth);
+    }
+}
+MRTS_HD void zero_mask_rt(int elem, int HW, void* out, int tid, int nth) {
+    if (elem == 4) zero_mask<4>(HW, out, tid, nth);
+    else zero_mask<1>(HW, out, tid, nth);
+}
+MRTS_HD void patch_mask_rt(int elem, const Sim& s, int player, const uint32_t* umask, void* out, int tid, int nth) {
+    if (elem == 4) patch_mask<4>(s, player, umask, out, tid, nth);
+    else patch_mask<1>(s, player, umask, out, tid, nth);
+}
+
+// Phase E (after unit_masks + barrier): the packed form of one view's mask -- one 16-byte entry
+// (cell, 78 bits) per unit of `player` that may act, in ASCENDING CELL ORDER (the expansion kernel builds
+// the mask rows of neighbouring cells together), behind a header word holding their count.  The group's
+// first warp walks the grid 32 cells at a time; a ballot keeps the order.
+MRTS_HD void emit_mask_entries(const Sim& s, int player, const uint32_t* umask, uint32_t* out, int tid, int nth) {
+    if (tid >= 32) return;
+    const int lanes = nth < 32 ? nth : 32;
+    int total = 0;
+#pragma unroll 1
+    for (int base = 0; base < s.HW; base += lanes) {
+        const int c = base + tid;
+        bool take = false;
+        int i = 0;
+        if (c < s.HW) {
+            const uint16_t g = s.grid[c];
+            if (g < G_WALL) {
+                const Unit& un = s.u[g];
+                i = g;
+                take = un.player == player && un.a_type < 0 && !(un.flags & UF_DEAD);
+            }
+        }
+        const unsigned m = Sim::wballot(take);
+        if (take) {
+            uint32_t* e = out + 4 * (size_t)(1 + total + Sim::popc(m & ((1u << tid) - 1u)));
+            e[0] = (uint32_t)c;
+            e[1] = umask[3 * i];
+            e[2] = umask[3 * i + 1];
+            e[3] = umask[3 * i + 2];
+        }
+        total += Sim::popc(m);
+    }
+    if (tid == 0) {
+        out[0] = (uint32_t)total;
+        out[1] = out[2] = out[3] = 0;
+    }
+}
+// host-side / reference expansion of the packed mask entries into (HW, 78) elements (what mrts_expand_kernel
+// does with bulk stores on the device): zero fill + the 78 entries of every listed cell
+template <int ELEM>
+MRTS_HD void expand_mask_entries(const uint32_t* ent, int HW, void* out) {
+    zero_mask<ELEM>(HW, out, 0, 1);
+    const int n = (int)ent[0];
+    for (int k = 0; k < n; k++) {
+        const uint32_t* e = ent + 4 * (size_t)(1 + k);
+        for (int b = 0; b < 78; b++) {
+            const uint32_t bit = (e[1 + (b >> 5)] >> (b & 31)) & 1u;
+            const size_t idx = (size_t)e[0] * 78 + b;
+            if (ELEM == 4) ((int32_t*)out)[idx] = (int32_t)bit;
+            else ((uint8_t*)out)[idx] = (uint8_t)bit;
+        }
+    }
+}
+
 // ---- masked-uniform action sampler (the recipe of the reference's hello_world.py:27-67: an
 // independent categorical per action component restricted to mask == 1; an all-zero group
 // yields 0), driven by a counter-based hash so a run is reproducible from (seed, launch counter).

@@ -52,13 +52,15 @@ static void worker_main(Pool* p, int rank) {
     }
 }
 
+int visible_cores() {
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    int n = sched_getaffinity(0, sizeof(set), &set) == 0 ? CPU_COUNT(&set) : (int)std::thread::hardware_concurrency();
+    return n > 0 ? n : 1;
+}
+
 Pool* pool_create(int threads) {
-    if (threads <= 0) {
-        cpu_set_t set;
-        CPU_ZERO(&set);
-        threads = sched_getaffinity(0, sizeof(set), &set) == 0 ? CPU_COUNT(&set) : (int)std::thread::hardware_concurrency();
-        if (threads <= 0) threads = 1;
-    }
+    if (threads <= 0) threads = visible_cores();
     Pool* p = new Pool();
     p->nthreads = threads;
     for (int r = 1; r < threads; r++) p->workers.emplace_back(worker_main, p, r);  // rank 0 = the caller

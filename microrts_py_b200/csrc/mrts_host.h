@@ -19,6 +19,7 @@ struct Pool;
 Pool* pool_create(int threads /* 0 = all cores this process may use */);
 void pool_destroy(Pool* p);
 int pool_threads(const Pool* p);
+int visible_cores();  // cores this process may run on (sched_getaffinity)
 
 // obs words (n_env, hw) -> one-hot (n_env, hw, planes), elem = 4 (int32) or 1 (uint8)
 void expand_obs(Pool* p, const uint32_t* words, size_t n_env, int hw, int planes, int elem, void* out);

@@ -1,0 +1,62 @@
+// Internal interface between the translation units of libmrts_b200.so.  The rules are compiled in
+// three units (light games, heavy games, the full-capacity / debug kernels) and the expansion
+// kernel in a fourth, so that `make -j` builds them side by side; mrts_api.cu holds the C ABI and
+// the launch logic.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "mrts_step.h"
+
+namespace mrts {
+
+constexpr int GPB_MAX = 4;  // games (warps) per block of the warp kernels, chosen per environment
+
+// ---- rules, one warp per game (mrts_rules_light.cu / mrts_rules_heavy.cu).  regs = 64 / 96 / 128: the
+// register budget variant (__launch_bounds__), chosen per environment from the map size.
+#define MRTS_RULES_API(K)                                                                                          \
+    cudaError_t K##_launch_warp(int regs, const EnvParams& P, int gpb, int smem_per_game, cudaStream_t st);          \
+    cudaError_t K##_launch_block(const EnvParams& P, int threads, int smem, cudaStream_t st);                         \
+    cudaError_t K##_set_smem(int warp_bytes, int block_bytes);                                                        \
+    int K##_warp_regs(int regs); /* registers per thread of the variant (cudaFuncGetAttributes), for introspection */
+MRTS_RULES_API(light)
+MRTS_RULES_API(heavy)
+#undef MRTS_RULES_API
+inline cudaError_t launch_rules_warp(int heavy, int regs, const EnvParams& P, int gpb, int smem_per_game, cudaStream_t st) {
+    return heavy ? heavy_launch_warp(regs, P, gpb, smem_per_game, st) : light_launch_warp(regs, P, gpb, smem_per_game, st);
+}
+// ---- rules + direct outputs, one 256-thread block per game (large maps, direct mode)
+inline cudaError_t launch_rules_block(int heavy, const EnvParams& P, int threads, int smem, cudaStream_t st) {
+    return heavy ? heavy_launch_block(P, threads, smem, st) : light_launch_block(P, threads, smem, st);
+}
+
+// ---- full-capacity pass over a list of games (deferred games; map rotation resets), any game class
+cudaError_t launch_overflow(const EnvParams& P, const int32_t* count, const int32_t* list, int grid, int smem, cudaStream_t st);
+// ---- raw engine access (trace replay)
+struct DebugArgs {
+    int game;
+    int op;  // 0 = issue_safe(rows), 1 = cycle
+    const int32_t* rows7;
+    int n;
+    int* gameover;
+};
+cudaError_t launch_debug(const EnvParams& P, const DebugArgs& A, int smem, cudaStream_t st);
+cudaError_t any_set_smem(int bytes);
+
+// ---- expansion of the packed outputs into the caller's tensors (mrts_expand.cu)
+struct ExpandParams {
+    const uint32_t* pobs;  // (N, HW) observation words
+    const uint32_t* ment;  // (N, 1 + cap, 4) mask entries
+    void* obs;             // (N, H, W, planes) or null
+    void* mask;            // (N, HW, 78) or null
+    int32_t env_lo, env_hi;
+    int32_t HW, planes, elem, cap;
+    int32_t* counter;      // work counter of this launch (zeroed by the caller): views are handed out one at a time
+};
+// true when the shape can take the bulk-store path (every view's obs and mask blocks are multiples of 16 bytes)
+bool expand_supported(int HW, int planes, int elem, const void* obs, const void* mask);
+cudaError_t launch_expand(const ExpandParams& X, int blocks, cudaStream_t st);
+cudaError_t expand_init();
+int expand_smem_bytes();
+int expand_threads();
+
+}  // namespace mrts

@@ -2,6 +2,7 @@
 // (JNIGridnetVecClient, J/tests/JNIGridnetVecClient.java:106-142) and flattens the map templates
 // (PhysicalGameState.load, J/rts/PhysicalGameState.java:685-711) into the pools the kernels read.
 #pragma once
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -110,13 +111,15 @@ inline int build_setup(const mrts_config* cfg, HostSetup& S, std::string& err) {
     P.HW = HW;
     P.cap = cap;
     P.scap = cap;  // the CUDA library may stage fewer (mrts_create)
-    P.ovf = nullptr;
+    P.ovf_cnt = nullptr;
+    P.ovf_list = nullptr;
     P.partial = cfg->partial_obs ? 1 : 0;
     P.planes = P.partial ? 31 : 29;
     P.none_mode = cfg->none_mode ? NONE_FORK : NONE_UPSTREAM;
     P.max_steps = cfg->max_steps;
     P.elem = cfg->elem_bytes;
     P.has_bot = 0;
+    P.any_bot = cfg->num_bot_envs > 0 ? 1 : 0;
     for (int b = 0; b < cfg->num_bot_envs; b++) {
         if (cfg->bot_ai[b] < 0 || cfg->bot_ai[b] >= AI_COUNT) {
             err = "unsupported scripted opponent id";
@@ -220,6 +223,63 @@ inline void export_blob(const uint8_t* blob, int32_t* hdr5, int32_t* rows12, int
             r[7] = r[8] = r[9] = r[10] = r[11] = 0;
         }
     }
+}
+
+// Inverse of export_blob (GameState.fromXML, J/rts/GameState.java:763-915): header + unit rows -> blob.  Derived
+// fields are rebuilt: uids follow the row order (= pgs.units order), the issue order of the pending assignments
+// (the unitActions LinkedHashMap) is `issue_order[i]` ascending when given, else (time of issue, row).  A scripted
+// bot's abstract-action table is not part of a GameState: it starts empty, as after a reset.
+inline bool import_blob(uint8_t* blob, const int32_t* hdr5, const int32_t* rows12, int n, const int32_t* issue_order, int W, int H, std::string& err) {
+    GameHdr* h = (GameHdr*)blob;
+    Unit* u = (Unit*)(blob + 32);
+    memset(h, 0, sizeof(*h));
+    h->time = hdr5[0];
+    h->res[0] = hdr5[1];
+    h->res[1] = hdr5[2];
+    h->steps = hdr5[3];
+    h->nunits = n;
+    h->next_uid = (uint16_t)n;
+    std::vector<int> issued;
+    for (int i = 0; i < n; i++) {
+        const int32_t* r = rows12 + 12 * i;
+        if (r[0] < 0 || r[0] >= N_UTYPES || r[1] < -1 || r[1] > 1 || r[2] < 0 || r[2] >= W || r[3] < 0 || r[3] >= H) {
+            err = "unit row out of range";
+            return false;
+        }
+        Unit& d = u[i];
+        memset(&d, 0, sizeof(d));
+        d.type = (uint8_t)r[0];
+        d.player = (int8_t)r[1];
+        d.x = (uint8_t)r[2];
+        d.y = (uint8_t)r[3];
+        d.res = r[4];
+        d.hp = (int16_t)r[5];
+        d.uid = (uint16_t)i;
+        d.vtype[0] = d.vtype[1] = -1;
+        d.a_type = -1;
+        d.a_param = -1;
+        d.a_utype = -1;
+        if (r[6] >= 0) {
+            if (r[6] > T_ATTACK) {
+                err = "unknown action type";
+                return false;
+            }
+            d.a_type = (int8_t)r[6];
+            d.a_param = (int16_t)r[7];
+            d.a_x = (uint8_t)r[8];
+            d.a_y = (uint8_t)r[9];
+            d.a_utype = (int8_t)r[10];
+            d.a_time = r[11];
+            issued.push_back(i);
+        }
+    }
+    std::stable_sort(issued.begin(), issued.end(), [&](int a, int b) {
+        if (issue_order) return issue_order[a] < issue_order[b];
+        return u[a].a_time < u[b].a_time;
+    });
+    for (size_t k = 0; k < issued.size(); k++) u[issued[k]].a_seq = (uint32_t)k;
+    h->next_seq = (uint32_t)issued.size();
+    return true;
 }
 
 }  // namespace mrts

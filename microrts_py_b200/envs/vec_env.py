@@ -25,6 +25,14 @@ Extra keyword-only arguments (all default to the reference's behaviour):
                 the reference's JNIBotClient; the action rows of those envs are ignored
   fuse_mask     compute the action mask of the resulting state inside ``step`` (one launch,
                 the state is staged once); ``get_action_mask`` then only hands it out
+  pipeline      "auto" (default), "direct" (the rules pass writes the tensors itself) or "split" (rules kernels
+                write a packed form, an expansion kernel streams it into the tensors with bulk async stores while
+                the next chunk's rules run); ``chunks`` = slab chunks of the split pipeline (0 = choose)
+
+``infos`` is always a real ``list`` of ``{"raw_rewards": (6,) float64}`` dicts in the NumPy modes, as in the
+reference (vec_env.py:1036); with ``return_torch=True`` it is a lazy list-like (``RawRewardInfos``) that supports
+``len``, iteration, integer and slice indexing (``list(infos[:])`` as experiments/ppo_gridnet.py:140 does) and
+only reads the device when an entry is looked at.
 """
 from __future__ import annotations
 
@@ -95,7 +103,7 @@ _RF_NAMES = [
     "ProduceCombatUnitRewardFunction",
 ]  # order of vec_env.py:185-195
 
-_DEFAULT_MICRORTS_PATHS = [os.environ.get("MICRORTS_PATH", ""), "/root/reference/gym_microrts/microrts"]
+
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -142,6 +150,8 @@ class MicroRTSGridModeVecEnv:
         threads_per_game=0,
         staged_units=0,
         ai1s=None,
+        pipeline="auto",
+        chunks=0,
     ):
         self.num_selfplay_envs = num_selfplay_envs
         self.num_bot_envs = num_bot_envs
@@ -170,7 +180,8 @@ class MicroRTSGridModeVecEnv:
             )
         if num_selfplay_envs % 2:
             raise ValueError("num_selfplay_envs must be even (two player views per self-play game)")
-        self.microrts_path = microrts_path or next((p for p in _DEFAULT_MICRORTS_PATHS if p and os.path.isdir(p)), "")
+        # maps resolve against an explicit root, $MICRORTS_PATH, or the map pack bundled with the package (maps.py)
+        self.microrts_path = microrts_path or os.environ.get("MICRORTS_PATH", "")
 
         # ---- maps: parsed once, device-resident templates (the reference re-parses per reset)
         cache = {}
@@ -226,6 +237,7 @@ class MicroRTSGridModeVecEnv:
             num_selfplay_envs, num_bot_envs, max_steps, partial_obs, templates, ai_ids,
             none_mode=_capi.NONE_FORK, device=dev_index, elem_bytes=self._np_dtype.itemsize, threads_per_game=threads_per_game, staged_units=staged_units,
             cycle_templates=cycle_templates, bot_ai1=ai1_ids,
+            pipeline={"auto": _capi.PIPELINE_AUTO, "direct": _capi.PIPELINE_DIRECT, "split": _capi.PIPELINE_SPLIT}[pipeline], chunks=int(chunks),
         )  # fmt: skip
         h = C.c_void_p()
         _capi.check(self._lib.mrts_create(C.byref(cfg), C.byref(h)))
@@ -243,7 +255,7 @@ class MicroRTSGridModeVecEnv:
             self.num_planes = [5, 5, 3, len(self.utt["unitTypes"]) + 1, 6, 2, 2]
         obs_length = sum(self.num_planes)
         assert obs_length == self._lib.mrts_planes(self._h)
-        self.observation_space = Box(low=0.0, high=1.0, shape=(self.height, self.width, obs_length), dtype=np.int32)
+        self.observation_space = Box(low=0.0, high=1.0, shape=(self.height, self.width, obs_length), dtype=self._np_dtype.type)
         self.num_planes_len = len(self.num_planes)
         self.num_planes_prefix_sum = [0]
         for num_plane in self.num_planes:
@@ -263,6 +275,7 @@ class MicroRTSGridModeVecEnv:
         self._mask_valid = False
         self._pending_actions: Optional[torch.Tensor] = None
         self._h_actions = torch.zeros(self._shape_act, dtype=torch.int32).pin_memory()
+        self._h_actions_free = None  # event behind the last host->device copy out of _h_actions
         self._rw_t = torch.as_tensor(self.reward_weight, dtype=torch.float64, device=self.device)
         self._host_ring = {}  # name -> [pinned tensors], cursor
         self.source_unit_mask = None
@@ -374,15 +387,23 @@ class MicroRTSGridModeVecEnv:
             if a.device.type == "cuda":
                 a = a.to(device=self.device, dtype=torch.int32).contiguous()
             else:
-                self._h_actions.copy_(a)
-                self._d_actions.copy_(self._h_actions, non_blocking=True)
-                a = self._d_actions
+                a = self._upload_actions(lambda: self._h_actions.copy_(a))
         else:
             a = np.asarray(actions).reshape(self._shape_act)
-            np.copyto(self._h_actions.numpy(), a, casting="unsafe")
-            self._d_actions.copy_(self._h_actions, non_blocking=True)
-            a = self._d_actions
+            a = self._upload_actions(lambda: np.copyto(self._h_actions.numpy(), a, casting="unsafe"))
         self._pending_actions = a
+
+    def _upload_actions(self, fill):
+        """Host actions -> the one pinned staging buffer -> device.  The copy is asynchronous and (return_torch)
+        nothing else synchronises between two steps: wait for the previous copy before the buffer is overwritten."""
+        if self._h_actions_free is not None:
+            self._h_actions_free.synchronize()
+        fill()
+        self._d_actions.copy_(self._h_actions, non_blocking=True)
+        if self._h_actions_free is None:
+            self._h_actions_free = torch.cuda.Event()
+        self._h_actions_free.record(torch.cuda.current_stream(self.device))
+        return self._d_actions
 
     def step_wait(self):
         """vec_env.py:1001-1057: (obs, reward @ reward_weight, done[:, 0], infos)."""
@@ -402,7 +423,9 @@ class MicroRTSGridModeVecEnv:
             self._h_mask_np = m
             if not self.reward_shaping:
                 reward[:, 1:] = 0
-            return o, reward @ self.reward_weight, d.astype(np.bool_), _LazyInfos(reward)
+            # `reward` is one of two alternating buffers: the infos get their own copy, so that rows a wrapper
+            # accumulates over an episode do not change two steps later
+            return o, reward @ self.reward_weight, d.astype(np.bool_), RawRewardInfos(reward.copy())
         obs = self._new(self._shape_obs, self._t_dtype)
         mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
         raw = self._new((N, 6), torch.float64)
@@ -413,7 +436,7 @@ class MicroRTSGridModeVecEnv:
         if self.return_torch:
             if not self.reward_shaping:
                 raw[:, 1:] = 0
-            return obs, raw @ self._rw_t, done.bool(), _LazyInfos(raw)
+            return obs, raw @ self._rw_t, done.bool(), RawRewardInfos(raw)
         o, r, d = self._finish_host(self._to_host("obs", obs), self._to_host("raw", raw), self._to_host("done", done))
         reward = r
         if not self.reward_shaping:
@@ -543,15 +566,29 @@ class MicroRTSBotVecEnv(MicroRTSGridModeVecEnv):
         raise NotImplementedError("MicroRTSBotVecEnv has no agent: the reference's inherited get_action_mask() fails in getMasks (no clients)")
 
 
-class _LazyInfos(Sequence):
-    """``infos`` of the torch mode: behaves like the reference's list of ``{"raw_rewards": (6,)}``
-    dicts but only materialises an entry (one device read) when a wrapper indexes it."""
+class RawRewardInfos(Sequence):
+    """``infos`` of the torch and host_transport modes: the reference's list of ``{"raw_rewards": (6,) float64}``
+    dicts (vec_env.py:1036) over the step's (N, 6) reward block (a device tensor, or a private NumPy copy).  Behaves like that list for the reference's own
+    consumers -- ``len``, iteration, ``infos[i]``, ``infos[:]`` / ``list(infos[:])`` and ``infos[i].copy()``
+    (MicroRTSStatsRecorder.step_wait, experiments/ppo_gridnet.py:138-158; SB3's VecMonitor) -- but only moves the
+    rewards to the host (one copy for all envs) when an entry is first looked at.  ``.raw`` is the device tensor."""
 
-    def __init__(self, raw: torch.Tensor):
+    def __init__(self, raw):
         self.raw = raw
+        self._host = raw if isinstance(raw, np.ndarray) else None
+
+    def _rows(self):
+        if self._host is None:
+            self._host = self.raw.detach().cpu().numpy()
+        return self._host
 
     def __len__(self):
         return self.raw.shape[0]
 
     def __getitem__(self, i):
-        return {"raw_rewards": self.raw[i]}
+        if isinstance(i, slice):
+            return [{"raw_rewards": row} for row in self._rows()[i]]
+        return {"raw_rewards": self._rows()[i]}
+
+    def __iter__(self):
+        return iter([{"raw_rewards": row} for row in self._rows()])

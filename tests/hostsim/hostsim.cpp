@@ -21,6 +21,10 @@ struct hs_env {
     std::vector<int32_t> cycle;  // map rotation (the host loop standing in for mrts_cycle_kernel)
     std::vector<uint8_t> ended;
     int cycle_pos = 0, n_maps = 0;
+    // MRTS_HOSTSIM_SPLIT=1: outputs go through the packed form (observation words + mask entries) and are
+    // expanded afterwards, as the split pipeline of the CUDA library does (mrts_expand.cuh)
+    bool split = false;
+    std::vector<uint32_t> pobs, ment;
 };
 struct NoSync {
     void operator()() const {}
@@ -44,11 +48,28 @@ static void pass(hs_env* e, int mode, const int32_t* actions, void* obs, void* m
     P.done = done;
     const bool rotate = mode == MODE_STEP && !e->cycle.empty();
     P.ended = rotate ? e->ended.data() : nullptr;
-    auto one = [&](const EnvParams& Q, int g) {
-        if (Q.elem == 4 && Q.planes == 29) game_pass<4, 29>(Q, g, e->mem.data(), 0, 1, NoSync());
-        else if (Q.elem == 4) game_pass<4, 31>(Q, g, e->mem.data(), 0, 1, NoSync());
-        else if (Q.planes == 29) game_pass<1, 29>(Q, g, e->mem.data(), 0, 1, NoSync());
-        else game_pass<1, 31>(Q, g, e->mem.data(), 0, 1, NoSync());
+    auto one = [&](const EnvParams& Q0, int g) {
+        EnvParams Q = Q0;
+        if (!e->split || (!Q.obs && !Q.mask)) {
+            game_pass_any(Q, g, e->mem.data(), 0, 1, NoSync());
+            return;
+        }
+        const size_t ms = ment_stride_words(Q.cap);
+        Q.obs = nullptr, Q.mask = nullptr;
+        Q.pobs = Q0.obs ? e->pobs.data() : nullptr;
+        Q.ment = Q0.mask ? e->ment.data() : nullptr;
+        game_pass_any(Q, g, e->mem.data(), 0, 1, NoSync());
+        const bool sp = Q.game_ai[g] == AI_NONE;
+        const int env0 = sp ? 2 * g : Q.num_selfplay + (g - Q.num_selfplay / 2);
+        for (int v = 0; v < (sp ? 2 : 1); v++) {
+            const size_t env = (size_t)(env0 + v);
+            if (Q0.obs) store_obs_rt(Q.elem, Q.planes, e->pobs.data() + env * Q.HW, Q.HW, (uint8_t*)Q0.obs + env * Q.HW * Q.planes * Q.elem, 0, 1);
+            if (Q0.mask) {
+                void* m = (uint8_t*)Q0.mask + env * Q.HW * 78 * Q.elem;
+                if (Q.elem == 4) expand_mask_entries<4>(e->ment.data() + env * ms, Q.HW, m);
+                else expand_mask_entries<1>(e->ment.data() + env * ms, Q.HW, m);
+            }
+        }
     };
     for (int g = 0; g < P.n_games; g++) one(P, g);
     if (rotate) {  // same rule as mrts_cycle_kernel + the reset launch (mrts_kernels.cu)
@@ -81,6 +102,10 @@ int hs_create(const mrts_config* cfg, hs_env** out) {
     e->ended.assign(P.n_games, 0);
     e->games.assign((size_t)P.n_games * P.game_stride + 64, 0);
     e->mem.assign(layout_of(P).total + 64, 0);
+    const char* sp = getenv("MRTS_HOSTSIM_SPLIT");
+    e->split = sp && sp[0] == '1';
+    e->pobs.assign((size_t)e->S.N * P.HW, 0);
+    e->ment.assign((size_t)e->S.N * ment_stride_words(P.cap), 0);
     pass(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr);
     *out = e;
     return 0;
