@@ -140,6 +140,8 @@ struct mrts_env {
     int rows_cap = 0;
     uint32_t sample_counter = 0;
     int last_launches = 0;  // kernels enqueued by the last launch()
+    bool pipeline_hint_direct = false;
+    int bulk_mask = 1;      // direct mode: bulk-store mask writer (MRTS_BULK_MASK=0 switches it off, tuning)
 };
 
 namespace {
@@ -223,6 +225,8 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
         P.mask = mask;
     }
     if (!warp) P.scap = P.cap;  // the block kernel stages the full capacity
+    // direct mode on the warp kernels: the tensors go through the copy engine when their rows line up with 16-byte groups
+    P.bulk_out = !split && warp && want && e->bulk_mask && expand_supported(P.HW, P.planes, P.elem, obs, mask) ? 1 : 0;
     const bool defer = warp && P.scap < P.cap;
 
     // ---- per-step counters: next step's class counts, deferred-game counts, expansion work counters
@@ -321,6 +325,7 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
             X.planes = P.planes;
             X.elem = P.elem;
             X.cap = P.cap;
+            X.empty_word = obs_empty_word(P.partial);
             X.counter = exp_ctr + c0;
             cudaStream_t se = st;
             if (fork) {
@@ -440,6 +445,15 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         mrts_destroy(e);
         return fail(MRTS_EINVAL, "map too large for shared-memory staging");
     }
+    // ---- pipeline
+    e->pipeline = cfg->pipeline == MRTS_PIPELINE_DIRECT || cfg->pipeline == MRTS_PIPELINE_SPLIT ? cfg->pipeline : 0;
+    {
+        const int forced = env_int("MRTS_PIPELINE", 0);
+        if (forced == MRTS_PIPELINE_DIRECT || forced == MRTS_PIPELINE_SPLIT) e->pipeline = forced;
+    }
+    if (e->pipeline == 0) e->pipeline = S.N >= 1024 ? MRTS_PIPELINE_SPLIT : MRTS_PIPELINE_DIRECT;
+    e->bulk_mask = env_int("MRTS_BULK_MASK", 1) != 0;
+    e->pipeline_hint_direct = e->pipeline == MRTS_PIPELINE_DIRECT && e->bulk_mask;
     // Register budget: light games (self-play, PassiveAI) fit 64 registers without spills -> 32 warps per SM;
     // the scripted-bot kernels take 96.
     e->regs[0] = env_int("MRTS_REGS_LIGHT", 64);
@@ -452,7 +466,7 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         int best = 1, best_w = 0;
         for (int g = 1; g <= GPB_MAX; g *= 2) {
             if (g * e->smem[k] > maxsm) break;
-            int blocks = smem_sm / (g * e->smem[k] + 1024);  // 1 KB per-block reservation
+            int blocks = smem_sm / (g * e->smem[k] + 1024 + (e->pipeline_hint_direct ? 8960 : 0));  // 1 KB per-block reservation (+ the bulk writer's zero tile)
             if (blocks > max_blocks) blocks = max_blocks;
             int w = blocks * g;
             if (w > by_regs) w = by_regs;
@@ -464,18 +478,12 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         if (e->gpb[k] > GPB_MAX) e->gpb[k] = GPB_MAX;
         while (e->gpb[k] > 1 && e->gpb[k] * e->smem[k] > maxsm) e->gpb[k] /= 2;
     }
-    CREATE_CK(light_set_smem(e->gpb[0] * e->smem[0], e->smem_block));
-    CREATE_CK(heavy_set_smem(e->gpb[1] * e->smem[1], e->smem_block));
+    CREATE_CK(light_set_smem(e->gpb[0] * e->smem[0] + 8960, e->smem_block));
+    CREATE_CK(heavy_set_smem(e->gpb[1] * e->smem[1] + 8960, e->smem_block));
     CREATE_CK(any_set_smem(e->smem_full));
     CREATE_CK(expand_init());
 
-    // ---- pipeline: chunks of the slab, light / heavy game lists per chunk
-    e->pipeline = cfg->pipeline == MRTS_PIPELINE_DIRECT || cfg->pipeline == MRTS_PIPELINE_SPLIT ? cfg->pipeline : 0;
-    {
-        const int forced = env_int("MRTS_PIPELINE", 0);
-        if (forced == MRTS_PIPELINE_DIRECT || forced == MRTS_PIPELINE_SPLIT) e->pipeline = forced;
-    }
-    if (e->pipeline == 0) e->pipeline = S.N >= 1024 ? MRTS_PIPELINE_SPLIT : MRTS_PIPELINE_DIRECT;
+    // ---- chunks of the slab, light / heavy game lists per chunk
     int K = cfg->chunks > 0 ? cfg->chunks : env_int("MRTS_CHUNKS", 0);
     if (K <= 0) {
         // a chunk should fill the GPU a few times over: ~20 games per SM are resident at once
@@ -605,7 +613,7 @@ int mrts_expand(mrts_env* e, const uint32_t* obs_words, const uint32_t* mask_ent
     if (!e) return fail(MRTS_EINVAL, "null env");
     if ((obs && !obs_words) || (mask && !mask_entries)) return fail(MRTS_EINVAL, "packed input missing");
     if (!obs && !mask) return MRTS_OK;
-    if (!expand_supported(e->P.HW, e->P.planes, e->P.elem, obs, mask))
+    if (!expand_supported(e->P.HW, e->P.planes, e->P.elem, obs, mask) || ((((uintptr_t)obs_words) | ((uintptr_t)mask_entries)) & 15))
         return fail(MRTS_EINVAL, "mrts_expand needs H*W*element_bytes to be a multiple of 16 and 16-byte aligned tensors");
     CK(cudaSetDevice(e->device));
     const cudaStream_t st = (cudaStream_t)stream;
@@ -624,6 +632,7 @@ int mrts_expand(mrts_env* e, const uint32_t* obs_words, const uint32_t* mask_ent
     X.planes = e->P.planes;
     X.elem = e->P.elem;
     X.cap = e->P.cap;
+    X.empty_word = obs_empty_word(e->P.partial);
     X.counter = ctr;
     int blocks = (e->N + 7) / 8;
     if (blocks > e->exp_blocks) blocks = e->exp_blocks;

@@ -8,6 +8,9 @@
 // The host build (tests/hostsim) calls them with (0, 1).
 #pragma once
 #include "mrts_core.h"
+#if defined(__CUDACC__)
+#include "mrts_bulk.cuh"
+#endif
 
 namespace mrts {
 
@@ -26,6 +29,8 @@ MRTS_HD uint32_t unit_obs_word(const Unit& un, int viewer, int act_type) {
     return w;
 }
 enum : uint32_t { OBS_EMPTY = (1u << OB_HP) | (1u << OB_RES) | (1u << OB_OWNER) | (1u << OB_TYPE) | (1u << OB_ACT) };
+// the word of most cells of a map: nothing on it, no wall, (partial_obs) not seen by the opponent
+MRTS_HD uint32_t obs_empty_word(int partial) { return OBS_EMPTY | (1u << OB_TERRAIN) | (partial ? (1u << OB_VIS) : 0u); }
 
 // Phase A (cells): words[c] for every cell.  vp < 0: the true state; vp = p: player p's stale
 // partially observable view (membership + assignment copy recorded in Unit::vis / vtype).
@@ -189,6 +194,50 @@ MRTS_HD void patch_mask_rt(int elem, const Sim& s, int player, const uint32_t* u
     if (elem == 4) patch_mask<4>(s, player, umask, out, tid, nth);
     else patch_mask<1>(s, player, umask, out, tid, nth);
 }
+
+#if defined(__CUDACC__)
+constexpr int BULK_SLOTS = 2;
+constexpr int BULK_ZERO_BYTES = 8 * bulk::GROUP_BYTES;                           // 4,992 bytes of zeros per block
+constexpr int BULK_TILES_BYTES = BULK_ZERO_BYTES + bulk::EMPTY_BYTES_MAX;        // per block, in front of the games' regions
+constexpr int BULK_SLOT_BYTES = BULK_SLOTS * (bulk::OBS_SLOT_BYTES + bulk::SLOT_BYTES);  // per game
+#endif
+#if defined(__CUDA_ARCH__)
+// Phases C / D, bulk form (warp kernels in direct mode, device only): one view's observation and mask through the
+// copy engine (mrts_bulk.cuh) -- runs of empty cells / zero rows straight from the block's static tiles, only the
+// cells that hold something staged.  The warp walks the grid 32 cells at a time so that mask rows arrive in
+// ascending cell order.
+__device__ __forceinline__ void bulk_mask_view(const Sim& s, int player, const uint32_t* umask, void* out, bulk::MaskWriter<BULK_SLOTS>& mw, int lane) {
+    mw.begin(out);
+#pragma unroll 1
+    for (int base = 0; base < s.HW; base += 32) {
+        const int c = base + lane;
+        bool take = false;
+        int i = 0;
+        if (c < s.HW) {
+            const uint16_t g = s.grid[c];
+            if (g < G_WALL) {
+                const Unit& un = s.u[g];
+                i = g;
+                take = un.player == player && un.a_type < 0 && !(un.flags & UF_DEAD);
+            }
+        }
+        unsigned m = __ballot_sync(0xFFFFFFFFu, take);
+#pragma unroll 1
+        while (m) {
+            const int src = __ffs((int)m) - 1;
+            m &= m - 1;
+            const int k = __shfl_sync(0xFFFFFFFFu, i, src);
+            mw.add((uint32_t)(base + src), umask[3 * k], umask[3 * k + 1], umask[3 * k + 2]);
+        }
+    }
+    mw.finish(s.HW / mw.cells_per_group());
+}
+__device__ __forceinline__ void bulk_obs_view(const uint32_t* words, int HW, void* out, bulk::ObsWriter<BULK_SLOTS>& ow) {
+    ow.begin(out);
+    ow.segment(words, 0, HW / ow.cells_per_group());
+    ow.finish(HW / ow.cells_per_group());
+}
+#endif
 
 // Phase E (after unit_masks + barrier): the packed form of one view's mask -- one 16-byte entry
 // (cell, 78 bits) per unit of `player` that may act, in ASCENDING CELL ORDER (the expansion kernel builds

@@ -50,6 +50,7 @@ struct ExpandParams {
     void* mask;            // (N, HW, 78) or null
     int32_t env_lo, env_hi;
     int32_t HW, planes, elem, cap;
+    uint32_t empty_word;   // observation word of an empty cell (mrts_encode.h: obs_empty_word)
     int32_t* counter;      // work counter of this launch (zeroed by the caller): views are handed out one at a time
 };
 // true when the shape can take the bulk-store path (every view's obs and mask blocks are multiples of 16 bytes)

@@ -34,8 +34,11 @@ __global__ void __launch_bounds__(32 * GPB_MAX, MINB) mrts_rules_warp_kernel(con
     extern __shared__ uint4 smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
+    // direct mode: the block's static tiles of the bulk writers (zero rows, empty cells) sit in front of the games' regions
+    const int zb = P.bulk_out ? BULK_TILES_BYTES : 0;
+    if (zb) bulk::tiles_init((uint8_t*)smem_raw, BULK_ZERO_BYTES, P.elem, P.planes, obs_empty_word(P.partial), (int)threadIdx.x, (int)blockDim.x);
     if (slot >= P.nslots) return;
-    game_pass<HEAVY>(P, slot_game(P, slot), (uint8_t*)smem_raw + (size_t)warp * smem_per_game, lane, 32, WarpSync());
+    game_pass<HEAVY>(P, slot_game(P, slot), (uint8_t*)smem_raw + zb + (size_t)warp * smem_per_game, lane, 32, WarpSync(), zb ? (uint8_t*)smem_raw : nullptr);
 }
 
 // one block per game: every thread takes part in the staging and the output phases (direct mode on large maps)
@@ -50,9 +53,10 @@ __global__ void __launch_bounds__(256) mrts_rules_block_kernel(const __grid_cons
 template <int HEAVY>
 static cudaError_t launch_warp_t(int regs, const EnvParams& P, int gpb, int smem_per_game, cudaStream_t st) {
     const dim3 grid((P.nslots + gpb - 1) / gpb);
-    if (regs <= 64) mrts_rules_warp_kernel<HEAVY, 8><<<grid, 32 * gpb, gpb * smem_per_game, st>>>(P, smem_per_game);
-    else if (regs <= 96) mrts_rules_warp_kernel<HEAVY, 5><<<grid, 32 * gpb, gpb * smem_per_game, st>>>(P, smem_per_game);
-    else mrts_rules_warp_kernel<HEAVY, 4><<<grid, 32 * gpb, gpb * smem_per_game, st>>>(P, smem_per_game);
+    const int smem = gpb * smem_per_game + (P.bulk_out ? BULK_TILES_BYTES : 0);
+    if (regs <= 64) mrts_rules_warp_kernel<HEAVY, 8><<<grid, 32 * gpb, smem, st>>>(P, smem_per_game);
+    else if (regs <= 96) mrts_rules_warp_kernel<HEAVY, 5><<<grid, 32 * gpb, smem, st>>>(P, smem_per_game);
+    else mrts_rules_warp_kernel<HEAVY, 4><<<grid, 32 * gpb, smem, st>>>(P, smem_per_game);
     return cudaGetLastError();
 }
 template <int HEAVY>

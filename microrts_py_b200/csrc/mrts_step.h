@@ -51,6 +51,7 @@ struct EnvParams {
     int32_t mode;
     int32_t game0, game1;           // this launch covers the slots / games [game0, game1)
     int32_t elem;                   // bytes per obs/mask element: 4 (int32, reference dtype) or 1 (uint8)
+    int32_t bulk_out;               // direct mode, warp kernels: obs / mask go through the copy engine (static tiles + staged groups, mrts_bulk.cuh)
     const int32_t* actions;         // (N, HW, 7) int32
     void* obs;                      // (N, H, W, planes) or null
     void* mask;                     // (N, HW, 78) or null
@@ -73,7 +74,7 @@ MRTS_HD int blob_bytes(int cap, int has_bot) { return 32 + cap * 32 + (has_bot ?
 MRTS_HD size_t ment_stride_words(int cap) { return (size_t)(1 + cap) * 4; }
 
 struct Layout {
-    int blob, grid, words, umask, pa, pa2, bits, astar, misc, total, nbits_words;
+    int blob, grid, words, umask, slots, pa, pa2, bits, astar, misc, total, nbits_words;
 };
 // Shared-memory plan of one game.  The rules scratch (PlayerActions, reservation bitmaps, A*
 // arrays) is dead once the rules are done, the output scratch (observation words, per-unit
@@ -105,6 +106,8 @@ MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int any_bot) {
     o += align16(HW * 4);  // one view at a time
     L.umask = o;
     o += align16(cap * 12);
+    L.slots = o;  // staging of the bulk writers (direct mode): 2 observation groups of 512 bytes, 2 mask groups of 640
+    o += 2 * (512 + 640);  // = BULK_SLOT_BYTES (mrts_encode.h)
     L.total = o > end_rules ? o : end_rules;
     return L;
 }
@@ -189,8 +192,9 @@ MRTS_HD int order_append(int32_t* cnt) {
 MRTS_HD bool game_is_heavy(const EnvParams& P, int g) { return ai_plans(P.game_ai[g]) || (P.game_ai1 && ai_plans(P.game_ai1[g])); }
 
 // SYNC: functor executing a barrier over the game's thread group.  HEAVY: see Sim::step_game.
+// `blk`: shared memory of the whole block (the bulk writer's tile of zeros lives at its start), null when unused.
 template <int HEAVY, class SYNC>
-MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync) {
+MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth, SYNC sync, uint8_t* blk = nullptr) {
     const long long t_start = P.timing ? cycles_now() : 0;
 #if defined(__CUDA_ARCH__)
     if (P.timing && tid == 0) {
@@ -327,6 +331,20 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     }
 
     // ---------------- observations, one view at a time (before compaction: stale views keep the dead)
+#if defined(__CUDA_ARCH__)
+    // direct mode on the warp kernels: the tensors go through the copy engine (mrts_bulk.cuh); the staged groups drain
+    // while the warp goes on (unit masks, packed outputs, blob write-back)
+    const bool bulk_out = P.bulk_out && blk != nullptr && nth == 32;
+    bulk::ObsWriter<BULK_SLOTS> ow;
+    bulk::MaskWriter<BULK_SLOTS> mw;
+    if (bulk_out) {
+        ow.init(mem + L.slots, blk + BULK_ZERO_BYTES, obs_empty_word(P.partial), P.elem, P.planes, tid);
+        mw.init(mem + L.slots + BULK_SLOTS * bulk::OBS_SLOT_BYTES, blk, BULK_ZERO_BYTES, P.elem, tid);
+    }
+#else
+    const bool bulk_out = false;
+    (void)blk;
+#endif
     const size_t obs_env = (size_t)P.HW * P.planes * P.elem;
     const size_t mask_env = (size_t)P.HW * 78 * P.elem;
     if (P.obs || P.pobs) {
@@ -337,6 +355,10 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
                 obs_words_dead(s, v, v, words, tid, nth);
             }
             sync();
+#if defined(__CUDA_ARCH__)
+            if (P.obs && bulk_out) bulk_obs_view(words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, ow);
+            else
+#endif
             if (P.obs) store_obs_rt(P.elem, P.planes, words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, tid, nth);
             if (P.pobs) copy16<uint32_t>(P.pobs + (size_t)(env0 + v) * P.HW, words, P.HW * 4, tid, nth);
             sync();
@@ -349,7 +371,8 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (P.mask || P.pmask || P.ment || P.next_actions) unit_masks(s, umask, tid, nth);
 
     // ---------------- mask: zero fill, then the 78 entries of every source unit
-    if (P.mask)
+    const bool bulk_mask = P.mask && bulk_out;
+    if (P.mask && !bulk_mask)
         for (int v = 0; v < nviews; v++) zero_mask_rt(P.elem, P.HW, (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env, tid, nth);
     if (P.pmask) {
         uint32_t* pm = P.pmask + (size_t)env0 * P.HW * 3;
@@ -369,12 +392,16 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (P.next_actions)
         for (int v = 0; v < nviews; v++)
             sample_actions(s, v, umask, P.next_actions + (size_t)(env0 + v) * P.HW * 7, P.seed, P.counter, (uint32_t)(env0 + v), tid, nth);
-    if (P.mask) {
+    if (P.mask && !bulk_mask) {
         for (int v = 0; v < nviews; v++) {
             void* m = (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env;
             patch_mask_rt(P.elem, s, v, umask, m, tid, nth);
         }
     }
+#if defined(__CUDA_ARCH__)
+    if (bulk_mask)
+        for (int v = 0; v < nviews; v++) bulk_mask_view(s, v, umask, (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env, mw, tid);
+#endif
     if (P.ment)
         for (int v = 0; v < nviews; v++) emit_mask_entries(s, v, umask, P.ment + (size_t)(env0 + v) * ment_stride_words(P.cap), tid, nth);
     if (P.pmask) {
@@ -395,6 +422,12 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         copy16<Q16>(gblob, mem + L.blob, 32 + n * 32, tid, nth);
         if (HEAVY && P.has_bot && naa > 0) copy16<Q16>(gblob + 32 + P.cap * 32, s.aa, align16(naa * 12), tid, nth);
     }
+#if defined(__CUDA_ARCH__)
+    if (bulk_out) {  // the staging slots and the block's static tiles must outlive the copies that read them
+        if (tid < 2) bulk::wait_read<0>();
+        __syncwarp();
+    }
+#endif
     if (P.timing && tid == 0) P.timing[12 * g + 1] = cycles_now() - t_start;
 }
 

@@ -25,6 +25,9 @@ Extra keyword-only arguments (all default to the reference's behaviour):
                 the reference's JNIBotClient; the action rows of those envs are ignored
   fuse_mask     compute the action mask of the resulting state inside ``step`` (one launch,
                 the state is staged once); ``get_action_mask`` then only hands it out
+  return_packed device tensors in the PACKED form (implies ``return_torch``): ``reset`` / ``step`` return the
+                observation words (N, H*W) int32 and ``get_action_mask`` the mask entries (N, 1 + cap, 4) int32 of
+                ``microrts_py_b200.packed``; ``expand(words, entries)`` widens them on the device (mrts_expand)
   pipeline      "auto" (default), "direct" (the rules pass writes the tensors itself) or "split" (rules kernels
                 write a packed form, an expansion kernel streams it into the tensors with bulk async stores while
                 the next chunk's rules run); ``chunks`` = slab chunks of the split pipeline (0 = choose)
@@ -152,6 +155,7 @@ class MicroRTSGridModeVecEnv:
         ai1s=None,
         pipeline="auto",
         chunks=0,
+        return_packed=False,
     ):
         self.num_selfplay_envs = num_selfplay_envs
         self.num_bot_envs = num_bot_envs
@@ -227,7 +231,8 @@ class MicroRTSGridModeVecEnv:
         if self._np_dtype not in (np.dtype(np.int32), np.dtype(np.uint8)):
             raise ValueError("dtype must be np.int32 (reference) or np.uint8")
         self._t_dtype = torch.int32 if self._np_dtype == np.int32 else torch.uint8
-        self.return_torch = bool(return_torch)
+        self.return_packed = bool(return_packed)
+        self.return_torch = bool(return_torch) or self.return_packed
         self.zero_copy = bool(zero_copy)
         self.fuse_mask = bool(fuse_mask)
         self.host_transport = bool(host_transport) and not self.return_torch
@@ -270,6 +275,10 @@ class MicroRTSGridModeVecEnv:
         self._shape_obs = (N, self.height, self.width, P)
         self._shape_mask = (N, HW, 78)
         self._shape_act = (N, HW, 7)
+        ow, mw = C.c_int64(), C.c_int64()
+        _capi.check(self._lib.mrts_packed_sizes(self._h, C.byref(ow), C.byref(mw)))
+        self._shape_words = (N, HW)
+        self._shape_entries = (N, mw.value // (4 * N), 4)
         self._d_actions = torch.zeros(self._shape_act, dtype=torch.int32, device=self.device)
         self._d_mask: Optional[torch.Tensor] = None  # mask of the current state when valid
         self._mask_valid = False
@@ -336,6 +345,12 @@ class MicroRTSGridModeVecEnv:
             _capi.check(self._lib.mrts_reset_host_slot(self._h, _np_ptr(o), _np_ptr(m), self._hcur))
             self._h_mask_np = m
             return o
+        if self.return_packed:
+            words, entries = self._new(self._shape_words, torch.int32), self._new(self._shape_entries, torch.int32)
+            with torch.cuda.device(self.device):
+                _capi.check(self._lib.mrts_reset_packed(self._h, _ptr(words), _ptr(entries), self._stream()))
+            self._d_mask, self._mask_valid = entries, True
+            return words
         obs = self._new(self._shape_obs, self._t_dtype)
         mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
         with torch.cuda.device(self.device):
@@ -355,6 +370,11 @@ class MicroRTSGridModeVecEnv:
                 raise RuntimeError("get_action_mask() before reset()")
             self.source_unit_mask = self._h_mask_np[:, :, 0]
             return self._h_mask_np
+        if self.return_packed:
+            if not self._mask_valid:
+                raise RuntimeError("return_packed: get_action_mask() hands out the entries of the last reset() / step()")
+            self.source_unit_mask = None
+            return self._d_mask
         if not self._mask_valid:
             mask = self._new(self._shape_mask, self._t_dtype)
             with torch.cuda.device(self.device):
@@ -426,10 +446,20 @@ class MicroRTSGridModeVecEnv:
             # `reward` is one of two alternating buffers: the infos get their own copy, so that rows a wrapper
             # accumulates over an episode do not change two steps later
             return o, reward @ self.reward_weight, d.astype(np.bool_), RawRewardInfos(reward.copy())
-        obs = self._new(self._shape_obs, self._t_dtype)
-        mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
         raw = self._new((N, 6), torch.float64)
         done = self._new((N,), torch.uint8)
+        if self.return_packed:
+            io = _capi.PackedIOC()
+            words, entries = self._new(self._shape_words, torch.int32), self._new(self._shape_entries, torch.int32)
+            io.actions, io.obs_words, io.mask_entries, io.reward, io.done = a.data_ptr(), words.data_ptr(), entries.data_ptr(), raw.data_ptr(), done.data_ptr()
+            with torch.cuda.device(self.device):
+                _capi.check(self._lib.mrts_step_packed(self._h, C.byref(io), self._stream()))
+            self._d_mask, self._mask_valid = entries, True
+            if not self.reward_shaping:
+                raw[:, 1:] = 0
+            return words, raw @ self._rw_t, done.bool(), RawRewardInfos(raw)
+        obs = self._new(self._shape_obs, self._t_dtype)
+        mask = self._new(self._shape_mask, self._t_dtype) if self.fuse_mask else None
         with torch.cuda.device(self.device):
             _capi.check(self._lib.mrts_step(self._h, _ptr(a), _ptr(obs), _ptr(mask), _ptr(raw), _ptr(done), self._stream()))
         self._d_mask, self._mask_valid = mask, mask is not None
@@ -487,6 +517,16 @@ class MicroRTSGridModeVecEnv:
         with torch.cuda.device(self.device):
             _capi.check(self._lib.mrts_step_ex(self._h, C.byref(io), self._stream()))
         self._d_mask, self._mask_valid = (mask, True) if mask is not None else (None, False)
+
+    def expand(self, words=None, entries=None):
+        """Packed form -> the reference's tensors on the device (mrts_expand: bulk async stores): returns (obs, mask),
+        ``None`` for an input that was not given."""
+        self._check_open()
+        obs = self._new(self._shape_obs, self._t_dtype) if words is not None else None
+        mask = self._new(self._shape_mask, self._t_dtype) if entries is not None else None
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.mrts_expand(self._h, _ptr(words), _ptr(entries), _ptr(obs), _ptr(mask), self._stream()))
+        return obs, mask
 
     def getattr_depth_check(self, name, already_found):
         if hasattr(self, name) and already_found:
