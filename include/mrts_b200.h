@@ -202,7 +202,7 @@ int mrts_debug_issue(mrts_env* env, int game, const int32_t* rows7, int n, void*
 /* GameState.cycle on one game; *gameover (host, may be NULL) receives the result. */
 int mrts_debug_cycle(mrts_env* env, int game, int* gameover, void* stream);
 
-/* Profiling aid: when device_buf (12 * num_games int64, device) is non-null every launch records per game
+/* Profiling aid: when device_buf (16 * num_games int64, device) is non-null every launch records per game
  * {cycles of the rules phase, cycles of the whole pass, 6 sub-phase cycle counts, #path searches, #expansions, start time in ns (globaltimer), SM id}; NULL switches it off again. */
 int mrts_debug_timing(mrts_env* env, long long* device_buf);
 

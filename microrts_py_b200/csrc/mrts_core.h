@@ -92,7 +92,8 @@ struct St {
     int explore;     // the bot acting now is a PO* variant (bot_action)
     int unobs_ready; // bitsC holds this bot call's not-observable cell bitmap (bot_melee)
     int timing_on;   // profiling aid (mrts_debug_timing): fill tp[]
-    int tp[8];       // cycles: decode, bot census/puts, bot translate, issue agent, issue bot, cycle; then #searches, #expansions
+    int tp[12];      // cycles: decode, bot census/puts, bot translate, issue agent, issue bot, cycle; then #searches, #expansions;
+                     // cycles inside path searches, cycles inside their reachability guard, #guards run, cycles of the staging phase
     int rew[2][6];   // integer reward terms per player view (exact small integers)
 };
 
@@ -1159,7 +1160,11 @@ struct Sim {
             // a search that keeps growing is checked once against a flood fill: unreachable -> null right away
             if (++expanded == ASTAR_GUARD_AFTER) {
                 MRTS_STAT(guard++);
-                if (!flood_reaches(sx, sy, tx, ty, range)) {
+                const int t_gd = tick();
+                const bool reach = flood_reaches(sx, sy, tx, ty, range);
+                st->tp[9] += tick() - t_gd;
+                st->tp[10]++;
+                if (!reach) {
                     MRTS_STAT(guard_fail++);
                     break;
                 }
@@ -1438,7 +1443,9 @@ struct Sim {
         }
         if (search) {
             tpos = tx + ty * W;
+            const int t_as = tick();
             const int mv = astar_first_move(i, tpos, range, vp);
+            st->tp[8] += tick() - t_as;
             if (mv >= 0) {
                 out.type = T_MOVE;
                 out.param = (int16_t)mv;

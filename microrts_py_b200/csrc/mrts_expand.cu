@@ -25,12 +25,10 @@ namespace {
 
 constexpr int EXP_WARPS = 8, EXP_THREADS = 32 * EXP_WARPS;
 using bulk::GROUP_BYTES;
-using bulk::SLOT_BYTES;
 constexpr int ZERO_BYTES = 16 * GROUP_BYTES;  // 9,984 bytes of zeros per block
-constexpr int NSLOTS = 4;          // staged groups in flight per warp, observation and mask each
 constexpr int SEG_CELLS = 1024;    // words of a view staged at a time
 constexpr int TILES_BYTES = ZERO_BYTES + bulk::EMPTY_BYTES_MAX;
-constexpr int WARP_BYTES = SEG_CELLS * 4 + NSLOTS * bulk::OBS_SLOT_BYTES + NSLOTS * SLOT_BYTES;
+constexpr int WARP_BYTES = SEG_CELLS * 4 + bulk::STAGE_BYTES;
 constexpr int SMEM_BYTES = TILES_BYTES + EXP_WARPS * WARP_BYTES;
 static_assert(WARP_BYTES % 16 == 0 && TILES_BYTES % 16 == 0, "128-bit alignment of the staging buffers");
 constexpr unsigned FULL = 0xFFFFFFFFu;
@@ -46,10 +44,12 @@ __global__ void __launch_bounds__(EXP_THREADS) mrts_expand_kernel(const __grid_c
     const int HW = X.HW;
     const size_t obs_env = (size_t)HW * PLANES * ELEM, mask_env = (size_t)HW * 78 * ELEM;
     const size_t ment_stride = ment_stride_words(X.cap);
-    bulk::ObsWriter<NSLOTS> ow;
-    ow.init(wm + SEG_CELLS * 4, sm + ZERO_BYTES, X.empty_word, ELEM, PLANES, lane);
-    bulk::MaskWriter<NSLOTS> mw;
-    mw.init(wm + SEG_CELLS * 4 + NSLOTS * bulk::OBS_SLOT_BYTES, sm, ZERO_BYTES, ELEM, lane);
+    bulk::Stage stage;
+    stage.init(wm + SEG_CELLS * 4, lane);
+    bulk::ObsWriter ow;
+    ow.init(&stage, sm + ZERO_BYTES, X.empty_word, ELEM, PLANES);
+    bulk::MaskWriter mw;
+    mw.init(&stage, sm, ZERO_BYTES, ELEM);
 
     for (;;) {
         int v = 0;
@@ -89,8 +89,8 @@ __global__ void __launch_bounds__(EXP_THREADS) mrts_expand_kernel(const __grid_c
             mw.finish(HW / (8 / ELEM));
         }
     }
-    // shared memory must outlive the copies that read it, and the writes must have landed before the grid ends
-    if (lane < 2) bulk::wait_all();
+    // shared memory must outlive the copies that read it
+    stage.drain();
 }
 
 }  // namespace

@@ -40,7 +40,7 @@ __global__ void mrts_debug_kernel(const __grid_constant__ EnvParams P, const Deb
         St z;
         z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.timing_on = z.rows_ready = z.nidle = z.explore = z.unobs_ready = 0;
         z.winner = -1;
-        for (int k = 0; k < 8; k++) z.tp[k] = 0;
+        for (int k = 0; k < 12; k++) z.tp[k] = 0;
         for (int p = 0; p < 2; p++)
             for (int k = 0; k < 6; k++) z.rew[p][k] = 0;
         *s.st = z;

@@ -66,7 +66,7 @@ struct EnvParams {
     uint64_t seed;                  // sampler key
     uint32_t counter;               // launch counter (sampler stream position)
     uint8_t* ended;                 // cycle_maps: per game, 1 when the step ended its episode (read by the map-rotation pass)
-    long long* timing;              // profiling aid, normally null: per game 12 values {rules cycles, total cycles, St::tp[0..7], start ns, SM id}
+    long long* timing;              // profiling aid, normally null: per game 16 values {rules cycles, total cycles, St::tp[0..7], start ns, SM id, St::tp[8..11]}
 };
 
 MRTS_HD int align16(int v) { return (v + 15) & ~15; }
@@ -106,8 +106,8 @@ MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int any_bot) {
     o += align16(HW * 4);  // one view at a time
     L.umask = o;
     o += align16(cap * 12);
-    L.slots = o;  // staging of the bulk writers (direct mode): 2 observation groups of 512 bytes, 2 mask groups of 640
-    o += 2 * (512 + 640);  // = BULK_SLOT_BYTES (mrts_encode.h)
+    L.slots = o;  // staging of the bulk writers (direct mode): bulk::STAGE_BYTES (mrts_bulk.cuh)
+    o += 2 * 2496;
     L.total = o > end_rules ? o : end_rules;
     return L;
 }
@@ -152,6 +152,28 @@ MRTS_HD void copy16(void* dst, const void* src, int bytes, int tid, int nth) {  
 struct alignas(16) Q16 {
     uint32_t a, b, c, d;
 };
+// the game blob <-> shared memory: the blob is re-read every step, its lines are kept in the L2 (evict-last) while the
+// write-once output stream passes through (evict-first, mrts_bulk.cuh)
+MRTS_HD void blob_load(void* smem_dst, const void* gsrc, int bytes, int tid, int nth) {
+#if defined(__CUDA_ARCH__)
+    const uint64_t pol = bulk::policy_evict_last();
+    const int n = bytes / 16;
+#pragma unroll 1
+    for (int i = tid; i < n; i += nth) ((uint4*)smem_dst)[i] = bulk::ldg_hint((const uint4*)gsrc + i, pol);
+#else
+    copy16<Q16>(smem_dst, gsrc, bytes, tid, nth);
+#endif
+}
+MRTS_HD void blob_store(void* gdst, const void* smem_src, int bytes, int tid, int nth) {
+#if defined(__CUDA_ARCH__)
+    const uint64_t pol = bulk::policy_evict_last();
+    const int n = bytes / 16;
+#pragma unroll 1
+    for (int i = tid; i < n; i += nth) bulk::stg_hint((uint4*)gdst + i, ((const uint4*)smem_src)[i], pol);
+#else
+    copy16<Q16>(gdst, smem_src, bytes, tid, nth);
+#endif
+}
 
 MRTS_HD long long cycles_now() {
 #if defined(__CUDA_ARCH__)
@@ -202,8 +224,8 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         unsigned sm;
         asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns));
         asm volatile("mov.u32 %0, %smid;" : "=r"(sm));
-        P.timing[12 * g + 10] = (long long)ns;
-        P.timing[12 * g + 11] = (long long)sm;
+        P.timing[16 * g + 10] = (long long)ns;
+        P.timing[16 * g + 11] = (long long)sm;
     }
 #endif
     const Layout L = layout_of(P);
@@ -257,8 +279,8 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
             if (tid == 0) defer_game(P, g);
             return;
         }
-        copy16<Q16>(mem + L.blob, gblob, 32 + n * 32, tid, nth);
-        if (HEAVY && P.has_bot && naa > 0) copy16<Q16>(s.aa, gblob + 32 + P.cap * 32, align16(naa * 12), tid, nth);
+        blob_load(mem + L.blob, gblob, 32 + n * 32, tid, nth);
+        if (HEAVY && P.has_bot && naa > 0) blob_load(s.aa, gblob + 32 + P.cap * 32, align16(naa * 12), tid, nth);
         copy16<uint32_t>(s.grid, grid0, align16(P.HW * 2), tid, nth);
     }
     if (P.mode == MODE_STEP && plans) s.astar_init(tid, nth);
@@ -267,7 +289,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         z.npa = z.npa2 = z.astar_gen = z.gameover = z.reset = z.nprod = z.rows_ready = z.nidle = z.explore = z.unobs_ready = 0;
         z.winner = -1;
         z.timing_on = P.timing != nullptr;
-        for (int k = 0; k < 8; k++) z.tp[k] = 0;
+        for (int k = 0; k < 12; k++) z.tp[k] = 0;
         for (int p = 0; p < 2; p++)
             for (int k = 0; k < 6; k++) z.rew[p][k] = 0;
         *s.st = z;
@@ -301,8 +323,10 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
         Sim::wsync();
         s.st->reset = r;
         if (P.timing && tid == 0) {
-            P.timing[12 * g] = cycles_now() - t_rules;
-            for (int k = 0; k < 8; k++) P.timing[12 * g + 2 + k] = s.st->tp[k];
+            P.timing[16 * g] = cycles_now() - t_rules;
+            s.st->tp[11] = (int)(t_rules - t_start);
+            for (int k = 0; k < 8; k++) P.timing[16 * g + 2 + k] = s.st->tp[k];
+            for (int k = 8; k < 12; k++) P.timing[16 * g + 4 + k] = s.st->tp[k];
         }
     }
     sync();
@@ -335,11 +359,14 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     // direct mode on the warp kernels: the tensors go through the copy engine (mrts_bulk.cuh); the staged groups drain
     // while the warp goes on (unit masks, packed outputs, blob write-back)
     const bool bulk_out = P.bulk_out && blk != nullptr && nth == 32;
-    bulk::ObsWriter<BULK_SLOTS> ow;
-    bulk::MaskWriter<BULK_SLOTS> mw;
+    static_assert(bulk::STAGE_BYTES == 2 * 2496, "Layout::slots");
+    bulk::Stage stage;
+    bulk::ObsWriter ow;
+    bulk::MaskWriter mw;
     if (bulk_out) {
-        ow.init(mem + L.slots, blk + BULK_ZERO_BYTES, obs_empty_word(P.partial), P.elem, P.planes, tid);
-        mw.init(mem + L.slots + BULK_SLOTS * bulk::OBS_SLOT_BYTES, blk, BULK_ZERO_BYTES, P.elem, tid);
+        stage.init(mem + L.slots, tid);
+        ow.init(&stage, blk + BULK_ZERO_BYTES, obs_empty_word(P.partial), P.elem, P.planes);
+        mw.init(&stage, blk, BULK_ZERO_BYTES, P.elem);
     }
 #else
     const bool bulk_out = false;
@@ -419,16 +446,13 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     // ---------------- put the blob back
     if (P.mode != MODE_OBSERVE || P.partial) {
         const int n = s.hdr->nunits, naa = s.hdr->n_aa;
-        copy16<Q16>(gblob, mem + L.blob, 32 + n * 32, tid, nth);
-        if (HEAVY && P.has_bot && naa > 0) copy16<Q16>(gblob + 32 + P.cap * 32, s.aa, align16(naa * 12), tid, nth);
+        blob_store(gblob, mem + L.blob, 32 + n * 32, tid, nth);
+        if (HEAVY && P.has_bot && naa > 0) blob_store(gblob + 32 + P.cap * 32, s.aa, align16(naa * 12), tid, nth);
     }
 #if defined(__CUDA_ARCH__)
-    if (bulk_out) {  // the staging slots and the block's static tiles must outlive the copies that read them
-        if (tid < 2) bulk::wait_read<0>();
-        __syncwarp();
-    }
+    if (bulk_out) stage.drain();  // the staging buffers and the block's static tiles must outlive the copies that read them
 #endif
-    if (P.timing && tid == 0) P.timing[12 * g + 1] = cycles_now() - t_start;
+    if (P.timing && tid == 0) P.timing[16 * g + 1] = cycles_now() - t_start;
 }
 
 // runtime choice of the instantiation (host build, overflow / debug launches)

@@ -468,7 +468,9 @@ class MicroRTSGridModeVecEnv:
                 raw[:, 1:] = 0
             return obs, raw @ self._rw_t, done.bool(), RawRewardInfos(raw)
         o, r, d = self._finish_host(self._to_host("obs", obs), self._to_host("raw", raw), self._to_host("done", done))
-        reward = r
+        # zero_copy hands out views of two alternating pinned buffers: fine for obs / mask, but the rows of `infos` are
+        # accumulated over an episode by the reference's wrappers, so the (tiny) reward block is always a private copy
+        reward = r.copy() if self.zero_copy else r
         if not self.reward_shaping:
             reward[:, 1:] = 0
         infos = [{"raw_rewards": item} for item in reward]

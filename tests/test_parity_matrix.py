@@ -71,9 +71,10 @@ def run_case(engine, nsp, ais, mp, partial, max_steps, steps, eps, seed=1234, ai
 # (a) 64x64 that fights: bot vs bot on BloodBath, two full games per env decided by elimination (~2,400 frames each)
 # ---------------------------------------------------------------------------------------------------------------
 @pytest.mark.gpu
-@pytest.mark.parametrize("pipeline", ["direct", "split"])
+@pytest.mark.parametrize("pipeline", ["direct", "block", "split"])
 def test_bloodbath64_bot_games_fight_to_the_end(pipeline):
-    n = run_case("cuda", 0, [W, LR], MAP_64, False, 6000, 5200, 0.0, ai1s=[LR, W], every=16, cuda_kw=dict(pipeline=pipeline, chunks=2), expect_deaths=True)
+    ckw = dict(pipeline="direct", threads_per_game=256) if pipeline == "block" else dict(pipeline=pipeline, chunks=2)
+    n = run_case("cuda", 0, [W, LR], MAP_64, False, 6000, 5200, 0.0, ai1s=[LR, W], every=16, cuda_kw=ckw, expect_deaths=True)
     assert n >= 2
 
 
@@ -90,10 +91,13 @@ MATRIX = {
     "u8_p31_8x8_split": (4, [W, LR, P], MAP_8, True, 150, 500, 0.08, dict(dtype=np.uint8, pipeline="split", chunks=2)),
     "u8_p31_32x32_direct": (2, [W, POL], MAP_32, True, 200, 450, 0.05, dict(dtype=np.uint8, pipeline="direct")),
     "u8_p31_32x32_split": (2, [W, POL], MAP_32, True, 200, 450, 0.05, dict(dtype=np.uint8, pipeline="split", chunks=3)),
-    "u8_p31_64x64_block": (2, [W], MAP_64, True, 120, 300, 0.05, dict(dtype=np.uint8, pipeline="direct")),
+    "u8_p31_64x64_block": (2, [W], MAP_64, True, 120, 300, 0.05, dict(dtype=np.uint8, pipeline="direct", threads_per_game=256)),
+    "u8_p31_64x64_warp": (2, [W], MAP_64, True, 120, 300, 0.05, dict(dtype=np.uint8, pipeline="direct")),
     "u8_p31_64x64_split": (2, [W], MAP_64, True, 120, 300, 0.05, dict(dtype=np.uint8, pipeline="split", chunks=2)),
-    "u8_p29_64x64_block": (2, [LR], MAP_64, False, 150, 320, 0.05, dict(dtype=np.uint8, pipeline="direct")),
-    "i32_p31_64x64_block": (2, [POW], MAP_64, True, 150, 320, 0.05, dict(pipeline="direct")),
+    "u8_p29_64x64_block": (2, [LR], MAP_64, False, 150, 320, 0.05, dict(dtype=np.uint8, pipeline="direct", threads_per_game=256)),
+    "i32_p31_64x64_block": (2, [POW], MAP_64, True, 150, 320, 0.05, dict(pipeline="direct", threads_per_game=256)),
+    "i32_p31_64x64_warp": (2, [POW], MAP_64, True, 150, 320, 0.05, dict(pipeline="direct")),
+    "i32_p29_16x16_plain_stores": (4, [W, P], MAP_16, False, 200, 500, 0.05, dict(pipeline="direct", threads_per_game=64)),
     "i32_p29_64x64_split": (2, [W], MAP_64, False, 150, 320, 0.05, dict(pipeline="split", chunks=2)),
     "i32_p29_16x16_split4": (6, [P, W, LR, W], MAP_16, False, 250, 700, 0.05, dict(pipeline="split", chunks=4)),
     "i32_p31_16x16_split": (4, [POW, POH, P], MAP_16, True, 300, 650, 0.05, dict(pipeline="split", chunks=2)),
