@@ -141,7 +141,7 @@ struct mrts_env {
     uint32_t sample_counter = 0;
     int last_launches = 0;  // kernels enqueued by the last launch()
     bool pipeline_hint_direct = false;
-    int bulk_mask = 1;      // direct mode: bulk-store mask writer (MRTS_BULK_MASK=0 switches it off, tuning)
+    int bulk_mask = 3;      // direct mode: which tensors take the bulk writers (bit 0 obs, bit 1 mask; MRTS_BULK_OUT overrides, tuning)
 };
 
 namespace {
@@ -226,7 +226,9 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     }
     if (!warp) P.scap = P.cap;  // the block kernel stages the full capacity
     // direct mode on the warp kernels: the tensors go through the copy engine when their rows line up with 16-byte groups
-    P.bulk_out = !split && warp && want && e->bulk_mask && expand_supported(P.HW, P.planes, P.elem, obs, mask) ? 1 : 0;
+    // (measured: a win from 16x16 up; on 8x8 maps and for the many non-empty cells of partially observable views the plain
+    // store loops are faster -- DESIGN.md section 4)
+    P.bulk_out = !split && warp && want && expand_supported(P.HW, P.planes, P.elem, obs, mask) ? e->bulk_mask : 0;
     const bool defer = warp && P.scap < P.cap;
 
     // ---- per-step counters: next step's class counts, deferred-game counts, expansion work counters
@@ -350,9 +352,9 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     return mark_last(e, st);
 }
 
-// direct mode: 32 = one warp per game (the bulk writers need no more threads to keep the copy engine busy, whatever
-// the map size); cfg->threads_per_game > 0 asks for the one-block-per-game kernel with plain stores instead
-int choose_threads(int) { return 32; }
+// direct mode: 32 = one warp per game; above 32x32 one 256-thread block per game (1.87 MB of output per 64x64 view:
+// measured faster with every thread of a block on the store loops).  cfg->threads_per_game overrides.
+int choose_threads(int HW) { return HW <= 1024 ? 32 : 256; }
 
 }  // namespace
 
@@ -451,8 +453,9 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         if (forced == MRTS_PIPELINE_DIRECT || forced == MRTS_PIPELINE_SPLIT) e->pipeline = forced;
     }
     if (e->pipeline == 0) e->pipeline = MRTS_PIPELINE_DIRECT;  // measured faster than SPLIT on every BASELINE config
-    e->bulk_mask = env_int("MRTS_BULK_MASK", 1) != 0;
-    e->pipeline_hint_direct = e->pipeline == MRTS_PIPELINE_DIRECT && e->bulk_mask;
+    e->bulk_mask = env_int("MRTS_BULK_OUT", -1);  // bit 0 = obs, bit 1 = mask; -1 = choose
+    if (e->bulk_mask < 0 || e->bulk_mask > 3) e->bulk_mask = HW >= 256 ? (P.partial ? 2 : 3) : 0;
+    e->pipeline_hint_direct = e->pipeline == MRTS_PIPELINE_DIRECT && e->bulk_mask != 0;
     // Register budget: light games (self-play, PassiveAI) fit 64 registers without spills -> 32 warps per SM;
     // the scripted-bot kernels take 96.
     e->regs[0] = env_int("MRTS_REGS_LIGHT", 64);

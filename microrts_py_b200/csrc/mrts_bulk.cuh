@@ -117,7 +117,7 @@ __device__ __forceinline__ void tiles_init(uint8_t* tiles, int zero_bytes, int e
 // groups; under partial observability whole regions differ from the empty pattern).  Both writers of a warp share
 // the buffers and LANE 0 issues every copy, so one bulk-group sequence orders all reuse: before a buffer is
 // written again the copy that read it two flushes ago must be done (wait_group.read 1).
-constexpr int STAGE_BUF_BYTES = 2496;  // 4 mask groups (4 x 624) or 5 observation groups (5 x 464 / 496)
+constexpr int STAGE_BUF_BYTES = 1248;  // 2 mask groups (2 x 624) or 2 observation groups (2 x 464 / 496): shared memory is what bounds the resident games
 constexpr int STAGE_BYTES = 2 * STAGE_BUF_BYTES;
 struct Stage {
     uint8_t* buf0;

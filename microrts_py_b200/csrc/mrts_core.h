@@ -919,18 +919,19 @@ struct Sim {
         else u[i].flags &= (uint8_t)~UF_AA_ATTACK;
         wsync();
     }
-    // The unit array is in creation order and uids are handed out in creation order (template
-    // index, then next_uid++), compaction is stable: the array is sorted by uid.
-    MRTS_HD int find_uid(uint16_t uid, int vp) const {  // pgs.getUnits().contains(u) on the view
+    // pgs.getUnits().contains(u) on the view: one unit per lane compares its uid (uids are unique inside an episode)
+    MRTS_HD int find_uid(uint16_t uid, int vp) const {
         if (uid == NO_UID) return -1;
-        int lo = 0, hi = nunits();
+        const int n = nunits();
 #pragma unroll 1
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            if (u[mid].uid < uid) lo = mid + 1;
-            else hi = mid;
+        for (int base = 0; base < n; base += nl) {
+            const int i = base + lane;
+            const unsigned m = wballot(i < n && u[i].uid == uid);
+            if (m) {
+                const int k = base + ffs32(m) - 1;
+                return inview(k, vp) ? k : -1;
+            }
         }
-        if (lo < nunits() && u[lo].uid == uid) return inview(lo, vp) ? lo : -1;
         return -1;
     }
     MRTS_HD static int iabs(int v) { return v < 0 ? -v : v; }
@@ -1059,15 +1060,50 @@ struct Sim {
     }
     // Can a search from (sx,sy) ever pop a cell within `range` of (tx,ty)?  Flood fill of F from the
     // start.  Only used to cut a search short that is bound to fail: the search result is unchanged.
+    // Device, maps up to 32 rows: lane y keeps row y in a register and every round each row takes in its
+    // two neighbours (shuffles) and spreads along its runs of ones -- a few dozen instructions per round, one
+    // round per row the fill has to travel, instead of serial sweeps over shared memory.
     MRTS_HD bool flood_reaches(int sx, int sy, int tx, int ty, int range) const {
         const uint64_t* F = rows_F();
         uint64_t* R = rows_R();
+        const uint64_t sbit = 1ull << sx;
+#if defined(__CUDA_ARCH__)
+        if (H <= 32) {
+            const uint64_t Fy = lane < H ? F[lane] : 0ull;
+            // the start cell itself is occupied: seed its enterable neighbours
+            uint64_t Ry = 0;
+            if (lane == sy - 1 || lane == sy + 1) Ry = sbit & Fy;
+            if (lane == sy) Ry = hfill(((sbit << 1) | (sbit >> 1)) & Fy, Fy);
+#pragma unroll 1
+            for (;;) {
+                uint64_t up = __shfl_up_sync(0xFFFFFFFFu, Ry, 1), dn = __shfl_down_sync(0xFFFFFFFFu, Ry, 1);
+                if (lane == 0) up = 0;
+                if (lane == 31) dn = 0;
+                const uint64_t filled = hfill((Ry | up | dn) & Fy, Fy);
+                const unsigned changed = wballot(filled != Ry);
+                Ry = filled;
+                if (!changed) break;
+            }
+            // any filled cell within range of the target?
+            const int dy = lane - ty, sq = range * range;
+            bool hit = false;
+            if (lane < H && dy >= -range && dy <= range) {
+#pragma unroll 1
+                for (int dx = -range; dx <= range; dx++) {
+                    const int x = tx + dx;
+                    if (x < 0 || x >= W || dx * dx + dy * dy > sq) continue;
+                    hit = hit || ((Ry >> x) & 1ull);
+                }
+            }
+            return wballot(hit) != 0;
+        }
+#endif
 #pragma unroll 1
         for (int y = 0; y < H; y++) R[y] = 0;
         // the start cell itself is occupied: seed its enterable neighbours
-        if (sy > 0) R[sy - 1] = (1ull << sx) & F[sy - 1];
-        if (sy + 1 < H) R[sy + 1] = (1ull << sx) & F[sy + 1];
-        R[sy] = hfill((((1ull << sx) << 1) | ((1ull << sx) >> 1)) & F[sy], F[sy]);
+        if (sy > 0) R[sy - 1] = sbit & F[sy - 1];
+        if (sy + 1 < H) R[sy + 1] = sbit & F[sy + 1];
+        R[sy] = hfill(((sbit << 1) | (sbit >> 1)) & F[sy], F[sy]);
         bool changed = true;
 #pragma unroll 1
         while (changed) {
@@ -1110,6 +1146,51 @@ struct Sim {
     // findPathToPositionInRange on a map up to 64 wide.  Same open-list order as astar_first_move
     // (the generic form below, which documents it), with cells addressed as (y << ws) | x and the
     // neighbour tests "enterable and not yet pushed" done on the row bitmaps.
+    //
+    // One expansion = one pop + up to four pushes.  The four neighbours (up, right, down, left) are handled by
+    // four lanes at once on the device (the host build walks d = 0..3): with a Manhattan heuristic a neighbour's
+    // f is either the popped node's f (it is closer to the target) or f + 2, so the pushes fall into two stacks and
+    // a ballot tells every lane who else pushes onto its stack -- the lane links its node to the next lower
+    // pusher (or to the old head), the highest pusher becomes the new head: exactly the order d = 0..3 of
+    // sequential pushes.  Each node also records the first move of its path (`parent` array: the root
+    // direction), so the answer is read off the node that ends the search instead of walking back.
+    // pusher d's link: the node below it on its stack after the pushes of this expansion (reads only)
+    MRTS_HD int astar_link(const AStarBuf& b, int d, unsigned okm, unsigned cm, int x, int y, int ws, int fcur) const {
+        if (!((okm >> d) & 1u)) return -1;
+        const bool closer = (cm >> d) & 1u;
+        const unsigned grp = closer ? cm : (okm & ~cm);
+        const unsigned lower = grp & ((1u << d) - 1u);
+        if (lower) {
+            const int dp = 31 - clz32(lower);  // the pusher right below this one on the same stack
+            return ((y + dir_dy(dp)) << ws) | (x + dir_dx(dp));
+        }
+        return b.head[closer ? fcur : fcur + 2];
+    }
+    // pusher d's stores (every lane / every d of an expansion reads its link before any of these run)
+    MRTS_HD void astar_store(const AStarBuf& b, uint64_t* V, int d, int link, unsigned okm, unsigned cm, int x, int y, int ws, int g1, int fcur, int root) const {
+        if (!((okm >> d) & 1u)) {
+            if (d == D_RIGHT && ((okm >> D_LEFT) & 1u)) V[y] |= (1ull << x) >> 1;  // the lane of `right` marks both cells of row y
+            return;
+        }
+        const int nx = x + dir_dx(d), ny = y + dir_dy(d);
+        const int np = (ny << ws) | nx;
+        const bool closer = (cm >> d) & 1u;
+        const unsigned grp = closer ? cm : (okm & ~cm);
+        b.cost[np] = (int16_t)g1;
+        b.parent[np] = (int16_t)(root >= 0 ? root : d);  // first move of the path to np
+        b.next[np] = (int16_t)link;
+        if ((grp >> (d + 1)) == 0) b.head[closer ? fcur : fcur + 2] = (int16_t)np;  // the last pusher of this stack
+        if (d == D_UP || d == D_DOWN) V[ny] |= 1ull << x;
+        else if (d == D_RIGHT) V[y] |= (2ull << x) | (((okm >> D_LEFT) & 1u) ? ((1ull << x) >> 1) : 0ull);
+        // (left: marked by the lane of `right`)
+    }
+    static MRTS_HD int clz32(unsigned v) {
+#if defined(__CUDA_ARCH__)
+        return __clz((int)v);
+#else
+        return v ? __builtin_clz(v) : 32;
+#endif
+    }
     MRTS_HD int astar_rows(int i, int targetpos, int range, int vp) {
         const AStarBuf b = astar_buf();
         const Unit& su = u[i];
@@ -1129,34 +1210,38 @@ struct Sim {
             return -1;
         }
         MRTS_STAT(searches++);
-        st->tp[6]++;
         wsync();
 #pragma unroll 1
         for (int y = lane; y < H; y += nl) V[y] = 0;
         wsync();
         const int startPk = (sy << ws) | sx;
         const int h0 = iabs(sx - tx) + iabs(sy - ty);
-        V[sy] = 1ull << sx;
-        b.parent[startPk] = (int16_t)startPk;
-        b.cost[startPk] = 0;
-        b.next[startPk] = -1;
-        b.head[h0] = (int16_t)startPk;
-        int fmin = h0, fmax = h0, flo = h0, nopen = 1, expanded = 0;
-        bool found = false;
-        int pk = startPk;
+        if (lane == 0) {
+            V[sy] = 1ull << sx;
+            b.parent[startPk] = -1;  // no move yet
+            b.cost[startPk] = 0;
+            b.next[startPk] = -1;
+            b.head[h0] = (int16_t)startPk;
+        }
+        wsync();
+        int fmin = h0, fmax = h0, nopen = 1, expanded = 0;
+        int result = -1;
 #pragma unroll 1
         while (nopen > 0) {
-            while (b.head[fmin] < 0) fmin++;
-            pk = b.head[fmin];
-            b.head[fmin] = b.next[pk];
-            nopen--;
+            int pk = b.head[fmin];
+#pragma unroll 1
+            while (pk < 0 && fmin < fmax) pk = b.head[++fmin];
+            if (pk < 0) break;  // (cannot happen while nopen > 0)
+            const int nxt = b.next[pk], gcur = b.cost[pk], root = b.parent[pk];
             const int x = pk & (WP - 1), y = pk >> ws;
+            wsync();  // every lane has read the stack before its head moves
+            if (lane == 0) b.head[fmin] = (int16_t)nxt;
+            nopen--;
             if ((x - tx) * (x - tx) + (y - ty) * (y - ty) <= sq) {
-                found = true;
+                result = root;  // -1 when the start itself is in range (null)
                 break;
             }
             MRTS_STAT(expanded++);
-            st->tp[7]++;
             // a search that keeps growing is checked once against a flood fill: unreachable -> null right away
             if (++expanded == ASTAR_GUARD_AFTER) {
                 MRTS_STAT(guard++);
@@ -1169,49 +1254,45 @@ struct Sim {
                     break;
                 }
             }
-            const int g1 = b.cost[pk] + 1;
-            const uint64_t bx = 1ull << x;
+            const int g1 = gcur + 1, hcur = iabs(x - tx) + iabs(y - ty), fcur = gcur + hcur;
             // enterable and not yet pushed, in the reference's neighbour order: up, right, down, left (:236-262)
-            const uint64_t mid = F[y] & ~V[y];
-            const bool ok_up = y > 0 && ((F[y - 1] & ~V[y - 1]) & bx);
-            const bool ok_right = x + 1 < W && (mid & (bx << 1));
-            const bool ok_down = y + 1 < H && ((F[y + 1] & ~V[y + 1]) & bx);
-            const bool ok_left = x > 0 && (mid & (bx >> 1));
-#pragma unroll
-            for (int d = 0; d < 4; d++) {
-                const bool ok = d == D_UP ? ok_up : (d == D_RIGHT ? ok_right : (d == D_DOWN ? ok_down : ok_left));
-                if (!ok) continue;
-                const int nx = x + dir_dx(d), ny = y + dir_dy(d);
-                const int np = (ny << ws) | nx;
-                const int f = iabs(nx - tx) + iabs(ny - ty) + g1;
-                b.cost[np] = (int16_t)g1;
-                b.parent[np] = (int16_t)pk;
-                V[ny] |= 1ull << nx;
-                b.next[np] = b.head[f];
-                b.head[f] = (int16_t)np;
-                if (f < fmin) fmin = f;
-                if (f < flo) flo = f;
-                if (f > fmax) fmax = f;
-                nopen++;
+            unsigned okm = 0, cm = 0;
+#if defined(__CUDA_ARCH__)
+            {
+                const int d = lane & 3, nx = x + dir_dx(d), ny = y + dir_dy(d);
+                bool ok = lane < 4 && nx >= 0 && ny >= 0 && nx < W && ny < H;
+                if (ok) ok = ((F[ny] & ~V[ny]) >> nx) & 1ull;
+                okm = wballot(ok) & 0xFu;
+                cm = wballot(ok && iabs(nx - tx) + iabs(ny - ty) < hcur) & 0xFu;
+                const int link = lane < 4 ? astar_link(b, d, okm, cm, x, y, ws, fcur) : -1;
+                wsync();  // all links are read before the stacks change
+                if (lane < 4) astar_store(b, V, d, link, okm, cm, x, y, ws, g1, fcur, root);
             }
+#else
+            for (int d = 0; d < 4; d++) {
+                const int nx = x + dir_dx(d), ny = y + dir_dy(d);
+                if (nx < 0 || ny < 0 || nx >= W || ny >= H) continue;
+                if (!(((F[ny] & ~V[ny]) >> nx) & 1ull)) continue;
+                okm |= 1u << d;
+                if (iabs(nx - tx) + iabs(ny - ty) < hcur) cm |= 1u << d;
+            }
+            {
+                int link[4];
+                for (int d = 0; d < 4; d++) link[d] = astar_link(b, d, okm, cm, x, y, ws, fcur);
+                for (int d = 0; d < 4; d++) astar_store(b, V, d, link[d], okm, cm, x, y, ws, g1, fcur, root);
+            }
+#endif
+            if (okm & ~cm) fmax = fmax > fcur + 2 ? fmax : fcur + 2;
+            nopen += popc(okm);
+            wsync();  // the pushes are visible to every lane before the next pop
         }
+        st->tp[6]++;
+        st->tp[7] += expanded;
         wsync();
 #pragma unroll 1
-        for (int f = flo + lane; f <= fmax; f += nl) b.head[f] = -1;  // leave the stacks empty for the next search
+        for (int f = h0 + lane; f <= fmax; f += nl) b.head[f] = -1;  // leave the stacks empty for the next search
         wsync();
-        if (!found) return -1;
-        int last = pk, parent = b.parent[pk];
-#pragma unroll 1
-        while (parent != pk) {
-            last = pk;
-            pk = parent;
-            parent = b.parent[pk];
-        }
-        if (last == pk + WP) return D_DOWN;
-        if (last == pk - 1) return D_LEFT;
-        if (last == pk - WP) return D_UP;
-        if (last == pk + 1) return D_RIGHT;
-        return -1;
+        return result;
     }
 
     // once per game pass, by the whole thread group, before the leader runs (the region is scratch)

@@ -51,7 +51,7 @@ struct EnvParams {
     int32_t mode;
     int32_t game0, game1;           // this launch covers the slots / games [game0, game1)
     int32_t elem;                   // bytes per obs/mask element: 4 (int32, reference dtype) or 1 (uint8)
-    int32_t bulk_out;               // direct mode, warp kernels: obs / mask go through the copy engine (static tiles + staged groups, mrts_bulk.cuh)
+    int32_t bulk_out;               // direct mode, warp kernels: bit 0 = obs, bit 1 = mask go through the copy engine (static tiles + staged groups, mrts_bulk.cuh)
     const int32_t* actions;         // (N, HW, 7) int32
     void* obs;                      // (N, H, W, planes) or null
     void* mask;                     // (N, HW, 78) or null
@@ -107,7 +107,7 @@ MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int any_bot) {
     L.umask = o;
     o += align16(cap * 12);
     L.slots = o;  // staging of the bulk writers (direct mode): bulk::STAGE_BYTES (mrts_bulk.cuh)
-    o += 2 * 2496;
+    o += 2 * 1248;
     L.total = o > end_rules ? o : end_rules;
     return L;
 }
@@ -359,7 +359,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     // direct mode on the warp kernels: the tensors go through the copy engine (mrts_bulk.cuh); the staged groups drain
     // while the warp goes on (unit masks, packed outputs, blob write-back)
     const bool bulk_out = P.bulk_out && blk != nullptr && nth == 32;
-    static_assert(bulk::STAGE_BYTES == 2 * 2496, "Layout::slots");
+    static_assert(bulk::STAGE_BYTES == 2 * 1248, "Layout::slots");
     bulk::Stage stage;
     bulk::ObsWriter ow;
     bulk::MaskWriter mw;
@@ -383,7 +383,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
             }
             sync();
 #if defined(__CUDA_ARCH__)
-            if (P.obs && bulk_out) bulk_obs_view(words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, ow);
+            if (P.obs && (P.bulk_out & 1) && bulk_out) bulk_obs_view(words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, ow);
             else
 #endif
             if (P.obs) store_obs_rt(P.elem, P.planes, words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, tid, nth);
@@ -398,7 +398,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (P.mask || P.pmask || P.ment || P.next_actions) unit_masks(s, umask, tid, nth);
 
     // ---------------- mask: zero fill, then the 78 entries of every source unit
-    const bool bulk_mask = P.mask && bulk_out;
+    const bool bulk_mask = P.mask && (P.bulk_out & 2) && bulk_out;
     if (P.mask && !bulk_mask)
         for (int v = 0; v < nviews; v++) zero_mask_rt(P.elem, P.HW, (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env, tid, nth);
     if (P.pmask) {

@@ -236,6 +236,7 @@ class MicroRTSGridModeVecEnv:
         self.zero_copy = bool(zero_copy)
         self.fuse_mask = bool(fuse_mask)
         self.host_transport = bool(host_transport) and not self.return_torch
+        self._host_slots = host_transport != "full"  # "full": the plain host-buffer calls, every element rewritten every step
 
         self._lib = _capi.lib()
         cfg, self._keep, cycle_idx = _capi.make_config(
@@ -342,7 +343,7 @@ class MicroRTSGridModeVecEnv:
         if self.host_transport:
             self._hcur ^= 1
             o, m = self._hbuf["obs"][self._hcur], self._hbuf["mask"][self._hcur]
-            _capi.check(self._lib.mrts_reset_host_slot(self._h, _np_ptr(o), _np_ptr(m), self._hcur))
+            _capi.check(self._lib.mrts_reset_host_slot(self._h, _np_ptr(o), _np_ptr(m), self._hcur if self._host_slots else -1))
             self._h_mask_np = m
             return o
         if self.return_packed:
@@ -439,7 +440,7 @@ class MicroRTSGridModeVecEnv:
             o, m, reward, d = self._hbuf["obs"][k], self._hbuf["mask"][k], self._hbuf["raw"][k], self._hbuf["done"][k]
             vp = C.c_void_p
             _capi.check(self._lib.mrts_step_host_slot(self._h, a.ctypes.data_as(vp), a.dtype.itemsize, _np_ptr(o), _np_ptr(m),
-                                                      reward.ctypes.data_as(vp), d.ctypes.data_as(vp), k))
+                                                      reward.ctypes.data_as(vp), d.ctypes.data_as(vp), k if self._host_slots else -1))
             self._h_mask_np = m
             if not self.reward_shaping:
                 reward[:, 1:] = 0

@@ -1,5 +1,6 @@
 // TEST INFRASTRUCTURE -- NOT PRODUCT CODE.  See mrts_oracle.hpp for the header note.
 // Plain C ABI over the oracle so tests / bench.py can drive it through ctypes.
+#include <thread>
 #include <cstring>
 
 #include "mrts_oracle.hpp"
@@ -79,6 +80,8 @@ int pa_to_rows(const PlayerAction& pa, int32_t* rows, int cap) {
 extern "C" {
 
 // ---- vectorised env
+// host threads the independent envs are spread over (the timed CPU baseline runs at 1 and at all cores)
+void orc_vec_set_threads(void* h, int threads) { ((VecEnv*)h)->threads = threads < 1 ? 1 : threads; }
 void* orc_vec_create(int num_selfplay, int num_bot, int max_steps, int partial_obs, int none_mode, int threads) {
     VecEnv* v = new VecEnv();
     v->num_selfplay = num_selfplay;
@@ -104,6 +107,56 @@ void orc_vec_set_ai1(void* h, int b, int ai1_id) {
 void orc_vec_init(void* h) { ((VecEnv*)h)->init(); }
 void orc_vec_reset(void* h, int32_t* obs) { ((VecEnv*)h)->reset(obs); }
 void orc_vec_masks(void* h, int32_t* mask78, int32_t* source) { ((VecEnv*)h)->get_masks(mask78, source); }
+// Policy stand-in of the timed CPU baseline (bench.py): one masked-uniform action per cell that may act, drawn from the
+// mask the caller just got from orc_vec_masks -- the recipe of the reference's hello_world.py:27-67, spread over the same
+// host threads as the env.  Not part of the restated path; it only feeds it valid actions quickly (NumPy takes ~10x the
+// env's own time at 8,192 envs).  actions (N, HW, 7) int32; cells that may not act get zeros.
+void orc_vec_sample_actions(void* h, const int32_t* mask78, uint64_t seed, int32_t* actions) {
+    VecEnv* v = (VecEnv*)h;
+    const int HW = v->H * v->W, N = v->N;
+    static const int lo[8] = {0, 6, 10, 14, 18, 22, 29, 78};
+    auto mix = [](uint64_t z) {
+        z += 0x9E3779B97F4A7C15ULL;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+        return z ^ (z >> 31);
+    };
+    auto work = [&](int e0, int e1) {
+        for (int e = e0; e < e1; e++)
+            for (int c = 0; c < HW; c++) {
+                const int32_t* m = mask78 + ((size_t)e * HW + c) * 78;
+                int32_t* a = actions + ((size_t)e * HW + c) * 7;
+                if (!m[0]) {
+                    for (int k = 0; k < 7; k++) a[k] = 0;
+                    continue;
+                }
+                uint64_t r = mix(seed ^ ((uint64_t)e << 20) ^ (uint64_t)c);
+                for (int k = 0; k < 7; k++) {
+                    int n = 0;
+                    for (int b = lo[k]; b < lo[k + 1]; b++) n += m[b] != 0;
+                    int pick = 0;
+                    if (n > 0) {
+                        r = mix(r);
+                        int want = (int)(r % (uint64_t)n);
+                        for (int b = lo[k]; b < lo[k + 1]; b++)
+                            if (m[b] && want-- == 0) {
+                                pick = b - lo[k];
+                                break;
+                            }
+                    }
+                    a[k] = pick;
+                }
+            }
+    };
+    const int T = v->threads;
+    if (T <= 1 || N < 2 * T) {
+        work(0, N);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; t++) th.emplace_back(work, (int)((long long)N * t / T), (int)((long long)N * (t + 1) / T));
+    for (auto& x : th) x.join();
+}
 void orc_vec_step(void* h, const int32_t* actions, int32_t* obs, double* rewards, uint8_t* done) {
     ((VecEnv*)h)->step(actions, obs, rewards, done);
 }

@@ -37,6 +37,8 @@ def lib():
         L.orc_vec_create.argtypes = [C.c_int] * 6
         L.orc_vec_add_env.argtypes = [vp, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.orc_vec_init.argtypes = [vp]
+        L.orc_vec_set_threads.argtypes = [vp, C.c_int]
+        L.orc_vec_sample_actions.argtypes = [vp, C.c_void_p, C.c_uint64, C.c_void_p]
         L.orc_vec_set_ai1.argtypes = [vp, C.c_int, C.c_int]
         L.orc_vec_reset.argtypes = [vp, C.c_void_p]
         L.orc_vec_masks.argtypes = [vp, C.c_void_p, C.c_void_p]
@@ -155,11 +157,23 @@ class OracleVecEnv:
         self.L.orc_vec_reset(self.h, _p(obs))
         return obs
 
-    def get_masks(self):
-        m = np.zeros((self.N, self.H * self.W, 78), np.int32)
-        s = np.zeros((self.N, self.H * self.W), np.int32)
+    def get_masks(self, out=None):
+        """(mask (N,HW,78), source_unit_mask (N,HW)); `out` = that pair of arrays to reuse (the Java client reuses its own)."""
+        if out is None:
+            m = np.zeros((self.N, self.H * self.W, 78), np.int32)
+            s = np.zeros((self.N, self.H * self.W), np.int32)
+        else:
+            m, s = out
         self.L.orc_vec_masks(self.h, _p(m), _p(s))
         return m, s
+
+    def set_threads(self, threads):
+        self.L.orc_vec_set_threads(self.h, int(threads))
+
+    def sample_actions(self, mask, seed, out):
+        """bench.py's policy stand-in for the CPU arms: masked-uniform actions for `mask` into `out` (N,HW,7) int32."""
+        self.L.orc_vec_sample_actions(self.h, _p(mask), C.c_uint64(seed), _p(out))
+        return out
 
     def step(self, actions, out=None):
         a = np.ascontiguousarray(np.asarray(actions).reshape(self.N, self.H * self.W, 7), np.int32)
