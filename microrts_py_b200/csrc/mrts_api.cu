@@ -140,8 +140,7 @@ struct mrts_env {
     int rows_cap = 0;
     uint32_t sample_counter = 0;
     int last_launches = 0;  // kernels enqueued by the last launch()
-    bool pipeline_hint_direct = false;
-    int bulk_mask = 3;      // direct mode: which tensors take the bulk writers (bit 0 obs, bit 1 mask; MRTS_BULK_OUT overrides, tuning)
+    int bulk_mask = 1;      // direct mode: the mask takes the bulk writer (MRTS_BULK_MASK overrides, tuning)
 };
 
 namespace {
@@ -226,9 +225,7 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     }
     if (!warp) P.scap = P.cap;  // the block kernel stages the full capacity
     // direct mode on the warp kernels: the tensors go through the copy engine when their rows line up with 16-byte groups
-    // (measured: a win from 16x16 up; on 8x8 maps and for the many non-empty cells of partially observable views the plain
-    // store loops are faster -- DESIGN.md section 4)
-    P.bulk_out = !split && warp && want && expand_supported(P.HW, P.planes, P.elem, obs, mask) ? e->bulk_mask : 0;
+    P.bulk_out = !split && warp && mask && e->bulk_mask && (P.HW * P.elem) % 8 == 0 && (((uintptr_t)mask) & 15) == 0 ? 1 : 0;
     const bool defer = warp && P.scap < P.cap;
 
     // ---- per-step counters: next step's class counts, deferred-game counts, expansion work counters
@@ -453,35 +450,47 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
         if (forced == MRTS_PIPELINE_DIRECT || forced == MRTS_PIPELINE_SPLIT) e->pipeline = forced;
     }
     if (e->pipeline == 0) e->pipeline = MRTS_PIPELINE_DIRECT;  // measured faster than SPLIT on every BASELINE config
-    e->bulk_mask = env_int("MRTS_BULK_OUT", -1);  // bit 0 = obs, bit 1 = mask; -1 = choose
-    if (e->bulk_mask < 0 || e->bulk_mask > 3) e->bulk_mask = HW >= 256 ? (P.partial ? 2 : 3) : 0;
-    e->pipeline_hint_direct = e->pipeline == MRTS_PIPELINE_DIRECT && e->bulk_mask != 0;
+    e->bulk_mask = env_int("MRTS_BULK_MASK", -1);  // 1 / 0 = force the bulk mask writer on / off; -1 = choose below
     // Register budget: light games (self-play, PassiveAI) fit 64 registers without spills -> 32 warps per SM;
     // the scripted-bot kernels take 96.
     e->regs[0] = env_int("MRTS_REGS_LIGHT", 64);
     e->regs[1] = env_int("MRTS_REGS_HEAVY", 96);
-    for (int k = 0; k < 2; k++) {
-        // Games per block: a block's shared memory and warp slots are only released when its slowest
-        // game is done and game times vary widely (scripted-bot path finding), so take the smallest
-        // count that still reaches the most resident games per SM.
+    // Games per block: a block's shared memory and warp slots are only released when its slowest
+    // game is done and game times vary widely (scripted-bot path finding), so take the smallest
+    // count that still reaches the most resident games per SM.  The bulk mask writer adds one tile of zeros per
+    // block: it is used unless that tile costs more than a twentieth of the resident games (32x32 maps).
+    auto choose_gpb = [&](int k, int tile_bytes, int* warps) {
         const int by_regs = 65536 / (32 * (e->regs[k] <= 64 ? 64 : (e->regs[k] <= 96 ? 96 : 128)));
         int best = 1, best_w = 0;
         for (int g = 1; g <= GPB_MAX; g *= 2) {
-            if (g * e->smem[k] > maxsm) break;
-            int blocks = smem_sm / (g * e->smem[k] + 1024 + (e->pipeline_hint_direct ? 8960 : 0));  // 1 KB per-block reservation (+ the bulk writer's zero tile)
+            if (g * e->smem[k] + tile_bytes > maxsm) break;
+            int blocks = smem_sm / (g * e->smem[k] + 1024 + tile_bytes);  // 1 KB per-block reservation
             if (blocks > max_blocks) blocks = max_blocks;
             int w = blocks * g;
             if (w > by_regs) w = by_regs;
             if (w > best_w) best_w = w, best = g;
         }
-        e->gpb[k] = cfg->threads_per_game < 0 ? -cfg->threads_per_game : best;
-        const int forced = env_int(k ? "MRTS_GPB_HEAVY" : "MRTS_GPB_LIGHT", 0);
-        if (forced > 0) e->gpb[k] = forced;
-        if (e->gpb[k] > GPB_MAX) e->gpb[k] = GPB_MAX;
-        while (e->gpb[k] > 1 && e->gpb[k] * e->smem[k] > maxsm) e->gpb[k] /= 2;
+        *warps = best_w;
+        return best;
+    };
+    {
+        int w_plain[2], w_bulk[2], g_plain[2], g_bulk[2];
+        for (int k = 0; k < 2; k++) {
+            g_plain[k] = choose_gpb(k, 0, &w_plain[k]);
+            g_bulk[k] = choose_gpb(k, 4992, &w_bulk[k]);
+        }
+        if (e->bulk_mask < 0) e->bulk_mask = 20 * w_bulk[0] >= 19 * w_plain[0] && 20 * w_bulk[1] >= 19 * w_plain[1] ? 1 : 0;
+        if (e->pipeline != MRTS_PIPELINE_DIRECT) e->bulk_mask = e->bulk_mask > 0 ? 1 : 0;
+        for (int k = 0; k < 2; k++) {
+            e->gpb[k] = cfg->threads_per_game < 0 ? -cfg->threads_per_game : (e->bulk_mask ? g_bulk[k] : g_plain[k]);
+            const int forced = env_int(k ? "MRTS_GPB_HEAVY" : "MRTS_GPB_LIGHT", 0);
+            if (forced > 0) e->gpb[k] = forced;
+            if (e->gpb[k] > GPB_MAX) e->gpb[k] = GPB_MAX;
+            while (e->gpb[k] > 1 && e->gpb[k] * e->smem[k] + 4992 > maxsm) e->gpb[k] /= 2;
+        }
     }
-    CREATE_CK(light_set_smem(e->gpb[0] * e->smem[0] + 8960, e->smem_block));
-    CREATE_CK(heavy_set_smem(e->gpb[1] * e->smem[1] + 8960, e->smem_block));
+    CREATE_CK(light_set_smem(e->gpb[0] * e->smem[0] + 4992, e->smem_block));
+    CREATE_CK(heavy_set_smem(e->gpb[1] * e->smem[1] + 4992, e->smem_block));
     CREATE_CK(any_set_smem(e->smem_full));
     CREATE_CK(expand_init());
 

@@ -100,6 +100,13 @@ __device__ __forceinline__ uint4 expand_chunk(const uint32_t* w, int j, int elem
     return v;
 }
 
+// a block's tile of zeros alone (every thread of the block, once; ends with a block barrier)
+__device__ __forceinline__ void zero_tile_init(uint8_t* tile, int zero_bytes, int tid, int nth) {
+#pragma unroll 1
+    for (int i = tid; i < zero_bytes / 16; i += nth) ((uint4*)tile)[i] = make_uint4(0, 0, 0, 0);
+    fence_smem();
+    __syncthreads();
+}
 // The block's static tiles: `zero_bytes` of zeros at `tiles`, then EMPTY_GROUPS observation groups of the empty cell.
 // Every thread of the block calls this once, before any writer runs (it ends with a block barrier).
 __device__ __forceinline__ void tiles_init(uint8_t* tiles, int zero_bytes, int elem, int planes, uint32_t empty_word, int tid, int nth) {

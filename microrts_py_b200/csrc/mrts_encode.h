@@ -197,13 +197,12 @@ MRTS_HD void patch_mask_rt(int elem, const Sim& s, int player, const uint32_t* u
 
 #if defined(__CUDACC__)
 constexpr int BULK_ZERO_BYTES = 8 * bulk::GROUP_BYTES;                           // 4,992 bytes of zeros per block
-constexpr int BULK_TILES_BYTES = BULK_ZERO_BYTES + bulk::EMPTY_BYTES_MAX;        // per block, in front of the games' regions
+constexpr int BULK_TILES_BYTES = BULK_ZERO_BYTES;                                // per block, in front of the games' regions
 #endif
 #if defined(__CUDA_ARCH__)
-// Phases C / D, bulk form (warp kernels in direct mode, device only): one view's observation and mask through the
-// copy engine (mrts_bulk.cuh) -- runs of empty cells / zero rows straight from the block's static tiles, only the
-// cells that hold something staged.  The warp walks the grid 32 cells at a time so that mask rows arrive in
-// ascending cell order.
+// Phase D, bulk form (warp kernels in direct mode, device only): one view's mask through the copy engine
+// (mrts_bulk.cuh) -- runs of zero rows straight from the block's zero tile, only the rows of units that may act staged.
+// The warp walks the grid 32 cells at a time so that the rows arrive in ascending cell order.
 __device__ __forceinline__ void bulk_mask_view(const Sim& s, int player, const uint32_t* umask, void* out, bulk::MaskWriter& mw, int lane) {
     mw.begin(out);
 #pragma unroll 1
@@ -229,11 +228,6 @@ __device__ __forceinline__ void bulk_mask_view(const Sim& s, int player, const u
         }
     }
     mw.finish(s.HW / mw.cells_per_group());
-}
-__device__ __forceinline__ void bulk_obs_view(const uint32_t* words, int HW, void* out, bulk::ObsWriter& ow) {
-    ow.begin(out);
-    ow.segment(words, 0, HW / ow.cells_per_group());
-    ow.finish(HW / ow.cells_per_group());
 }
 #endif
 

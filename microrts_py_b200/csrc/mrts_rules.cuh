@@ -34,9 +34,9 @@ __global__ void __launch_bounds__(32 * GPB_MAX, MINB) mrts_rules_warp_kernel(con
     extern __shared__ uint4 smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
-    // direct mode: the block's static tiles of the bulk writers (zero rows, empty cells) sit in front of the games' regions
+    // direct mode: the block's tile of zeros of the bulk mask writer sits in front of the games' regions
     const int zb = P.bulk_out ? BULK_TILES_BYTES : 0;
-    if (zb) bulk::tiles_init((uint8_t*)smem_raw, BULK_ZERO_BYTES, P.elem, P.planes, obs_empty_word(P.partial), (int)threadIdx.x, (int)blockDim.x);
+    if (zb) bulk::zero_tile_init((uint8_t*)smem_raw, BULK_ZERO_BYTES, (int)threadIdx.x, (int)blockDim.x);
     if (slot >= P.nslots) return;
     game_pass<HEAVY>(P, slot_game(P, slot), (uint8_t*)smem_raw + zb + (size_t)warp * smem_per_game, lane, 32, WarpSync(), zb ? (uint8_t*)smem_raw : nullptr);
 }

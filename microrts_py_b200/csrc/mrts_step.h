@@ -51,7 +51,7 @@ struct EnvParams {
     int32_t mode;
     int32_t game0, game1;           // this launch covers the slots / games [game0, game1)
     int32_t elem;                   // bytes per obs/mask element: 4 (int32, reference dtype) or 1 (uint8)
-    int32_t bulk_out;               // direct mode, warp kernels: bit 0 = obs, bit 1 = mask go through the copy engine (static tiles + staged groups, mrts_bulk.cuh)
+    int32_t bulk_out;               // direct mode, warp kernels: the mask goes through the copy engine (zero tile + staged rows, mrts_bulk.cuh)
     const int32_t* actions;         // (N, HW, 7) int32
     void* obs;                      // (N, H, W, planes) or null
     void* mask;                     // (N, HW, 78) or null
@@ -356,16 +356,16 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
 
     // ---------------- observations, one view at a time (before compaction: stale views keep the dead)
 #if defined(__CUDA_ARCH__)
-    // direct mode on the warp kernels: the tensors go through the copy engine (mrts_bulk.cuh); the staged groups drain
-    // while the warp goes on (unit masks, packed outputs, blob write-back)
+    // direct mode on the warp kernels: the mask goes through the copy engine (mrts_bulk.cuh) -- 73 % of a step's bytes,
+    // > 99 % of them zeros that leave from the block's zero tile without touching the load/store pipe; the staged rows
+    // drain while the warp goes on (packed outputs, blob write-back).  The observation keeps its 128-bit store loop:
+    // measured faster than staging it (every cell has to be expanded anyway).
     const bool bulk_out = P.bulk_out && blk != nullptr && nth == 32;
     static_assert(bulk::STAGE_BYTES == 2 * 1248, "Layout::slots");
     bulk::Stage stage;
-    bulk::ObsWriter ow;
     bulk::MaskWriter mw;
     if (bulk_out) {
         stage.init(mem + L.slots, tid);
-        ow.init(&stage, blk + BULK_ZERO_BYTES, obs_empty_word(P.partial), P.elem, P.planes);
         mw.init(&stage, blk, BULK_ZERO_BYTES, P.elem);
     }
 #else
@@ -382,10 +382,6 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
                 obs_words_dead(s, v, v, words, tid, nth);
             }
             sync();
-#if defined(__CUDA_ARCH__)
-            if (P.obs && (P.bulk_out & 1) && bulk_out) bulk_obs_view(words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, ow);
-            else
-#endif
             if (P.obs) store_obs_rt(P.elem, P.planes, words, P.HW, (uint8_t*)P.obs + (size_t)(env0 + v) * obs_env, tid, nth);
             if (P.pobs) copy16<uint32_t>(P.pobs + (size_t)(env0 + v) * P.HW, words, P.HW * 4, tid, nth);
             sync();
@@ -398,7 +394,7 @@ MRTS_HD void game_pass(const EnvParams& P, int g, uint8_t* mem, int tid, int nth
     if (P.mask || P.pmask || P.ment || P.next_actions) unit_masks(s, umask, tid, nth);
 
     // ---------------- mask: zero fill, then the 78 entries of every source unit
-    const bool bulk_mask = P.mask && (P.bulk_out & 2) && bulk_out;
+    const bool bulk_mask = P.mask && bulk_out;
     if (P.mask && !bulk_mask)
         for (int v = 0; v < nviews; v++) zero_mask_rt(P.elem, P.HW, (uint8_t*)P.mask + (size_t)(env0 + v) * mask_env, tid, nth);
     if (P.pmask) {

@@ -215,6 +215,19 @@ static int dump_state(const GameState& gs, int32_t* hdr3, int32_t* rows, int cap
     }
     return (int)gs.units.size();
 }
+// position of every unit's assignment in the unitActions map (issue order), -1 = idle; one entry per unit in pgs.units order
+int orc_game_issue_order(void* h, int32_t* out, int cap) {
+    const GameState& gs = ((GameHandle*)h)->gs;
+    int n = 0;
+    for (auto& u : gs.units) {
+        if (n >= cap) break;
+        int pos = -1;
+        for (size_t k = 0; k < gs.acts.size(); k++)
+            if (gs.acts[k]->unit.get() == u.get()) pos = (int)k;
+        out[n++] = pos;
+    }
+    return n;
+}
 int orc_game_state(void* h, int32_t* hdr3, int32_t* rows, int cap) { return dump_state(((GameHandle*)h)->gs, hdr3, rows, cap); }
 int orc_vec_game_state(void* h, int env, int32_t* hdr3, int32_t* rows, int cap) {
     VecEnv* v = (VecEnv*)h;

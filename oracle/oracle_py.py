@@ -55,6 +55,7 @@ def lib():
         L.orc_game_time.argtypes = [vp]
         L.orc_game_winner.argtypes = [vp]
         L.orc_game_state.argtypes = [vp, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_game_issue_order.argtypes = [vp, C.c_void_p, C.c_int]
         L.orc_game_masks.argtypes = [vp, C.c_int, C.c_void_p]
         L.orc_bot_create.restype = vp
         L.orc_bot_create.argtypes = [C.c_int]
@@ -104,6 +105,12 @@ class OracleGame:
         rows = np.zeros((cap, 12), np.int32)
         n = self.L.orc_game_state(self.h, _p(hdr), _p(rows), cap)
         return hdr, rows[:n].copy()
+
+    def issue_order(self):
+        """position of every unit's assignment in the unitActions map (issue order), -1 = idle, in unit order"""
+        out = np.zeros(self.W * self.H, np.int32)
+        n = self.L.orc_game_issue_order(self.h, _p(out), len(out))
+        return out[:n].copy()
 
     def masks(self, player):
         m = np.zeros((self.H, self.W, 79), np.int32)

@@ -32,6 +32,7 @@ def lib():
         L.hs_set_cycle_maps.argtypes = [vp, vp, C.c_int]
         L.hs_unit_capacity.argtypes = [vp]
         L.hs_export_state.argtypes = [vp, C.c_int, vp, vp, C.c_int]
+        L.hs_import_state.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
         L.hs_last_error.restype = C.c_char_p
         _lib = L
     return _lib
@@ -86,6 +87,13 @@ class HostSimVecEnv:
         if with_mask:
             return obs, rew, done, mask
         return obs, rew, done
+
+    def import_state(self, game, hdr5, rows12, issue_order=None):
+        rows12 = np.ascontiguousarray(rows12, np.int32).reshape(-1, 12)
+        hdr5 = np.ascontiguousarray(hdr5, np.int32)
+        order = np.ascontiguousarray(issue_order, np.int32) if issue_order is not None else None
+        if self.L.hs_import_state(self.h, game, _p(hdr5), _p(rows12), len(rows12), _p(order) if order is not None else None):
+            raise ValueError(self.L.hs_last_error().decode())
 
     def game_state(self, game):
         cap = self.L.hs_unit_capacity(self.h)

@@ -133,6 +133,12 @@ int hs_set_cycle_maps(hs_env* e, const int32_t* idx, int n) {
 }
 int hs_planes(hs_env* e) { return e->S.P.planes; }
 int hs_unit_capacity(hs_env* e) { return e->S.P.cap; }
+int hs_import_state(hs_env* e, int game, const int32_t* hdr5, const int32_t* rows12, int n, const int32_t* issue_order) {
+    if (game < 0 || game >= e->S.P.n_games || n > e->S.P.cap) return -1;
+    uint8_t* blob = e->games.data() + (size_t)game * e->S.P.game_stride;
+    memset(blob, 0, e->S.P.game_stride);
+    return import_blob(blob, hdr5, rows12, n, issue_order, e->S.P.W, e->S.P.H, g_err) ? 0 : -1;
+}
 int hs_export_state(hs_env* e, int game, int32_t* hdr5, int32_t* rows12, int cap_rows) {
     const uint8_t* blob = e->games.data() + (size_t)game * e->S.P.game_stride;
     export_blob(blob, hdr5, rows12, cap_rows);
