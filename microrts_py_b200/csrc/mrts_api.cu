@@ -80,6 +80,11 @@ int env_int(const char* name, int dflt) {
 
 }  // namespace
 
+// error reporting for the other translation units that hold entry points (mrts_expand_static.cu)
+namespace mrts {
+int api_fail(int code, const std::string& msg) { return fail(code, msg); }
+}  // namespace mrts
+
 constexpr int MAX_CHUNKS = 16;
 
 struct mrts_env {
@@ -458,7 +463,7 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
     // Games per block: a block's shared memory and warp slots are only released when its slowest
     // game is done and game times vary widely (scripted-bot path finding), so take the smallest
     // count that still reaches the most resident games per SM.  The bulk mask writer adds one tile of zeros per
-    // block: it is used unless that tile costs more than a twentieth of the resident games (32x32 maps).
+    // block (see the choice below).
     auto choose_gpb = [&](int k, int tile_bytes, int* warps) {
         const int by_regs = 65536 / (32 * (e->regs[k] <= 64 ? 64 : (e->regs[k] <= 96 ? 96 : 128)));
         int best = 1, best_w = 0;
@@ -479,7 +484,13 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
             g_plain[k] = choose_gpb(k, 0, &w_plain[k]);
             g_bulk[k] = choose_gpb(k, 4992, &w_bulk[k]);
         }
-        if (e->bulk_mask < 0) e->bulk_mask = 20 * w_bulk[0] >= 19 * w_plain[0] && 20 * w_bulk[1] >= 19 * w_plain[1] ? 1 : 0;
+        // Measured (profiles/ab_r02_bulk_mask.md): up to 16x16 the bulk writer wins although its tile costs an eighth
+        // of the resident light games (28 of 32 warps); on 32x32 (16 of 18 warps) it loses.  Larger maps keep the
+        // occupancy test.
+        if (e->bulk_mask < 0) {
+            const bool keeps_occupancy = 20 * w_bulk[0] >= 19 * w_plain[0] && 20 * w_bulk[1] >= 19 * w_plain[1];
+            e->bulk_mask = P.HW <= 256 || keeps_occupancy ? 1 : 0;
+        }
         if (e->pipeline != MRTS_PIPELINE_DIRECT) e->bulk_mask = e->bulk_mask > 0 ? 1 : 0;
         for (int k = 0; k < 2; k++) {
             e->gpb[k] = cfg->threads_per_game < 0 ? -cfg->threads_per_game : (e->bulk_mask ? g_bulk[k] : g_plain[k]);
