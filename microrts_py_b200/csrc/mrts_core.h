@@ -332,7 +332,7 @@ struct Sim {
 
     // Unit.canExecuteAction (Unit.java:531-534): is `a` in getUnitActions?  Evaluated directly for the
     // one action instead of enumerating the whole set (unit_mask); tests/test_engine_units.py checks
-    // the two agree on every (unit, action) of sampled states.
+    // (hs_can_execute_disagreements, tests/hostsim/hostsim.cpp) that the two agree on every (unit, action) of sampled states.
     MRTS_HD bool can_execute(int i, const PAct& a) const {
         if (a.type == T_NONE) return true;  // NONE(noneDuration = ETA(a)) is always in the list
         const Unit& un = u[i];

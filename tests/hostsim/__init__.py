@@ -33,6 +33,7 @@ def lib():
         L.hs_unit_capacity.argtypes = [vp]
         L.hs_export_state.argtypes = [vp, C.c_int, vp, vp, C.c_int]
         L.hs_import_state.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
+        L.hs_can_execute_disagreements.argtypes = [vp, C.c_int, C.POINTER(C.c_int64)]
         L.hs_last_error.restype = C.c_char_p
         _lib = L
     return _lib
@@ -94,6 +95,12 @@ class HostSimVecEnv:
         order = np.ascontiguousarray(issue_order, np.int32) if issue_order is not None else None
         if self.L.hs_import_state(self.h, game, _p(hdr5), _p(rows12), len(rows12), _p(order) if order is not None else None):
             raise ValueError(self.L.hs_last_error().decode())
+
+    def can_execute_disagreements(self, game):
+        """(pairs on which Sim::can_execute and Sim::unit_mask disagree, pairs compared) on the stored state of `game`"""
+        n = C.c_int64(0)
+        bad = self.L.hs_can_execute_disagreements(self.h, game, C.byref(n))
+        return bad, n.value
 
     def game_state(self, game):
         cap = self.L.hs_unit_capacity(self.h)

@@ -139,6 +139,47 @@ int hs_import_state(hs_env* e, int game, const int32_t* hdr5, const int32_t* row
     memset(blob, 0, e->S.P.game_stride);
     return import_blob(blob, hdr5, rows12, n, issue_order, e->S.P.W, e->S.P.H, g_err) ? 0 : -1;
 }
+// Sim::can_execute against Sim::unit_mask on the stored state of `game`: every unit x every action the action space can
+// name (NONE; MOVE / HARVEST / RETURN x 4 directions; PRODUCE x 4 directions x 7 types; ATTACK x 49 relative cells).
+// Returns the number of (unit, action) pairs on which the two disagree; *checked = pairs compared.
+int hs_can_execute_disagreements(hs_env* e, int game, int64_t* checked) {
+    EnvParams P = e->S.P;
+    P.game_ai = e->S.game_ai.data();
+    P.game_ai1 = e->S.game_ai1.data();
+    P.scap = P.cap;
+    const Layout L = layout_of(P);
+    std::vector<uint8_t> mem((size_t)L.total + 64, 0);
+    Sim s;
+    bind_sim(s, P, L, mem.data(), game);
+    const uint8_t* blob = e->games.data() + (size_t)game * P.game_stride;
+    memcpy(mem.data() + L.blob, blob, 32 + (size_t)P.cap * 32);
+    const MapTpl tpl = e->S.tpls[e->S.game_map[game]];
+    memcpy(s.grid, e->S.grids.data() + tpl.grid_off, (size_t)P.HW * 2);
+    for (int i = 0; i < s.hdr->nunits; i++) s.grid[s.u[i].x + s.u[i].y * P.W] = (uint16_t)i;
+    int bad = 0;
+    int64_t n = 0;
+    auto cmp = [&](int i, int type, int param, int x, int y, int utype, bool want) {
+        PAct a;
+        a.unit = (uint16_t)i, a.type = (int8_t)type, a.param = (int16_t)param, a.x = (int16_t)x, a.y = (int16_t)y, a.utype = (int8_t)utype, a.pad = 0;
+        n++;
+        if (s.can_execute(i, a) != want) bad++;
+    };
+    for (int i = 0; i < s.hdr->nunits; i++) {
+        const Mask78 m = s.unit_mask(i);
+        const Unit& un = s.u[i];
+        cmp(i, T_NONE, 0, 0, 0, 0, mget(m, MB_TYPE + T_NONE));
+        for (int d = 0; d < 4; d++) {
+            cmp(i, T_MOVE, d, 0, 0, 0, mget(m, MB_MOVE + d));
+            cmp(i, T_HARVEST, d, 0, 0, 0, mget(m, MB_HARVEST + d));
+            cmp(i, T_RETURN, d, 0, 0, 0, mget(m, MB_RETURN + d));
+            for (int k = 0; k < N_UTYPES; k++) cmp(i, T_PRODUCE, d, 0, 0, k, mget(m, MB_TYPE + T_PRODUCE) && mget(m, MB_PDIR + d) && mget(m, MB_PTYPE + k));
+        }
+        for (int dy = -3; dy <= 3; dy++)
+            for (int dx = -3; dx <= 3; dx++) cmp(i, T_ATTACK, 0, un.x + dx, un.y + dy, 0, mget(m, MB_ATTACK + (3 + dy) * 7 + 3 + dx));
+    }
+    if (checked) *checked = n;
+    return bad;
+}
 int hs_export_state(hs_env* e, int game, int32_t* hdr5, int32_t* rows12, int cap_rows) {
     const uint8_t* blob = e->games.data() + (size_t)game * e->S.P.game_stride;
     export_blob(blob, hdr5, rows12, cap_rows);
