@@ -140,6 +140,27 @@ int mrts_reset_packed(mrts_env* env, uint32_t* obs_words, uint32_t* mask_entries
 int mrts_step_packed(mrts_env* env, const mrts_packed_io* io, void* stream);
 int mrts_expand(mrts_env* env, const uint32_t* obs_words, const uint32_t* mask_entries, void* obs, void* mask, void* stream);
 
+/* mrts_expand without an env and without allocating: for code under CUDA graph capture, serving loops and harnesses that
+ * may not call cudaMalloc.  This entry point has NO counterpart in the reference.
+ * The shape that mrts_expand takes from the env comes with the call: n_views views of height x width
+ * cells, mask_entries with 1 + unit_capacity rows per view, 31 planes when partial_obs else 29, element_bytes 4 (int32)
+ * or 1 (uint8).  The CURRENT device is used; all four arrays live on it.  Scratch memory (a work counter and the order in
+ * which views are handed out, heaviest first) is a file-scope __device__ array of MRTS_EXPAND_STATIC_SCRATCH_BYTES that
+ * every GPU loading the library holds until exit; the call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limits and rules:
+ *   - n_views <= MRTS_EXPAND_STATIC_MAX_VIEWS, else MRTS_EINVAL (split the call, or use mrts_expand);
+ *   - H*W*element_bytes a multiple of 16, arrays 16-byte aligned (as mrts_expand);
+ *   - every call on a device shares the one scratch array: calls whose kernels overlap on the GPU (different streams
+ *     with no ordering between them, or two host threads) RACE; calls on one stream, or ordered by events, are safe.
+ *     Each call rewrites the scratch it uses; nothing needs clearing between calls;
+ *   - the first call on a device does the one-time set-up (cudaGetSymbolAddress, kernel attributes): make it outside
+ *     graph capture.
+ * Output is identical to mrts_expand's (tests/test_zz_no_alloc.py). */
+#define MRTS_EXPAND_STATIC_MAX_VIEWS 65536
+#define MRTS_EXPAND_STATIC_SCRATCH_BYTES (256 + 4 * MRTS_EXPAND_STATIC_MAX_VIEWS)
+int mrts_expand_static(const uint32_t* obs_words, const uint32_t* mask_entries, void* obs, void* mask, int n_views, int height, int width,
+                       int unit_capacity, int partial_obs, int element_bytes, void* stream);
+
 /* Host-buffer forms of reset / gameStep + getMasks: every pointer is a HOST pointer (pageable is fine),
  * the call returns when the arrays are filled -- what the reference's NumPy-returning methods do
  * (gym_microrts/envs/vec_env.py:278-282, 968-1061, 1091-1101).  obs (N,H,W,P) and mask (N,H*W,78) have

@@ -212,6 +212,7 @@ SYMBOLS = [
     "mrts_reset_packed",
     "mrts_step_packed",
     "mrts_expand",
+    "mrts_expand_static",
     "mrts_pipeline",
     "mrts_chunks",
     "mrts_kernel_info",
@@ -251,6 +252,7 @@ def lib():
         L.mrts_reset_packed.argtypes = [vp, vp, vp, vp]
         L.mrts_step_packed.argtypes = [vp, C.POINTER(PackedIOC), vp]
         L.mrts_expand.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.mrts_expand_static.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
         L.mrts_pipeline.argtypes = [vp]
         L.mrts_chunks.argtypes = [vp]
         L.mrts_kernel_info.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
