@@ -19,6 +19,7 @@ pre-warmed for `--prewarm` steps of masked-uniform play; the e2e arm and both CP
 The lit_* workloads are the literal BASELINE shapes (N = 2 / N = 24) through the default NumPy API: a latency measurement.
 """
 import argparse
+import ctypes as C
 import hashlib
 import json
 import os
@@ -485,7 +486,12 @@ def e2e_run(args, wl, rank, dist, dev, prewarm):
         if dist is not None:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             world = dist.get_world_size()
-        res = dict(v=k * world * steps / float(t[0].item()), v_loop=k * world * steps / float(t[1].item()), ms=1e3 * float(t[0].item()) / steps,
+        ph = (C.c_double * 8)()
+        env._lib.mrts_host_timing(env._h, ph, 0)
+        calls = max(ph[7], 1.0)
+        phases = {"pack_actions_ms": 1e3 * ph[0] / calls, "h2d_launch_ms": 1e3 * ph[1] / calls, "wait_device_ms": 1e3 * ph[2] / calls, "patch_or_widen_ms": 1e3 * ph[3] / calls,
+                  "copy_out_ms": 1e3 * ph[4] / calls, "changed_cells_per_env_step": ph[5] / calls / k, "d2h_bytes_per_step": ph[6] / calls}
+        res = dict(phases=phases, v=k * world * steps / float(t[0].item()), v_loop=k * world * steps / float(t[1].item()), ms=1e3 * float(t[0].item()) / steps,
                    hw=env.height * env.width, threads=env._lib.mrts_host_threads(env._h), nbytes=int(obs.nbytes + m.nbytes), act=a_host.numel() * 4)
         env.close()
         return res
@@ -496,11 +502,13 @@ def e2e_run(args, wl, rank, dist, dev, prewarm):
     n_dflt = max(2, min(n, int(4e8 // per_env) // 2 * 2))  # fresh arrays: keep the default-mode leg below ~0.4 GB per call
     dflt = run(dict(), max(5, steps // 10), min(prewarm, 20), n_envs=n_dflt)
     hw = slot["hw"]
-    return {"value": slot["v"], "unit": "env-steps/s", "h2d_bytes_per_step": n * hw * 2, "d2h_bytes_per_step": n * hw * 16 + n * 6 * 8 + n, "envs_per_gpu": n, "steps": steps,
+    d2h = int(slot["phases"]["d2h_bytes_per_step"]) or n * hw * 16 + n * 6 * 8 + n
+    return {"value": slot["v"], "unit": "env-steps/s", "h2d_bytes_per_step": n * hw * 2, "d2h_bytes_per_step": d2h, "d2h_bytes_per_step_full_write": n * hw * 16 + n * 6 * 8 + n,
+            "host_phases": slot["phases"], "envs_per_gpu": n, "steps": steps,
             "prewarm_steps": prewarm, "ms_per_step": slot["ms"], "value_incl_policy_copy": slot["v_loop"], "policy_copy_d2h_bytes_per_step": slot["act"],
             "value_full_write": full["v"], "value_default_numpy": dflt["v"], "default_numpy_envs": n_dflt,
             "timed": "step(host actions) + get_action_mask() per step, summed over the steps (max over ranks); the stand-in policy's device sampling and its action-grid copy to the host run between the timed regions, as the reference arm excludes action sampling",
-            "api": "MicroRTSGridModeVecEnv(host_transport=True).step/get_action_mask, NumPy int32 in/out, two alternating result buffers; mrts_step_host_slot moves 1 bit per element over PCIe and %d host threads rewrite the cells of the arrays that changed; value_full_write = mrts_step_host (every element written every step); value_default_numpy = the default mode (fresh arrays, full tensors over PCIe)" % slot["threads"],
+            "api": "MicroRTSGridModeVecEnv(host_transport=True).step/get_action_mask, NumPy int32 in/out, two alternating result buffers; mrts_step_host_slot: the device compares the step's packed words with the slot's shadow in HBM (mrts_delta_kernel) and ONE copy brings count, rewards, dones, the source-cell bitmap and the changed cells to the host, where %d threads rewrite those cells of the arrays; value_full_write = mrts_step_host (every element written every step); value_default_numpy = the default mode (fresh arrays, full tensors over PCIe)" % slot["threads"],
             "result_array_bytes_per_step": slot["nbytes"]}
 
 

@@ -177,7 +177,10 @@ int mrts_step_host(mrts_env* env, const void* actions, int action_elem_bytes, vo
  * library keeps the words it last widened into them and rewrites only the cells whose value changed
  * (between two steps most of a map does not change): the host then writes a few hundred bytes per
  * env-step instead of ~110 KB at 16x16.  First use of a slot, or a different pointer, = full write;
- * slot < 0 = the plain forms above.  mrts_host_forget_slot drops what is remembered about a slot. */
+ * slot < 0 = the plain forms above.  mrts_host_forget_slot drops what is remembered about a slot.
+ * With both arrays given the comparison runs on the DEVICE (csrc/mrts_delta.cu): the slot's words stay in HBM, a
+ * kernel emits the list of cells that differ plus one bit per cell for the source-unit mask, and one copy of a few
+ * tens of KB (count, rewards, dones, bitmap, entries) replaces the 16 bytes per cell of the plain forms. */
 #define MRTS_HOST_SLOTS 4
 int mrts_reset_host_slot(mrts_env* env, void* obs, void* mask, int slot);
 int mrts_step_host_slot(mrts_env* env, const void* actions, int action_elem_bytes, void* obs, void* mask, double* reward, uint8_t* done, int slot);
@@ -191,7 +194,14 @@ int mrts_host_pack_actions(const void* actions, int action_elem_bytes, const uin
 /* the incremental widening alone: `shadow` = the words `out` currently holds the expansion of (updated in place) */
 int mrts_host_expand_obs_delta(const uint32_t* words, uint32_t* shadow, int64_t n_env, int hw, int planes, int elem_bytes, void* out);
 int mrts_host_expand_mask_delta(const uint32_t* mask_words, uint32_t* shadow, int64_t n_env, int hw, int elem_bytes, void* out);
+/* the codec of the device-delta slot calls: action rows picked by a bitmap over the flat cell index (only set cells of `out`
+ * are written), and entries (count, 5) {flat cell, obs word, mask words 0..2} patched into obs (cells, planes) / mask (cells, 78) */
+int mrts_host_pack_actions_bitmap(const void* actions, int action_elem_bytes, const uint32_t* bitmap, int64_t cells, uint16_t* out);
+int mrts_host_patch_cells(const uint32_t* entries, int64_t count, int planes, int elem_bytes, void* obs, void* mask);
 int mrts_host_threads(const mrts_env* env); /* worker threads of the widening pool (0 before the first host call) */
+/* profiling aid: accumulated wall seconds of the host-buffer step calls {pack actions, copy + launch, wait for the device,
+ * widen / patch, copy-out, changed cells, bytes device->host, calls}; reset != 0 clears them */
+int mrts_host_timing(mrts_env* env, double* out8, int reset);
 
 /* Introspection (synchronises the stream). */
 int mrts_num_envs(const mrts_env* env);

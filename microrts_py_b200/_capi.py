@@ -213,6 +213,9 @@ SYMBOLS = [
     "mrts_step_packed",
     "mrts_expand",
     "mrts_expand_static",
+    "mrts_host_timing",
+    "mrts_host_pack_actions_bitmap",
+    "mrts_host_patch_cells",
     "mrts_pipeline",
     "mrts_chunks",
     "mrts_kernel_info",
@@ -268,6 +271,9 @@ def lib():
         L.mrts_host_expand_obs_delta.argtypes = [vp, vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]
         L.mrts_host_expand_mask_delta.argtypes = [vp, vp, C.c_int64, C.c_int, C.c_int, vp]
         L.mrts_host_threads.argtypes = [vp]
+        L.mrts_host_timing.argtypes = [vp, vp, C.c_int]
+        L.mrts_host_pack_actions_bitmap.argtypes = [vp, C.c_int, vp, C.c_int64, vp]
+        L.mrts_host_patch_cells.argtypes = [vp, C.c_int64, C.c_int, C.c_int, vp, vp]
         L.mrts_host_expand_obs.argtypes = [vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]
         L.mrts_host_expand_mask.argtypes = [vp, C.c_int64, C.c_int, C.c_int, vp]
         L.mrts_host_pack_actions.argtypes = [vp, C.c_int, vp, C.c_int64, C.c_int, vp]

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -127,8 +128,18 @@ struct mrts_env {
         // result-array pairs the caller hands back unmodified (mrts_*_host_slot): the words last expanded into them
         struct Slot {
             void *obs = nullptr, *mask = nullptr;
-            std::vector<uint32_t> pobs, pmask;
+            std::vector<uint32_t> pobs, pmask;  // host-side shadows (calls that pass only one of the two arrays)
+            bool on_device = false;             // d_shadow[slot] holds the words expanded into (obs, mask)
         } slots[MRTS_HOST_SLOTS];
+        // delta transport of the slot calls (mrts_delta.cu): ONE device buffer and its pinned mirror
+        //   [header 64 words: word 0 = changed cells | reward N x 6 doubles | done N bytes | bitmap | entries cap x 5 words]
+        // so that a step's results leave with a single copy
+        uint32_t *d_delta = nullptr, *h_delta = nullptr;
+        size_t off_rew = 0, off_done = 0, off_bitmap = 0, off_entries = 0, delta_cap = 0;  // byte offsets; capacity in entries
+        uint32_t* d_shadow[MRTS_HOST_SLOTS] = {nullptr};
+        size_t last_count = 0;
+        bool bitmap_valid = false;  // h_delta's bitmap describes the mask of the current state (else h_pmask does)
+        double t_phase[8] = {0};    // accumulated wall seconds: pack, launch, wait, patch / expand, copy-out; [5] = changed cells, [6] = bytes device->host, [7] = calls
     } hio;
     const uint16_t* cur_pact = nullptr;  // per-launch packed pointers (set by the host / packed entry points)
     uint32_t *cur_pobs = nullptr, *cur_pmask = nullptr, *cur_ment = nullptr;
@@ -571,6 +582,10 @@ void mrts_destroy(mrts_env* e) {
         auto& h = e->hio;
         for (void* p : {(void*)h.h_pact, (void*)h.h_pobs, (void*)h.h_pmask, (void*)h.h_rew, (void*)h.h_done})
             if (p) cudaFreeHost(p);
+        if (h.h_delta) cudaFreeHost(h.h_delta);
+        if (h.d_delta) cudaFree(h.d_delta);
+        for (uint32_t* p : h.d_shadow)
+            if (p) cudaFree(p);
         for (void* p : {(void*)h.d_pact, (void*)h.d_pobs, (void*)h.d_pmask, (void*)h.d_rew, (void*)h.d_done})
             if (p) cudaFree(p);
         if (h.ev_obs) cudaEventDestroy(h.ev_obs);
@@ -703,6 +718,7 @@ static int hostio_finish(mrts_env* e, void* h_obs, void* h_mask, double* h_rewar
     if (h_done) CK(cudaMemcpyAsync(h.h_done, h.d_done, N, cudaMemcpyDeviceToHost, h.stream));
     CK(cudaEventSynchronize(h.ev_obs));
     mrts_env::HostIO::Slot* S = slot >= 0 ? &h.slots[slot] : nullptr;
+    if (S) S->on_device = false;  // this path keeps its shadows on the host: the device shadow no longer matches the arrays
     if (h_obs) {
         if (S && S->obs == h_obs && S->pobs.size() == N * HW) {
             mrts_host::expand_obs_delta(h.pool, h.h_pobs, S->pobs.data(), N, (int)HW, e->P.planes, e->P.elem, h_obs);
@@ -732,6 +748,97 @@ static int hostio_finish(mrts_env* e, void* h_obs, void* h_mask, double* h_rewar
     return MRTS_OK;
 }
 
+static double now_s() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+// buffers of the delta transport: the shared result buffer on first use, one shadow per slot
+static int hostio_delta_init(mrts_env* e, int slot) {
+    auto& h = e->hio;
+    CK(cudaSetDevice(e->device));
+    const size_t N = (size_t)e->N, cells = N * (size_t)e->P.HW;
+    if (!h.d_delta) {
+        auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+        h.off_rew = 256;
+        h.off_done = h.off_rew + up(N * 48);
+        h.off_bitmap = h.off_done + up(N);
+        h.off_entries = h.off_bitmap + up((cells + 31) / 32 * 4);
+        h.delta_cap = cells;  // every cell may change (a reset of all games): the list can never overflow
+        const size_t bytes = h.off_entries + h.delta_cap * 20;
+        CK(cudaMalloc((void**)&h.d_delta, bytes));
+        CK(cudaMallocHost((void**)&h.h_delta, bytes));
+        CK(cudaMemset(h.d_delta, 0, h.off_entries));
+        memset(h.h_delta, 0, h.off_entries);
+    }
+    if (!h.d_shadow[slot]) CK(cudaMalloc((void**)&h.d_shadow[slot], cells * 16));
+    return MRTS_OK;
+}
+
+// Slot form with both arrays given: the device compares this step's words with the slot's shadow and only the cells that
+// differ cross PCIe (one copy: count, rewards, dones, source bitmap, entries); the host pool rewrites those cells.
+// The first call on a slot (or after its arrays changed) expands everything and seeds the shadow.
+static int hostio_finish_slot(mrts_env* e, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done, int slot) {
+    auto& h = e->hio;
+    auto& S = h.slots[slot];
+    const size_t N = (size_t)e->N, HW = (size_t)e->P.HW, cells = N * HW;
+    const bool delta = S.on_device && S.obs == h_obs && S.mask == h_mask;
+    uint8_t* const db = (uint8_t*)h.d_delta;
+    uint8_t* const hb = (uint8_t*)h.h_delta;
+    CK(cudaMemsetAsync(h.d_delta, 0, 256, h.stream));
+    DeltaParams D;
+    D.pobs = h.d_pobs;
+    D.pmask = h.d_pmask;
+    D.shadow = h.d_shadow[slot];
+    D.count = h.d_delta;
+    D.bitmap = (uint32_t*)(db + h.off_bitmap);
+    D.entries = (uint32_t*)(db + h.off_entries);
+    D.cells = (long long)cells;
+    D.cap = (uint32_t)h.delta_cap;
+    D.init = delta ? 0 : 1;
+    CK(launch_delta(D, e->n_sm, h.stream));
+    e->last_launches++;
+    const double t0 = now_s();
+    double t1, t2;
+    if (!delta) {
+        CK(cudaMemcpyAsync(h.h_pobs, h.d_pobs, cells * 4, cudaMemcpyDeviceToHost, h.stream));
+        CK(cudaEventRecord(h.ev_obs, h.stream));
+        CK(cudaMemcpyAsync(h.h_pmask, h.d_pmask, cells * 12, cudaMemcpyDeviceToHost, h.stream));
+        CK(cudaMemcpyAsync(hb, db, h.off_entries, cudaMemcpyDeviceToHost, h.stream));
+        CK(cudaEventSynchronize(h.ev_obs));
+        mrts_host::expand_obs(h.pool, h.h_pobs, N, (int)HW, e->P.planes, e->P.elem, h_obs);
+        CK(cudaStreamSynchronize(h.stream));
+        t1 = now_s();
+        mrts_host::expand_mask(h.pool, h.h_pmask, N, (int)HW, e->P.elem, h_mask);
+        S.obs = h_obs, S.mask = h_mask, S.on_device = true;
+        S.pobs.clear(), S.pmask.clear();
+        t2 = now_s();
+    } else {
+        size_t guess = 2 * h.last_count > 4096 ? 2 * h.last_count : 4096;
+        if (guess > h.delta_cap) guess = h.delta_cap;
+        CK(cudaMemcpyAsync(hb, db, h.off_entries + guess * 20, cudaMemcpyDeviceToHost, h.stream));
+        CK(cudaStreamSynchronize(h.stream));
+        const size_t count = h.h_delta[0];
+        if (count > h.delta_cap) return fail(MRTS_ECUDA, "delta list overflow");
+        if (count > guess) {
+            CK(cudaMemcpyAsync(hb + h.off_entries + guess * 20, db + h.off_entries + guess * 20, (count - guess) * 20, cudaMemcpyDeviceToHost, h.stream));
+            CK(cudaStreamSynchronize(h.stream));
+        }
+        t1 = now_s();
+        mrts_host::patch_cells(h.pool, (const uint32_t*)(hb + h.off_entries), count, e->P.planes, e->P.elem, h_obs, h_mask);
+        h.last_count = count;
+        h.t_phase[5] += (double)count, h.t_phase[6] += (double)(h.off_entries + (count > guess ? count : guess) * 20);
+        t2 = now_s();
+    }
+    h.have_mask = true;
+    h.bitmap_valid = true;
+    if (h_reward) memcpy(h_reward, hb + h.off_rew, N * 48);
+    if (h_done) memcpy(h_done, hb + h.off_done, N);
+    h.t_phase[2] += t1 - t0, h.t_phase[3] += t2 - t1, h.t_phase[4] += now_s() - t2;
+    return MRTS_OK;
+}
+
 int mrts_reset_host(mrts_env* e, void* h_obs, void* h_mask) { return mrts_reset_host_slot(e, h_obs, h_mask, -1); }
 int mrts_step_host(mrts_env* e, const void* h_actions, int action_elem_bytes, void* h_obs, void* h_mask, double* h_reward, uint8_t* h_done) {
     return mrts_step_host_slot(e, h_actions, action_elem_bytes, h_obs, h_mask, h_reward, h_done, -1);
@@ -749,8 +856,12 @@ int mrts_reset_host_slot(mrts_env* e, void* h_obs, void* h_mask, int slot) {
     if (rc) return rc;
     e->cur_pobs = e->hio.d_pobs;
     e->cur_pmask = e->hio.d_pmask;
+    const bool slot_path = slot >= 0 && h_obs && h_mask;
+    if (slot_path && (rc = hostio_delta_init(e, slot))) return rc;
     rc = launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, e->hio.stream);
     if (rc) return rc;
+    if (slot_path) return hostio_finish_slot(e, h_obs, h_mask, nullptr, nullptr, slot);
+    e->hio.bitmap_valid = false;
     return hostio_finish(e, h_obs, h_mask, nullptr, nullptr, slot);
 }
 
@@ -770,14 +881,24 @@ int mrts_step_host_slot(mrts_env* e, const void* h_actions, int action_elem_byte
         rc = hostio_finish(e, nullptr, nullptr, nullptr, nullptr);
         if (rc) return rc;
     }
-    mrts_host::pack_actions(h.pool, h_actions, action_elem_bytes, h.h_pmask, N, (int)HW, h.h_pact);
+    const bool slot_path = slot >= 0 && h_obs && h_mask;
+    if (slot_path && (rc = hostio_delta_init(e, slot))) return rc;
+    const double t0 = now_s();
+    if (h.bitmap_valid) mrts_host::pack_actions_bitmap(h.pool, h_actions, action_elem_bytes, (const uint32_t*)((const uint8_t*)h.h_delta + h.off_bitmap), N * HW, h.h_pact);
+    else mrts_host::pack_actions(h.pool, h_actions, action_elem_bytes, h.h_pmask, N, (int)HW, h.h_pact);
+    const double t1 = now_s();
     CK(cudaMemcpyAsync(h.d_pact, h.h_pact, N * HW * 2, cudaMemcpyHostToDevice, h.stream));
     e->cur_pact = h.d_pact;
     e->cur_pobs = h.d_pobs;
     e->cur_pmask = h.d_pmask;
+    double* const d_rew = slot_path ? (double*)((uint8_t*)h.d_delta + h.off_rew) : h.d_rew;
+    uint8_t* const d_done = slot_path ? (uint8_t*)h.d_delta + h.off_done : h.d_done;
     // `actions` is unused when the packed rows are given; pass a valid non-null pointer for the argument check
-    rc = launch(e, MODE_STEP, (const int32_t*)h.d_pact, nullptr, nullptr, h.d_rew, h.d_done, h.stream);
+    rc = launch(e, MODE_STEP, (const int32_t*)h.d_pact, nullptr, nullptr, d_rew, d_done, h.stream);
     if (rc) return rc;
+    h.t_phase[0] += t1 - t0, h.t_phase[1] += now_s() - t1, h.t_phase[7] += 1;
+    if (slot_path) return hostio_finish_slot(e, h_obs, h_mask, h_reward, h_done, slot);
+    h.bitmap_valid = false;
     return hostio_finish(e, h_obs, h_mask, h_reward, h_done, slot);
 }
 
@@ -820,6 +941,27 @@ int mrts_host_pack_actions(const void* actions, int action_elem_bytes, const uin
     mrts_host::Pool* p = mrts_host::pool_create(0);
     mrts_host::pack_actions(p, actions, action_elem_bytes, mask_words, (size_t)n_env, hw, out);
     mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
+int mrts_host_pack_actions_bitmap(const void* actions, int action_elem_bytes, const uint32_t* bitmap, int64_t cells, uint16_t* out) {
+    if (!actions || !bitmap || !out || cells < 0 || (action_elem_bytes != 4 && action_elem_bytes != 8)) return fail(MRTS_EINVAL, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    mrts_host::pack_actions_bitmap(p, actions, action_elem_bytes, bitmap, (size_t)cells, out);
+    mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
+int mrts_host_patch_cells(const uint32_t* entries, int64_t count, int planes, int elem_bytes, void* obs, void* mask) {
+    if (!entries || count < 0 || (elem_bytes != 4 && elem_bytes != 1) || planes < 1 || planes > 31) return fail(MRTS_EINVAL, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    mrts_host::patch_cells(p, entries, (size_t)count, planes, elem_bytes, obs, mask);
+    mrts_host::pool_destroy(p);
+    return MRTS_OK;
+}
+int mrts_host_timing(mrts_env* e, double* out8, int reset) {
+    if (!e || !out8) return fail(MRTS_EINVAL, "null argument");
+    for (int k = 0; k < 8; k++) out8[k] = e->hio.t_phase[k];
+    if (reset)
+        for (double& t : e->hio.t_phase) t = 0;
     return MRTS_OK;
 }
 int mrts_host_threads(const mrts_env* e) { return e && e->hio.pool ? mrts_host::pool_threads(e->hio.pool) : 0; }

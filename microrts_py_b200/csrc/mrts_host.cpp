@@ -5,6 +5,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <time.h>
+
+#include <atomic>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -16,39 +19,60 @@
 #endif
 
 namespace mrts_host {
+#if defined(__x86_64__)
+static void mask_row_avx2_32(const uint32_t* pm, int32_t* o);  // defined with the incremental forms below
+#endif
 
 // ------------------------------------------------------------------------------------------------
+// Workers SPIN for a short while after a job (MRTS_HOST_SPIN_US, default 300) before they block on the condition
+// variable: a host-buffer step runs two short jobs ~0.2 ms apart (pack the actions, patch the results) and a
+// futex wake-up of every worker cost as much as the jobs themselves.  The pool never has more threads than
+// the cores this rank may use (mrts_api.cu: visible cores / LOCAL_WORLD_SIZE), so the spinning starves nobody.
 struct Pool {
     std::vector<std::thread> workers;
     std::mutex mu;
-    std::condition_variable cv_work, cv_done;
+    std::condition_variable cv_work;
     std::function<void(size_t, size_t)> fn;
     size_t n = 0;
-    int generation = 0, pending = 0;
-    bool stop = false;
+    std::atomic<int> generation{0}, pending{0}, sleepers{0};
+    std::atomic<bool> stop{false};
     int nthreads = 1;
+    long spin_ns = 300000;
 };
+
+static inline void cpu_relax() {
+#if defined(__x86_64__)
+    _mm_pause();
+#endif
+}
+static inline long mono_ns() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1000000000L + ts.tv_nsec;
+}
 
 static void worker_main(Pool* p, int rank) {
     int seen = 0;
     for (;;) {
-        std::function<void(size_t, size_t)> fn;
-        size_t n;
-        {
-            std::unique_lock<std::mutex> lk(p->mu);
-            p->cv_work.wait(lk, [&] { return p->stop || p->generation != seen; });
-            if (p->stop) return;
-            seen = p->generation;
-            fn = p->fn;
-            n = p->n;
+        long t0 = mono_ns();
+        int spins = 0;
+        while (p->generation.load() == seen && !p->stop.load()) {
+            cpu_relax();
+            if ((++spins & 255) == 0 && mono_ns() - t0 > p->spin_ns) {
+                std::unique_lock<std::mutex> lk(p->mu);
+                p->sleepers.fetch_add(1);
+                p->cv_work.wait(lk, [&] { return p->stop.load() || p->generation.load() != seen; });
+                p->sleepers.fetch_sub(1);
+                break;
+            }
         }
+        if (p->stop.load()) return;
+        seen = p->generation.load();
+        const size_t n = p->n;
         const size_t per = (n + p->nthreads - 1) / p->nthreads;
         const size_t b = per * rank, e = b + per < n ? b + per : n;
-        if (b < e) fn(b, e);
-        {
-            std::lock_guard<std::mutex> lk(p->mu);
-            if (--p->pending == 0) p->cv_done.notify_all();
-        }
+        if (b < e) p->fn(b, e);
+        p->pending.fetch_sub(1);
     }
 }
 
@@ -63,6 +87,7 @@ Pool* pool_create(int threads) {
     if (threads <= 0) threads = visible_cores();
     Pool* p = new Pool();
     p->nthreads = threads;
+    if (const char* v = getenv("MRTS_HOST_SPIN_US")) p->spin_ns = atol(v) * 1000L;
     for (int r = 1; r < threads; r++) p->workers.emplace_back(worker_main, p, r);  // rank 0 = the caller
     return p;
 }
@@ -70,7 +95,7 @@ void pool_destroy(Pool* p) {
     if (!p) return;
     {
         std::lock_guard<std::mutex> lk(p->mu);
-        p->stop = true;
+        p->stop.store(true);
     }
     p->cv_work.notify_all();
     for (auto& t : p->workers) t.join();
@@ -83,18 +108,21 @@ static void parallel_for(Pool* p, size_t n, const std::function<void(size_t, siz
         fn(0, n);
         return;
     }
-    {
+    p->fn = fn;
+    p->n = n;
+    p->pending.store((int)p->workers.size());
+    p->generation.fetch_add(1);  // publishes fn / n (sequentially consistent, as is the sleepers test below)
+    if (p->sleepers.load() > 0) {
         std::lock_guard<std::mutex> lk(p->mu);
-        p->fn = fn;
-        p->n = n;
-        p->pending = (int)p->workers.size();
-        p->generation++;
+        p->cv_work.notify_all();
     }
-    p->cv_work.notify_all();
     const size_t per = (n + p->nthreads - 1) / p->nthreads;
     if (per > 0) fn(0, per < n ? per : n);
-    std::unique_lock<std::mutex> lk(p->mu);
-    p->cv_done.wait(lk, [&] { return p->pending == 0; });
+    int spins = 0;
+    while (p->pending.load() != 0) {
+        cpu_relax();
+        if ((++spins & 4095) == 0) sched_yield();
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -222,6 +250,12 @@ void expand_mask(Pool* p, const uint32_t* pmask, size_t n_env, int hw, int elem,
             for (int c = 0; c < hw; c++) {
                 const uint32_t m0 = pm[3 * c], m1 = pm[3 * c + 1], m2 = pm[3 * c + 2];
                 if ((m0 | m1 | m2) == 0) continue;
+#if defined(__x86_64__)
+                if (elem == 4 && has_avx2()) {
+                    mask_row_avx2_32(pm + 3 * c, (int32_t*)o + (size_t)c * 78);
+                    continue;
+                }
+#endif
                 for (int k = 0; k < 78; k++) {
                     const uint32_t word = k < 32 ? m0 : (k < 64 ? m1 : m2);
                     const uint32_t bit = (word >> (k & 31)) & 1u;
@@ -263,6 +297,15 @@ __attribute__((target("avx2"))) static inline void obs_cell_avx2_32(uint32_t w, 
     _mm256_storeu_si256((__m256i*)(o + 8), _mm256_and_si256(_mm256_srlv_epi32(v, _mm256_add_epi32(s0, _mm256_set1_epi32(8))), one));
     _mm256_storeu_si256((__m256i*)(o + 16), _mm256_and_si256(_mm256_srlv_epi32(v, _mm256_add_epi32(s0, _mm256_set1_epi32(16))), one));
     _mm256_storeu_si256((__m256i*)(o + planes - 8), _mm256_and_si256(_mm256_srlv_epi32(v, _mm256_add_epi32(s0, _mm256_set1_epi32(planes - 8))), one));
+}
+// one mask row, int32: nine aligned-to-row stores of 8 elements and one overlapping the tail (elements 70..77)
+__attribute__((target("avx2"))) static inline void mask_cell_avx2_32(const uint32_t* pm, int32_t* o) {
+    const __m256i one = _mm256_set1_epi32(1), s0 = _mm256_setr_epi32(0, 1, 2, 3, 4, 5, 6, 7);
+    for (int k = 0; k < 9; k++) {
+        const uint32_t chunk = (pm[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
+        _mm256_storeu_si256((__m256i*)(o + 8 * k), _mm256_and_si256(_mm256_srlv_epi32(_mm256_set1_epi32((int)chunk), s0), one));
+    }
+    _mm256_storeu_si256((__m256i*)(o + 70), _mm256_and_si256(_mm256_srlv_epi32(_mm256_set1_epi32((int)(pm[2] >> 6)), s0), one));
 }
 __attribute__((target("avx2"))) static void obs_delta_avx2(const uint32_t* w, uint32_t* sh, size_t cells, int planes, int elem, uint8_t* out) {
     const size_t cell_bytes = (size_t)planes * elem;
@@ -312,6 +355,10 @@ __attribute__((target("avx2"))) static void mask_delta_avx2(const uint32_t* pm, 
         mask_cell(n, elem, out + c * cell_bytes);
     }
 }
+#endif
+
+#if defined(__x86_64__)
+__attribute__((target("avx2"))) static void mask_row_avx2_32(const uint32_t* pm, int32_t* o) { mask_cell_avx2_32(pm, o); }
 #endif
 
 void expand_obs_delta(Pool* p, const uint32_t* words, uint32_t* shadow, size_t n_env, int hw, int planes, int elem, void* out) {
@@ -384,6 +431,84 @@ void pack_actions(Pool* p, const void* actions, int action_elem, const uint32_t*
                 }
                 const size_t row = (env * (size_t)hw + c) * 7;
                 o[c] = action_elem == 8 ? pack_row((const int64_t*)actions + row) : pack_row((const int32_t*)actions + row);
+            }
+        }
+    });
+}
+
+// Both loops below touch a few scattered cache lines per item of a large array: the addresses of a small batch are
+// computed and prefetched first so that the misses overlap instead of queueing behind one another.
+void pack_actions_bitmap(Pool* p, const void* actions, int action_elem, const uint32_t* bitmap, size_t cells, uint16_t* out) {
+    const size_t nwords = (cells + 31) / 32;
+    parallel_for(p, nwords, [=](size_t b, size_t e) {
+        constexpr int BATCH = 64;
+        size_t idx[BATCH + 32];
+        const size_t row_bytes = (size_t)7 * action_elem;
+        size_t i = b;
+        while (i < e) {
+            int k = 0;
+            while (i < e && k < BATCH) {
+                uint32_t bits = bitmap[i];
+                while (bits) {
+                    const size_t g = i * 32 + (size_t)__builtin_ctz(bits);
+                    bits &= bits - 1;
+                    if (g < cells) idx[k++] = g;
+                }
+                i++;
+            }
+            for (int j = 0; j < k; j++) {
+                const char* row = (const char*)actions + idx[j] * row_bytes;
+                __builtin_prefetch(row, 0, 0);
+                __builtin_prefetch(row + row_bytes - 1, 0, 0);
+            }
+            for (int j = 0; j < k; j++) {
+                const size_t g = idx[j];
+                out[g] = action_elem == 8 ? pack_row((const int64_t*)actions + g * 7) : pack_row((const int32_t*)actions + g * 7);
+            }
+        }
+    });
+}
+
+void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int elem, void* obs, void* mask) {
+    parallel_for(p, count, [=](size_t b, size_t e) {
+        const size_t obs_cell_bytes = (size_t)planes * elem, mask_cell_bytes = (size_t)78 * elem;
+        constexpr size_t AHEAD = 6;
+#if defined(__x86_64__)
+        const bool wide = has_avx2() && elem == 4 && planes >= 24 && planes <= 32;
+#endif
+        auto prefetch = [&](size_t i) {
+            const size_t g = entries[5 * i];
+            if (obs) {
+                const char* o = (const char*)obs + g * obs_cell_bytes;
+                for (size_t k = 0; k < obs_cell_bytes; k += 64) __builtin_prefetch(o + k, 1, 0);
+                __builtin_prefetch(o + obs_cell_bytes - 1, 1, 0);
+            }
+            if (mask) {
+                const char* m = (const char*)mask + g * mask_cell_bytes;
+                for (size_t k = 0; k < mask_cell_bytes; k += 64) __builtin_prefetch(m + k, 1, 0);
+                __builtin_prefetch(m + mask_cell_bytes - 1, 1, 0);
+            }
+        };
+        for (size_t i = b; i < e && i < b + AHEAD; i++) prefetch(i);
+        for (size_t i = b; i < e; i++) {
+            if (i + AHEAD < e) prefetch(i + AHEAD);
+            const uint32_t* en = entries + 5 * i;
+            const size_t g = en[0];
+            if (obs) {
+                uint8_t* o = (uint8_t*)obs + g * obs_cell_bytes;
+#if defined(__x86_64__)
+                if (wide) obs_cell_avx2_32(en[1], planes, (int32_t*)o);
+                else
+#endif
+                    obs_cell(en[1], planes, elem, o);
+            }
+            if (mask) {
+                uint8_t* m = (uint8_t*)mask + g * mask_cell_bytes;
+#if defined(__x86_64__)
+                if (has_avx2() && elem == 4 && (en[2] | en[3] | en[4])) mask_cell_avx2_32(en + 2, (int32_t*)m);
+                else
+#endif
+                    mask_cell(en + 2, elem, m);
             }
         }
     });

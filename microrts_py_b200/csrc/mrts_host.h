@@ -35,4 +35,11 @@ void expand_mask_delta(Pool* p, const uint32_t* pmask, uint32_t* shadow, size_t 
 // (the mask the caller was given for this state) are non-zero; other cells 0
 void pack_actions(Pool* p, const void* actions, int action_elem /* 4 or 8 */, const uint32_t* pmask, size_t n_env, int hw, uint16_t* out);
 
+// The same with the source cells given as a bitmap over the flat cell index (bit = mask bit 0, mrts_delta.cu): only the
+// rows of set bits are read and only those cells of `out` are written (the device reads no other cell).
+void pack_actions_bitmap(Pool* p, const void* actions, int action_elem, const uint32_t* bitmap, size_t cells, uint16_t* out);
+// entries (count, 5) {flat cell, obs word, mask words 0..2} -> those cells of obs (cells, planes) and mask (cells, 78);
+// every cell appears at most once, either array may be null
+void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int elem, void* obs, void* mask);
+
 }  // namespace mrts_host

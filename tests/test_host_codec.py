@@ -111,3 +111,47 @@ def test_incremental_widening_tracks_a_changing_state(hw, planes, dtype):
         bits = np.concatenate([(pm[:, :, j : j + 1] >> np.arange(32, dtype=np.uint32)) & 1 for j in range(3)], axis=2)[:, :, :78]
         np.testing.assert_array_equal(out_m, bits.astype(dtype))
         assert not buf_o[0] and not buf_o[1 + n * hw * planes :].any() and not buf_m[0] and not buf_m[1 + n * hw * 78 :].any()
+
+
+@pytest.mark.parametrize("dtype", [np.int32, np.int64])
+def test_action_rows_pack_by_bitmap_touch_only_set_cells(dtype):
+    """the device-delta slot path: source cells come as one bit per flat cell (csrc/mrts_delta.cu)"""
+    L = _capi.lib()
+    rng = np.random.default_rng(12)
+    cells = 23 * 70 + 5  # not a multiple of 32
+    a = rng.integers(-2, 9, size=(cells, 7)).astype(dtype)
+    a[:, 6] = rng.integers(-3, 60, size=cells)
+    src = rng.random(cells) < 0.2
+    bits = np.zeros((cells + 31) // 32 * 32, np.uint8)
+    bits[:cells] = src
+    bitmap = np.packbits(bits.reshape(-1, 32), axis=1, bitorder="little").view(np.uint32).reshape(-1)
+    out = np.full(cells, 0xABCD, np.uint16)
+    _capi.check(L.mrts_host_pack_actions_bitmap(_p(a), np.dtype(dtype).itemsize, _p(bitmap), cells, _p(out)))
+    want = np.full(cells, 0xABCD, np.uint16)
+    for c in np.nonzero(src)[0]:
+        want[c] = _pack_ref(a[c])
+    np.testing.assert_array_equal(out, want)
+
+
+@pytest.mark.parametrize("planes,dtype", [(29, np.int32), (31, np.int32), (29, np.uint8), (31, np.uint8)])
+def test_entries_patch_exactly_their_cells(planes, dtype):
+    L = _capi.lib()
+    rng = np.random.default_rng(planes)
+    cells = 4000
+    obs = rng.integers(0, 2, size=(cells, planes)).astype(dtype)
+    mask = rng.integers(0, 2, size=(cells, 78)).astype(dtype)
+    want_obs, want_mask = obs.copy(), mask.copy()
+    picked = rng.choice(cells, size=700, replace=False)
+    ent = np.zeros((700, 5), np.uint32)
+    ent[:, 0] = picked
+    ent[:, 1] = rng.integers(0, 2 ** planes, size=700, dtype=np.uint64)
+    ent[:, 2:4] = rng.integers(0, 2 ** 32, size=(700, 2), dtype=np.uint64)
+    ent[:, 4] = rng.integers(0, 2 ** 14, size=700, dtype=np.uint64)
+    ent[::9, 2:] = 0  # all-zero rows take the memset branch
+    want_obs[picked] = ((ent[:, 1, None] >> np.arange(planes, dtype=np.uint32)) & 1).astype(dtype)
+    k = np.arange(78)
+    want_mask[picked] = ((ent[:, 2 + k // 32] >> (k % 32).astype(np.uint32)) & 1).astype(dtype)
+    _capi.check(L.mrts_host_patch_cells(_p(ent), 700, planes, np.dtype(dtype).itemsize, _p(obs), _p(mask)))
+    np.testing.assert_array_equal(obs, want_obs)
+    np.testing.assert_array_equal(mask, want_mask)
+    _capi.check(L.mrts_host_patch_cells(_p(ent), 700, planes, np.dtype(dtype).itemsize, _p(obs), None))  # either array may be null

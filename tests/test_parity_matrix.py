@@ -110,6 +110,11 @@ MATRIX = {
     "i32_odd15x14_split_falls_back": (2, [W, LR, P], MAP_ODD, False, 200, 500, 0.05, dict(pipeline="split")),
     "u8_odd15x14_partial": (2, [W, P], MAP_ODD, True, 200, 400, 0.05, dict(dtype=np.uint8)),
     "i32_9x8_split": (2, [W, LR], MAP_9x8, False, 150, 400, 0.05, dict(pipeline="split", chunks=2)),
+    # (d) host-buffer transport with result-buffer slots: device-side delta compaction (mrts_delta_kernel) + host patching;
+    # 5 x 210 cells is not a multiple of 32 (partial bitmap word), resets rewrite whole maps
+    "host_i32_odd15x14": (2, [W, LR, P], MAP_ODD, False, 200, 500, 0.05, dict(host_transport=True)),
+    "host_u8_p31_8x8": (4, [W, LR, P], MAP_8, True, 150, 500, 0.08, dict(dtype=np.uint8, host_transport=True)),
+    "host_i32_p31_32x32": (2, [W, POL], MAP_32, True, 200, 300, 0.05, dict(host_transport=True)),
     "u8_9x8_split_falls_back": (2, [W, LR], MAP_9x8, True, 150, 400, 0.05, dict(dtype=np.uint8, pipeline="split")),
     "u8_10x10": (4, [W, LR], MAP_10, False, 200, 450, 0.05, dict(dtype=np.uint8)),
 }

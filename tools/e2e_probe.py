@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Where an end-to-end step (bench.py e2e loop) spends its time: policy stand-in, its action grid
 device->host, env.step (mrts_step_host_slot).  Usage: python tools/e2e_probe.py [workload] [envs]"""
+import ctypes as C
 import os
 import sys
 import time
@@ -27,6 +28,8 @@ K = 40
 for it in range(K + 5):
     if it == 5:
         T = dict.fromkeys(T, 0.0)
+        ph = (C.c_double * 8)()
+        env._lib.mrts_host_timing(env._h, ph, 1)
     t0 = time.perf_counter()
     a = env.sample_actions()
     torch.cuda.synchronize()
@@ -42,3 +45,9 @@ for it in range(K + 5):
     T["step"] += t3 - t2
 tot = sum(T.values())
 print(f"{name} {n} envs: " + " | ".join(f"{k} {1e3 * v / K:.2f} ms" for k, v in T.items()) + f" | total {1e3 * tot / K:.2f} ms = {n * K / tot / 1e6:.2f} M env-steps/s")
+ph = (C.c_double * 8)()
+env._lib.mrts_host_timing(env._h, ph, 0)
+calls = max(ph[7], 1)
+names = ["pack actions", "h2d + launch", "wait device", "patch / widen", "copy-out"]
+print("  inside mrts_step_host_slot (%d threads): " % env._lib.mrts_host_threads(env._h) + " | ".join(f"{k} {1e3 * ph[i] / calls:.3f} ms" for i, k in enumerate(names))
+      + f" | {ph[5] / calls / n:.2f} changed cells/env, {ph[6] / calls / 1e6:.2f} MB d2h" + f" | env.step total {1e3 * T['step'] / K:.3f} ms = {n * K / T['step'] / 1e6:.2f} M env-steps/s")
