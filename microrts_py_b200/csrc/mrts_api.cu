@@ -113,6 +113,10 @@ struct mrts_env {
     int32_t* d_ovf_list = nullptr;
     uint32_t *d_pobs = nullptr, *d_ment = nullptr;  // packed outputs of the split pipeline
     cudaStream_t s_rules[2] = {nullptr, nullptr}, s_exp = nullptr;
+    // direct pipeline with both game classes: the light (bandwidth-bound) launch runs on its own low-priority stream
+    // beside the heavy (latency-bound) one instead of behind its tail
+    cudaStream_t s_light = nullptr;
+    cudaEvent_t ev_lfork = nullptr, ev_ljoin = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_rules[MAX_CHUNKS] = {nullptr};
     long long* d_timing = nullptr;  // profiling aid (mrts_debug_timing)
     // ---- host-buffer entry points (mrts_reset_host / mrts_step_host): packed transport, see mrts_host.h
@@ -156,6 +160,7 @@ struct mrts_env {
     int rows_cap = 0;
     uint32_t sample_counter = 0;
     int last_launches = 0;  // kernels enqueued by the last launch()
+    int diag_skip = 0;      // MRTS_DIAG_SKIP bits: 1 / 2 = heavy games write no mask / obs, 4 / 8 = light games (timing experiments only)
     int bulk_mask = 1;      // direct mode: the mask takes the bulk writer (MRTS_BULK_MASK overrides, tuning)
 };
 
@@ -280,11 +285,19 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
                 Q.order_next = ord_next + Q.game0;
                 Q.order_cnt_next = cnt_next + 4 * q;
             }
+            const bool beside = e->s_light && !fork && e->chunk_nheavy[q] > 0 && e->chunk_nlight[q] > 0;
+            const cudaStream_t sl = beside ? e->s_light : sr;
+            if (beside) {
+                CK(cudaEventRecord(e->ev_lfork, sr));  // behind the counter memset and everything earlier on the caller's stream
+                CK(cudaStreamWaitEvent(sl, e->ev_lfork, 0));
+            }
             if (e->chunk_nheavy[q] > 0) {
                 EnvParams H = Q;
                 H.order = ord_cur + Q.game0;
                 H.order_cnt = cnt_cur + 4 * q;
                 H.nslots = e->chunk_nheavy[q];
+                if (e->diag_skip & 1) H.mask = nullptr, H.bulk_out = 0;  // diagnostics only (MRTS_DIAG_SKIP): outputs are then incomplete
+                if (e->diag_skip & 2) H.obs = nullptr;
                 if (warp) CK(launch_rules_warp(1, e->regs[1], H, e->gpb[1], e->smem[1], sr));
                 else CK(launch_rules_block(1, H, e->threads, e->smem_block, sr));
                 launches++;
@@ -295,9 +308,15 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
                 L.order = e->d_light + e->chunk_light_off[q];
                 L.order_cnt = nullptr;
                 L.nslots = e->chunk_nlight[q];
-                if (warp) CK(launch_rules_warp(0, e->regs[0], L, e->gpb[0], e->smem[0], sr));
-                else CK(launch_rules_block(0, L, e->threads, e->smem_block, sr));
+                if (e->diag_skip & 4) L.mask = nullptr, L.bulk_out = 0;
+                if (e->diag_skip & 8) L.obs = nullptr;
+                if (warp) CK(launch_rules_warp(0, e->regs[0], L, e->gpb[0], e->smem[0], sl));
+                else CK(launch_rules_block(0, L, e->threads, e->smem_block, sl));
                 launches++;
+            }
+            if (beside) {
+                CK(cudaEventRecord(e->ev_ljoin, sl));
+                CK(cudaStreamWaitEvent(sr, e->ev_ljoin, 0));
             }
             if (defer) {
                 EnvParams F = Q;  // full-capacity parameters of the overflow launch
@@ -468,15 +487,15 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
     if (e->pipeline == 0) e->pipeline = MRTS_PIPELINE_DIRECT;  // measured faster than SPLIT on every BASELINE config
     e->bulk_mask = env_int("MRTS_BULK_MASK", -1);  // 1 / 0 = force the bulk mask writer on / off; -1 = choose below
     // Register budget: light games (self-play, PassiveAI) fit 64 registers without spills -> 32 warps per SM;
-    // the scripted-bot kernels take 96.
+    // the scripted-bot kernels take 80 (44 bytes of spills; 25 instead of 21 resident warps: measured +7 % on WorkerRush).
     e->regs[0] = env_int("MRTS_REGS_LIGHT", 64);
-    e->regs[1] = env_int("MRTS_REGS_HEAVY", 96);
+    e->regs[1] = env_int("MRTS_REGS_HEAVY", 80);
     // Games per block: a block's shared memory and warp slots are only released when its slowest
     // game is done and game times vary widely (scripted-bot path finding), so take the smallest
     // count that still reaches the most resident games per SM.  The bulk mask writer adds one tile of zeros per
     // block (see the choice below).
     auto choose_gpb = [&](int k, int tile_bytes, int* warps) {
-        const int by_regs = 65536 / (32 * (e->regs[k] <= 64 ? 64 : (e->regs[k] <= 96 ? 96 : 128)));
+        const int by_regs = 65536 / (32 * (e->regs[k] <= 64 ? 64 : (e->regs[k] <= 80 ? 80 : (e->regs[k] <= 96 ? 96 : 128))));
         int best = 1, best_w = 0;
         for (int g = 1; g <= GPB_MAX; g *= 2) {
             if (g * e->smem[k] + tile_bytes > maxsm) break;
@@ -565,6 +584,18 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
             for (int q = 0; q < K; q++) CREATE_CK(cudaEventCreateWithFlags(&e->ev_rules[q], cudaEventDisableTiming));
         }
     }
+    e->diag_skip = env_int("MRTS_DIAG_SKIP", 0);
+    if (env_int("MRTS_OVERLAP", 1)) {
+        bool both = false;
+        for (int q = 0; q < K; q++) both = both || (e->chunk_nheavy[q] > 0 && e->chunk_nlight[q] > 0);
+        if (both) {
+            int lo = 0, hi = 0;
+            CREATE_CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            CREATE_CK(cudaStreamCreateWithPriority(&e->s_light, cudaStreamNonBlocking, lo));
+            CREATE_CK(cudaEventCreateWithFlags(&e->ev_lfork, cudaEventDisableTiming));
+            CREATE_CK(cudaEventCreateWithFlags(&e->ev_ljoin, cudaEventDisableTiming));
+        }
+    }
     // start every game from its template so that the state is defined before the first reset()
     CREATE_RC(launch(e, MODE_RESET, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr));
     CREATE_CK(cudaDeviceSynchronize());
@@ -597,7 +628,9 @@ void mrts_destroy(mrts_env* e) {
         if (ev) cudaEventDestroy(ev);
     for (cudaEvent_t ev : e->ev_rules)
         if (ev) cudaEventDestroy(ev);
-    for (cudaStream_t s : {e->s_rules[0], e->s_rules[1], e->s_exp})
+    for (cudaEvent_t ev : {e->ev_lfork, e->ev_ljoin})
+        if (ev) cudaEventDestroy(ev);
+    for (cudaStream_t s : {e->s_rules[0], e->s_rules[1], e->s_exp, e->s_light})
         if (s) cudaStreamDestroy(s);
     for (void* p : e->allocs) cudaFree(p);
     if (e->d_rows) cudaFree(e->d_rows);

@@ -28,7 +28,7 @@ __device__ __forceinline__ int slot_game(const EnvParams& P, int slot) {
     return P.order[(size_t)c * P.order_stride + k];
 }
 
-// MINB = resident 128-thread blocks per SM the register budget must allow: 8 -> 64 registers, 5 -> 96, 4 -> 128
+// MINB = resident 128-thread blocks per SM the register budget must allow: 8 -> 64 registers, 6 -> 80, 5 -> 96, 4 -> 128
 template <int HEAVY, int MINB>
 __global__ void __launch_bounds__(32 * GPB_MAX, MINB) mrts_rules_warp_kernel(const __grid_constant__ EnvParams P, const int smem_per_game) {
     extern __shared__ uint4 smem_raw[];
@@ -55,6 +55,7 @@ static cudaError_t launch_warp_t(int regs, const EnvParams& P, int gpb, int smem
     const dim3 grid((P.nslots + gpb - 1) / gpb);
     const int smem = gpb * smem_per_game + (P.bulk_out ? BULK_TILES_BYTES : 0);
     if (regs <= 64) mrts_rules_warp_kernel<HEAVY, 8><<<grid, 32 * gpb, smem, st>>>(P, smem_per_game);
+    else if (regs <= 80) mrts_rules_warp_kernel<HEAVY, 6><<<grid, 32 * gpb, smem, st>>>(P, smem_per_game);
     else if (regs <= 96) mrts_rules_warp_kernel<HEAVY, 5><<<grid, 32 * gpb, smem, st>>>(P, smem_per_game);
     else mrts_rules_warp_kernel<HEAVY, 4><<<grid, 32 * gpb, smem, st>>>(P, smem_per_game);
     return cudaGetLastError();
@@ -64,6 +65,7 @@ static cudaError_t set_smem_t(int warp_bytes, int block_bytes) {
     cudaError_t e = cudaSuccess;
     if (warp_bytes > 48 * 1024) {
         if ((e = cudaFuncSetAttribute(mrts_rules_warp_kernel<HEAVY, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, warp_bytes)) != cudaSuccess) return e;
+        if ((e = cudaFuncSetAttribute(mrts_rules_warp_kernel<HEAVY, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, warp_bytes)) != cudaSuccess) return e;
         if ((e = cudaFuncSetAttribute(mrts_rules_warp_kernel<HEAVY, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, warp_bytes)) != cudaSuccess) return e;
         if ((e = cudaFuncSetAttribute(mrts_rules_warp_kernel<HEAVY, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, warp_bytes)) != cudaSuccess) return e;
     }
@@ -75,6 +77,7 @@ static int warp_regs_t(int regs) {
     cudaFuncAttributes a;
     cudaError_t e;
     if (regs <= 64) e = cudaFuncGetAttributes(&a, mrts_rules_warp_kernel<HEAVY, 8>);
+    else if (regs <= 80) e = cudaFuncGetAttributes(&a, mrts_rules_warp_kernel<HEAVY, 6>);
     else if (regs <= 96) e = cudaFuncGetAttributes(&a, mrts_rules_warp_kernel<HEAVY, 5>);
     else e = cudaFuncGetAttributes(&a, mrts_rules_warp_kernel<HEAVY, 4>);
     return e == cudaSuccess ? a.numRegs : -1;

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Where an end-to-end step (bench.py e2e loop) spends its time: policy stand-in, its action grid
-device->host, env.step (mrts_step_host_slot).  Usage: python tools/e2e_probe.py [workload] [envs]"""
+device->host, env.step (mrts_step_host_slot).  Usage: python tools/e2e_probe.py [workload] [envs] [prewarm steps]"""
 import ctypes as C
 import os
 import sys
@@ -16,6 +16,7 @@ from microrts_py_b200.envs import MicroRTSGridModeVecEnv  # noqa: E402
 
 name = sys.argv[1] if len(sys.argv) > 1 else "cfg2_rollout16"
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
+prewarm = int(sys.argv[3]) if len(sys.argv) > 3 else 5
 wl = bench.workload_setup(name, None)
 nsp = int(n * (wl["nsp"] / wl["n"])) // 2 * 2
 nbot = n - nsp
@@ -25,8 +26,21 @@ a_host = torch.zeros((n, env.height * env.width, 7), dtype=torch.int32).pin_memo
 env.reset()
 T = {"sample": 0.0, "actions_d2h": 0.0, "step": 0.0}
 K = 40
-for it in range(K + 5):
-    if it == 5:
+lib_s = [0.0]
+_orig = env._lib.mrts_step_host_slot
+
+
+def _timed(*args):
+    t = time.perf_counter()
+    r = _orig(*args)
+    lib_s[0] += time.perf_counter() - t
+    return r
+
+
+env._lib.mrts_step_host_slot = _timed
+for it in range(K + prewarm):
+    if it == prewarm:
+        lib_s[0] = 0.0
         T = dict.fromkeys(T, 0.0)
         ph = (C.c_double * 8)()
         env._lib.mrts_host_timing(env._h, ph, 1)
@@ -50,4 +64,4 @@ env._lib.mrts_host_timing(env._h, ph, 0)
 calls = max(ph[7], 1)
 names = ["pack actions", "h2d + launch", "wait device", "patch / widen", "copy-out"]
 print("  inside mrts_step_host_slot (%d threads): " % env._lib.mrts_host_threads(env._h) + " | ".join(f"{k} {1e3 * ph[i] / calls:.3f} ms" for i, k in enumerate(names))
-      + f" | {ph[5] / calls / n:.2f} changed cells/env, {ph[6] / calls / 1e6:.2f} MB d2h" + f" | env.step total {1e3 * T['step'] / K:.3f} ms = {n * K / T['step'] / 1e6:.2f} M env-steps/s")
+      + f" | {ph[5] / calls / n:.2f} changed cells/env, {ph[6] / calls / 1e6:.2f} MB d2h" + f" | inside the C call {1e3 * lib_s[0] / K:.3f} ms" + f" | env.step total {1e3 * T['step'] / K:.3f} ms = {n * K / T['step'] / 1e6:.2f} M env-steps/s")

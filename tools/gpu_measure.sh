@@ -62,7 +62,7 @@ launches)
 full)
   B="python bench.py --steps 4 --warmup 3 --prewarm 300 --cpu-budget 0 --e2e-envs 0 --workload $NCU_WL $EXTRA"
   timeout 400 $B > gpurun_out/${T}_full_plain.log 2>&1 && \
-  timeout 1800 ncu --set full --clock-control none --import-source on -k regex:mrts_rules -s ${NCU_SKIP:-310} -c ${NCU_COUNT:-4} -f -o gpurun_out/${T}_full_$NCU_WL $B > gpurun_out/${T}_full_ncu.log 2>&1
+  timeout 1800 ncu --set full --clock-control none --import-source on -k regex:mrts_ -s ${NCU_SKIP:-930} -c ${NCU_COUNT:-6} -f -o gpurun_out/${T}_full_$NCU_WL $B > gpurun_out/${T}_full_ncu.log 2>&1
   say "full rc=$? $(ls -la gpurun_out/${T}_full_$NCU_WL.ncu-rep 2>&1 | awk '{print $5}') bytes";;
 src)
   B="python bench.py --steps 12 --warmup 2 --prewarm 200 --cpu-budget 0 --e2e-envs 0 --workload diag_wrush16"
