@@ -195,7 +195,8 @@ int mrts_host_pack_actions(const void* actions, int action_elem_bytes, const uin
 int mrts_host_expand_obs_delta(const uint32_t* words, uint32_t* shadow, int64_t n_env, int hw, int planes, int elem_bytes, void* out);
 int mrts_host_expand_mask_delta(const uint32_t* mask_words, uint32_t* shadow, int64_t n_env, int hw, int elem_bytes, void* out);
 /* the codec of the device-delta slot calls: action rows picked by a bitmap over the flat cell index (only set cells of `out`
- * are written), and entries (count, 5) {flat cell, obs word, mask words 0..2} patched into obs (cells, planes) / mask (cells, 78) */
+ * are written), and entries (count, 6) {flat cell, obs word, mask words 0..2, span} patched into obs (cells, planes) / mask (cells, 78);
+ * span = first | last << 5 changed observation plane, first << 10 | last << 17 changed mask entry (first > last: row unchanged) */
 int mrts_host_pack_actions_bitmap(const void* actions, int action_elem_bytes, const uint32_t* bitmap, int64_t cells, uint16_t* out);
 int mrts_host_patch_cells(const uint32_t* entries, int64_t count, int planes, int elem_bytes, void* obs, void* mask);
 int mrts_host_threads(const mrts_env* env); /* worker threads of the widening pool (0 before the first host call) */

@@ -136,7 +136,7 @@ struct mrts_env {
             bool on_device = false;             // d_shadow[slot] holds the words expanded into (obs, mask)
         } slots[MRTS_HOST_SLOTS];
         // delta transport of the slot calls (mrts_delta.cu): ONE device buffer and its pinned mirror
-        //   [header 64 words: word 0 = changed cells | reward N x 6 doubles | done N bytes | bitmap | entries cap x 5 words]
+        //   [header 64 words: word 0 = changed cells | reward N x 6 doubles | done N bytes | bitmap | entries cap x 6 words]
         // so that a step's results leave with a single copy
         uint32_t *d_delta = nullptr, *h_delta = nullptr;
         size_t off_rew = 0, off_done = 0, off_bitmap = 0, off_entries = 0, delta_cap = 0;  // byte offsets; capacity in entries
@@ -384,9 +384,11 @@ int launch(mrts_env* e, int mode, const int32_t* actions, void* obs, void* mask,
     return mark_last(e, st);
 }
 
-// direct mode: 32 = one warp per game; above 32x32 one 256-thread block per game (1.87 MB of output per 64x64 view:
-// measured faster with every thread of a block on the store loops).  cfg->threads_per_game overrides.
-int choose_threads(int HW) { return HW <= 1024 ? 32 : 256; }
+// direct mode: 32 = one warp per game up to 16x16; above it a block per game so that every thread takes part in the
+// store loops (446 KB per 32x32 partial view, 1.87 MB per 64x64 view) and in the per-cell visibility tests.  Measured at
+// 32x32 partial (cfg4, M env-steps/s): warp kernel 8.8, blocks of 64 / 128 / 256 threads 8.8 / 10.6 / 8.4; at 64x64 256
+// threads.  cfg->threads_per_game overrides.
+int choose_threads(int HW) { return HW <= 256 ? 32 : (HW <= 1024 ? 128 : 256); }
 
 }  // namespace
 
@@ -441,6 +443,7 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
     // ---- kernels.  threads_per_game: 0 = choose; n > 0 = n threads per game (block kernel, direct mode);
     // n < 0 = warp kernels with -n games per block (tuning)
     e->threads = cfg->threads_per_game > 0 ? cfg->threads_per_game : (cfg->threads_per_game < 0 ? 32 : choose_threads(HW));
+    if (cfg->threads_per_game == 0 && env_int("MRTS_THREADS_PER_GAME", 0) > 0) e->threads = env_int("MRTS_THREADS_PER_GAME", 0);  // tuning experiments
     if (e->threads > 256) e->threads = 256;
     if (e->threads < 32 || (e->threads & 31)) {
         mrts_destroy(e);
@@ -487,9 +490,16 @@ int mrts_create(const mrts_config* cfg, mrts_env** out) {
     if (e->pipeline == 0) e->pipeline = MRTS_PIPELINE_DIRECT;  // measured faster than SPLIT on every BASELINE config
     e->bulk_mask = env_int("MRTS_BULK_MASK", -1);  // 1 / 0 = force the bulk mask writer on / off; -1 = choose below
     // Register budget: light games (self-play, PassiveAI) fit 64 registers without spills -> 32 warps per SM;
-    // the scripted-bot kernels take 80 (44 bytes of spills; 25 instead of 21 resident warps: measured +7 % on WorkerRush).
+    // the scripted-bot kernels take 80 when every game is one (44 bytes of spills; 25 instead of 21 resident warps: +7 % on WorkerRush).
     e->regs[0] = env_int("MRTS_REGS_LIGHT", 64);
-    e->regs[1] = env_int("MRTS_REGS_HEAVY", 80);
+    {
+        // With both game classes the light launch runs beside the heavy one (s_light): 96 registers leave the light warps
+        // room on every SM.  Measured on cfg2 (M env-steps/s, int32 / uint8): 96 -> 40.7 / 48.5, 80 -> 39.3 / 40.9.
+        int n_heavy = 0;
+        for (int g = 0; g < P.n_games; g++) n_heavy += ai_plans(S.game_ai[g]) || ai_plans(S.game_ai1[g]);
+        const bool mixed = n_heavy > 0 && n_heavy < P.n_games && env_int("MRTS_OVERLAP", 1);
+        e->regs[1] = env_int("MRTS_REGS_HEAVY", mixed ? 96 : 80);
+    }
     // Games per block: a block's shared memory and warp slots are only released when its slowest
     // game is done and game times vary widely (scripted-bot path finding), so take the smallest
     // count that still reaches the most resident games per SM.  The bulk mask writer adds one tile of zeros per
@@ -781,6 +791,7 @@ static int hostio_finish(mrts_env* e, void* h_obs, void* h_mask, double* h_rewar
     return MRTS_OK;
 }
 
+constexpr size_t DELTA_ENTRY_BYTES = DELTA_ENTRY_WORDS * sizeof(uint32_t);
 static double now_s() {
     timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
@@ -799,7 +810,7 @@ static int hostio_delta_init(mrts_env* e, int slot) {
         h.off_bitmap = h.off_done + up(N);
         h.off_entries = h.off_bitmap + up((cells + 31) / 32 * 4);
         h.delta_cap = cells;  // every cell may change (a reset of all games): the list can never overflow
-        const size_t bytes = h.off_entries + h.delta_cap * 20;
+        const size_t bytes = h.off_entries + h.delta_cap * DELTA_ENTRY_BYTES;
         CK(cudaMalloc((void**)&h.d_delta, bytes));
         CK(cudaMallocHost((void**)&h.h_delta, bytes));
         CK(cudaMemset(h.d_delta, 0, h.off_entries));
@@ -850,18 +861,18 @@ static int hostio_finish_slot(mrts_env* e, void* h_obs, void* h_mask, double* h_
     } else {
         size_t guess = 2 * h.last_count > 4096 ? 2 * h.last_count : 4096;
         if (guess > h.delta_cap) guess = h.delta_cap;
-        CK(cudaMemcpyAsync(hb, db, h.off_entries + guess * 20, cudaMemcpyDeviceToHost, h.stream));
+        CK(cudaMemcpyAsync(hb, db, h.off_entries + guess * DELTA_ENTRY_BYTES, cudaMemcpyDeviceToHost, h.stream));
         CK(cudaStreamSynchronize(h.stream));
         const size_t count = h.h_delta[0];
         if (count > h.delta_cap) return fail(MRTS_ECUDA, "delta list overflow");
         if (count > guess) {
-            CK(cudaMemcpyAsync(hb + h.off_entries + guess * 20, db + h.off_entries + guess * 20, (count - guess) * 20, cudaMemcpyDeviceToHost, h.stream));
+            CK(cudaMemcpyAsync(hb + h.off_entries + guess * DELTA_ENTRY_BYTES, db + h.off_entries + guess * DELTA_ENTRY_BYTES, (count - guess) * DELTA_ENTRY_BYTES, cudaMemcpyDeviceToHost, h.stream));
             CK(cudaStreamSynchronize(h.stream));
         }
         t1 = now_s();
         mrts_host::patch_cells(h.pool, (const uint32_t*)(hb + h.off_entries), count, e->P.planes, e->P.elem, h_obs, h_mask);
         h.last_count = count;
-        h.t_phase[5] += (double)count, h.t_phase[6] += (double)(h.off_entries + (count > guess ? count : guess) * 20);
+        h.t_phase[5] += (double)count, h.t_phase[6] += (double)(h.off_entries + (count > guess ? count : guess) * DELTA_ENTRY_BYTES);
         t2 = now_s();
     }
     h.have_mask = true;

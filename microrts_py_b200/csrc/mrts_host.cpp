@@ -19,6 +19,7 @@
 #endif
 
 namespace mrts_host {
+constexpr int ENTRY_WORDS = 6;  // mrts_launch.h: DELTA_ENTRY_WORDS
 #if defined(__x86_64__)
 static void mask_row_avx2_32(const uint32_t* pm, int32_t* o);  // defined with the incremental forms below
 #endif
@@ -472,43 +473,55 @@ void pack_actions_bitmap(Pool* p, const void* actions, int action_elem, const ui
 void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int elem, void* obs, void* mask) {
     parallel_for(p, count, [=](size_t b, size_t e) {
         const size_t obs_cell_bytes = (size_t)planes * elem, mask_cell_bytes = (size_t)78 * elem;
-        constexpr size_t AHEAD = 6;
-#if defined(__x86_64__)
-        const bool wide = has_avx2() && elem == 4 && planes >= 24 && planes <= 32;
-#endif
+        constexpr size_t AHEAD = 8;
+        // the changed range of an entry's two rows: byte offsets [lo, hi) inside the tensors, or lo >= hi
+        auto obs_range = [&](const uint32_t* en, size_t& lo, size_t& hi) {
+            const uint32_t k0 = en[5] & 31u, k1 = (en[5] >> 5) & 31u;
+            lo = en[0] * obs_cell_bytes + (size_t)k0 * elem;
+            hi = k0 <= k1 ? en[0] * obs_cell_bytes + (size_t)(k1 + 1) * elem : lo;
+        };
+        auto mask_range = [&](const uint32_t* en, size_t& lo, size_t& hi) {
+            const uint32_t b0 = (en[5] >> 10) & 127u, b1 = (en[5] >> 17) & 127u;
+            lo = en[0] * mask_cell_bytes + (size_t)b0 * elem;
+            hi = b0 <= b1 ? en[0] * mask_cell_bytes + (size_t)(b1 + 1) * elem : lo;
+        };
         auto prefetch = [&](size_t i) {
-            const size_t g = entries[5 * i];
+            const uint32_t* en = entries + ENTRY_WORDS * i;
+            size_t lo, hi;
             if (obs) {
-                const char* o = (const char*)obs + g * obs_cell_bytes;
-                for (size_t k = 0; k < obs_cell_bytes; k += 64) __builtin_prefetch(o + k, 1, 0);
-                __builtin_prefetch(o + obs_cell_bytes - 1, 1, 0);
+                obs_range(en, lo, hi);
+                for (size_t a = lo & ~(size_t)63; a < hi; a += 64) __builtin_prefetch((const char*)obs + a, 1, 0);
             }
             if (mask) {
-                const char* m = (const char*)mask + g * mask_cell_bytes;
-                for (size_t k = 0; k < mask_cell_bytes; k += 64) __builtin_prefetch(m + k, 1, 0);
-                __builtin_prefetch(m + mask_cell_bytes - 1, 1, 0);
+                mask_range(en, lo, hi);
+                for (size_t a = lo & ~(size_t)63; a < hi; a += 64) __builtin_prefetch((const char*)mask + a, 1, 0);
             }
         };
         for (size_t i = b; i < e && i < b + AHEAD; i++) prefetch(i);
         for (size_t i = b; i < e; i++) {
             if (i + AHEAD < e) prefetch(i + AHEAD);
-            const uint32_t* en = entries + 5 * i;
+            const uint32_t* en = entries + ENTRY_WORDS * i;
             const size_t g = en[0];
             if (obs) {
-                uint8_t* o = (uint8_t*)obs + g * obs_cell_bytes;
-#if defined(__x86_64__)
-                if (wide) obs_cell_avx2_32(en[1], planes, (int32_t*)o);
-                else
-#endif
-                    obs_cell(en[1], planes, elem, o);
+                const uint32_t k0 = en[5] & 31u, k1 = (en[5] >> 5) & 31u, w = en[1];
+                if (elem == 4) {
+                    int32_t* o = (int32_t*)obs + g * planes;
+                    for (uint32_t k = k0; k <= k1 && k < (uint32_t)planes; k++) o[k] = (int32_t)((w >> k) & 1u);
+                } else {
+                    uint8_t* o = (uint8_t*)obs + g * planes;
+                    for (uint32_t k = k0; k <= k1 && k < (uint32_t)planes; k++) o[k] = (uint8_t)((w >> k) & 1u);
+                }
             }
             if (mask) {
-                uint8_t* m = (uint8_t*)mask + g * mask_cell_bytes;
-#if defined(__x86_64__)
-                if (has_avx2() && elem == 4 && (en[2] | en[3] | en[4])) mask_cell_avx2_32(en + 2, (int32_t*)m);
-                else
-#endif
-                    mask_cell(en + 2, elem, m);
+                const uint32_t b0 = (en[5] >> 10) & 127u, b1 = (en[5] >> 17) & 127u;
+                const uint32_t* pm = en + 2;
+                if (elem == 4) {
+                    int32_t* m = (int32_t*)mask + g * 78;
+                    for (uint32_t k = b0; k <= b1 && k < 78u; k++) m[k] = (int32_t)((pm[k >> 5] >> (k & 31)) & 1u);
+                } else {
+                    uint8_t* m = (uint8_t*)mask + g * 78;
+                    for (uint32_t k = b0; k <= b1 && k < 78u; k++) m[k] = (uint8_t)((pm[k >> 5] >> (k & 31)) & 1u);
+                }
             }
         }
     });

@@ -38,8 +38,11 @@ void pack_actions(Pool* p, const void* actions, int action_elem /* 4 or 8 */, co
 // The same with the source cells given as a bitmap over the flat cell index (bit = mask bit 0, mrts_delta.cu): only the
 // rows of set bits are read and only those cells of `out` are written (the device reads no other cell).
 void pack_actions_bitmap(Pool* p, const void* actions, int action_elem, const uint32_t* bitmap, size_t cells, uint16_t* out);
-// entries (count, 5) {flat cell, obs word, mask words 0..2} -> those cells of obs (cells, planes) and mask (cells, 78);
-// every cell appears at most once, either array may be null
+// entries (count, 6) {flat cell, obs word, mask words 0..2, span} -> those cells of obs (cells, planes) and mask (cells, 78).
+// span = first | last << 5 changed plane of the cell's observation row, first << 10 | last << 17 changed entry of its mask
+// row (mrts_delta.cu): only those ranges are rewritten -- usually one cache line per tensor instead of the rows' two to six,
+// and it is the cache lines touched (each one a miss in arrays of hundreds of MB) that this costs.  Every cell appears at
+// most once, either array may be null.
 void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int elem, void* obs, void* mask);
 
 }  // namespace mrts_host

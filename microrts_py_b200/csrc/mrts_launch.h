@@ -61,13 +61,14 @@ int expand_smem_bytes();
 int expand_threads();
 
 // ---- delta compaction of the packed outputs against a result-buffer slot's shadow (mrts_delta.cu)
+constexpr int DELTA_ENTRY_WORDS = 6;  // {flat cell, obs word, mask words 0..2, span}: 24 bytes
 struct DeltaParams {
     const uint32_t* pobs;   // (cells) observation words of this step
     const uint32_t* pmask;  // (cells, 3) mask words of this step
     uint32_t* shadow;       // (cells, 4) {obs word, mask words} last expanded into the slot's arrays; brought up to date
     uint32_t* count;        // number of cells that differ (may exceed cap: then the entries are incomplete)
     uint32_t* bitmap;       // ceil(cells / 32) words: bit = mask bit 0 of the cell
-    uint32_t* entries;      // (cap, 5) {flat cell, obs word, mask words}
+    uint32_t* entries;      // (cap, DELTA_ENTRY_WORDS)
     long long cells;
     uint32_t cap;
     int init;               // 1 = only fill the shadow and the bitmap (the host expands the whole arrays this time)

@@ -134,24 +134,51 @@ def test_action_rows_pack_by_bitmap_touch_only_set_cells(dtype):
 
 
 @pytest.mark.parametrize("planes,dtype", [(29, np.int32), (31, np.int32), (29, np.uint8), (31, np.uint8)])
-def test_entries_patch_exactly_their_cells(planes, dtype):
+def test_entries_patch_exactly_the_changed_range_of_their_cells(planes, dtype):
+    """entries as mrts_delta_kernel emits them: new words + the first / last changed element per row; the arrays hold the
+    expansion of the OLD words, after the patch they must hold the expansion of the new ones and nothing else may move"""
     L = _capi.lib()
     rng = np.random.default_rng(planes)
-    cells = 4000
-    obs = rng.integers(0, 2, size=(cells, planes)).astype(dtype)
-    mask = rng.integers(0, 2, size=(cells, 78)).astype(dtype)
-    want_obs, want_mask = obs.copy(), mask.copy()
-    picked = rng.choice(cells, size=700, replace=False)
-    ent = np.zeros((700, 5), np.uint32)
+    cells, n = 4000, 700
+    k78 = np.arange(78)
+
+    def expand(ow, mw):
+        o = ((ow[:, None] >> np.arange(planes, dtype=np.uint32)) & 1).astype(dtype)
+        m = ((mw[:, k78 // 32] >> (k78 % 32).astype(np.uint32)) & 1).astype(dtype)
+        return np.ascontiguousarray(o), np.ascontiguousarray(m)  # (fancy indexing may hand back another memory order)
+
+    old_o = rng.integers(0, 2 ** planes, size=cells, dtype=np.uint64).astype(np.uint32)
+    old_m = rng.integers(0, 2 ** 32, size=(cells, 3), dtype=np.uint64).astype(np.uint32)
+    old_m[:, 2] &= (1 << 14) - 1
+    obs, mask = expand(old_o, old_m)
+    picked = rng.choice(cells, size=n, replace=False)
+    new_o, new_m = old_o.copy(), old_m.copy()
+    flips = rng.integers(0, 2 ** planes, size=n, dtype=np.uint64).astype(np.uint32)
+    flips[::5] = 0            # observation row unchanged
+    flips[1::7] = 1 << 3      # a single plane
+    new_o[picked] ^= flips
+    mflip = rng.integers(0, 2 ** 32, size=(n, 3), dtype=np.uint64).astype(np.uint32)
+    mflip[:, 2] &= (1 << 14) - 1
+    mflip[::3] = 0            # mask row unchanged
+    mflip[1::4, 0] = 0        # change starts in the second word
+    mflip[2::9, 1:] = 0       # change confined to the first word
+    mflip[5::5] = 0
+    mflip[5::5, 1] = 1 << 9   # a single entry
+    new_m[picked] ^= mflip
+    both_same = (flips == 0) & (mflip == 0).all(axis=1)
+    ent = np.zeros((n, 6), np.uint32)
     ent[:, 0] = picked
-    ent[:, 1] = rng.integers(0, 2 ** planes, size=700, dtype=np.uint64)
-    ent[:, 2:4] = rng.integers(0, 2 ** 32, size=(700, 2), dtype=np.uint64)
-    ent[:, 4] = rng.integers(0, 2 ** 14, size=700, dtype=np.uint64)
-    ent[::9, 2:] = 0  # all-zero rows take the memset branch
-    want_obs[picked] = ((ent[:, 1, None] >> np.arange(planes, dtype=np.uint32)) & 1).astype(dtype)
-    k = np.arange(78)
-    want_mask[picked] = ((ent[:, 2 + k // 32] >> (k % 32).astype(np.uint32)) & 1).astype(dtype)
-    _capi.check(L.mrts_host_patch_cells(_p(ent), 700, planes, np.dtype(dtype).itemsize, _p(obs), _p(mask)))
+    ent[:, 1] = new_o[picked]
+    ent[:, 2:5] = new_m[picked]
+    for i in range(n):
+        xo = int(flips[i])
+        ko0, ko1 = (31, 0) if xo == 0 else ((xo & -xo).bit_length() - 1, xo.bit_length() - 1)
+        xm = int(mflip[i, 0]) | (int(mflip[i, 1]) << 32) | (int(mflip[i, 2]) << 64)
+        kb0, kb1 = (127, 0) if xm == 0 else ((xm & -xm).bit_length() - 1, xm.bit_length() - 1)
+        ent[i, 5] = ko0 | (ko1 << 5) | (kb0 << 10) | (kb1 << 17)
+    ent = np.ascontiguousarray(ent[~both_same])
+    want_obs, want_mask = expand(new_o, new_m)
+    _capi.check(L.mrts_host_patch_cells(_p(ent), len(ent), planes, np.dtype(dtype).itemsize, _p(obs), _p(mask)))
     np.testing.assert_array_equal(obs, want_obs)
     np.testing.assert_array_equal(mask, want_mask)
-    _capi.check(L.mrts_host_patch_cells(_p(ent), 700, planes, np.dtype(dtype).itemsize, _p(obs), None))  # either array may be null
+    _capi.check(L.mrts_host_patch_cells(_p(ent), len(ent), planes, np.dtype(dtype).itemsize, _p(obs), None))  # either array may be null

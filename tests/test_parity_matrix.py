@@ -90,6 +90,8 @@ MATRIX = {
     "u8_p31_8x8_direct": (4, [W, LR, P], MAP_8, True, 150, 500, 0.08, dict(dtype=np.uint8, pipeline="direct")),
     "u8_p31_8x8_split": (4, [W, LR, P], MAP_8, True, 150, 500, 0.08, dict(dtype=np.uint8, pipeline="split", chunks=2)),
     "u8_p31_32x32_direct": (2, [W, POL], MAP_32, True, 200, 450, 0.05, dict(dtype=np.uint8, pipeline="direct")),
+    "u8_p31_32x32_warp": (2, [W, POL], MAP_32, True, 200, 450, 0.05, dict(dtype=np.uint8, pipeline="direct", threads_per_game=-2)),
+    "i32_p29_32x32_block128": (2, [LR, P], MAP_32, False, 200, 400, 0.05, dict(pipeline="direct")),
     "u8_p31_32x32_split": (2, [W, POL], MAP_32, True, 200, 450, 0.05, dict(dtype=np.uint8, pipeline="split", chunks=3)),
     "u8_p31_64x64_block": (2, [W], MAP_64, True, 120, 300, 0.05, dict(dtype=np.uint8, pipeline="direct", threads_per_game=256)),
     "u8_p31_64x64_warp": (2, [W], MAP_64, True, 120, 300, 0.05, dict(dtype=np.uint8, pipeline="direct")),

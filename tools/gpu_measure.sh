@@ -9,6 +9,7 @@
 #   bench     the default bench.py line (cpu_baseline + e2e included) for $WORKLOADS -> TAG_bench.jsonl
 #   launches  ncu launch list (gpu__time_duration) of $NCU_WL (default cfg2_rollout16)
 #   full      ncu --set full of the dominant kernel of $NCU_WL -> TAG_full.ncu-rep (+ traffic json via tools/ncu_traffic.py)
+#   scale     NGPU=N torchrun bench lines of $WORKLOADS (run under gpurun --gpus N)
 #   src       ncu source counters of the heavy rules kernel on diag_wrush16
 # ncu stages run the same command without ncu first and only go on when it exits 0.
 set -u
@@ -62,13 +63,20 @@ launches)
 full)
   B="python bench.py --steps 4 --warmup 3 --prewarm 300 --cpu-budget 0 --e2e-envs 0 --workload $NCU_WL $EXTRA"
   timeout 400 $B > gpurun_out/${T}_full_plain.log 2>&1 && \
-  timeout 1800 ncu --set full --clock-control none --import-source on -k regex:mrts_ -s ${NCU_SKIP:-930} -c ${NCU_COUNT:-6} -f -o gpurun_out/${T}_full_$NCU_WL $B > gpurun_out/${T}_full_ncu.log 2>&1
+  timeout 1800 ncu --set full --clock-control none --import-source on -k regex:mrts_ -s ${NCU_SKIP:-906} -c ${NCU_COUNT:-6} -f -o gpurun_out/${T}_full_$NCU_WL $B > gpurun_out/${T}_full_ncu.log 2>&1
   say "full rc=$? $(ls -la gpurun_out/${T}_full_$NCU_WL.ncu-rep 2>&1 | awk '{print $5}') bytes";;
 src)
   B="python bench.py --steps 12 --warmup 2 --prewarm 200 --cpu-budget 0 --e2e-envs 0 --workload diag_wrush16"
   timeout 400 $B > gpurun_out/${T}_src_plain.log 2>&1 && \
   timeout 1500 ncu --section SourceCounters --section WarpStateStats --section SchedulerStats --clock-control none --import-source on -k regex:mrts_rules_warp -s 205 -c 12 -f -o gpurun_out/${T}_src_wrush $B > gpurun_out/${T}_src_ncu.log 2>&1
   say "src rc=$?";;
+scale)  # under `gpurun --gpus N`: NGPU=N; one torchrun per workload, e2e arm included, CPU legs skipped
+  : ${NGPU:?NGPU}
+  for WL in $WORKLOADS; do
+    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $NGPU --workload $WL --steps 100 --warmup 10 --cpu-budget 0 $EXTRA > gpurun_out/${T}_scale${NGPU}_$WL.json 2> gpurun_out/${T}_scale${NGPU}_$WL.err
+    tail -n 1 gpurun_out/${T}_scale${NGPU}_$WL.json >> gpurun_out/${T}_scale.jsonl
+    say "$(digest gpurun_out/${T}_scale${NGPU}_$WL.json "N=$NGPU $WL [$EXTRA]")"
+  done;;
 *) say "unknown stage $stage";;
 esac
 done
