@@ -859,7 +859,7 @@ static int hostio_finish_slot(mrts_env* e, void* h_obs, void* h_mask, double* h_
         S.pobs.clear(), S.pmask.clear();
         t2 = now_s();
     } else {
-        size_t guess = 2 * h.last_count > 4096 ? 2 * h.last_count : 4096;
+        size_t guess = h.last_count + h.last_count / 4 + 1024;  // the count moves slowly from step to step; a short second copy covers a miss
         if (guess > h.delta_cap) guess = h.delta_cap;
         CK(cudaMemcpyAsync(hb, db, h.off_entries + guess * DELTA_ENTRY_BYTES, cudaMemcpyDeviceToHost, h.stream));
         CK(cudaStreamSynchronize(h.stream));

@@ -102,12 +102,14 @@ MRTS_HD Layout make_layout(int W, int HW, int cap, int has_bot, int any_bot) {
     const int end_rules = o;
     // ---- output scratch (aliases the rules scratch)
     o = scratch;
+    // The observation words (one view at a time) are dead when the last view's observation is stored; the staging
+    // buffers of the bulk mask writer (bulk::STAGE_BYTES, mrts_bulk.cuh) are first written after that: same bytes.
+    // At 16x16 this takes a light game from 6.3 to 5.3 KB: 8 instead of 7 resident blocks of four games per SM.
     L.words = o;
-    o += align16(HW * 4);  // one view at a time
+    L.slots = o;
+    o += align16(HW * 4) > 2 * 1248 ? align16(HW * 4) : 2 * 1248;
     L.umask = o;
     o += align16(cap * 12);
-    L.slots = o;  // staging of the bulk writers (direct mode): bulk::STAGE_BYTES (mrts_bulk.cuh)
-    o += 2 * 1248;
     L.total = o > end_rules ? o : end_rules;
     return L;
 }

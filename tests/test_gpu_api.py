@@ -146,6 +146,43 @@ def test_full_size_properties(mp, nsp, partial):
     env.close()
 
 
+@pytest.mark.parametrize("mp,n,partial,max_steps", [(MAP_8, 65536, False, 150), (MAP_32, 16384, True, 400)], ids=["cfg3_65536", "cfg4_16384"])
+def test_baseline_sized_slabs_match_the_oracle_on_a_subsample(mp, n, partial, max_steps):
+    """SURVEY 8(d) subsample protocol at BASELINE.json's sizes (configs[2]: 65,536 envs 8x8; configs[3]: 16,384 envs 32x32
+    partial_obs): the whole slab steps on the device with device-sampled actions; 128 self-play games spread over the slab
+    (256 envs) are mirrored on the oracle (all cores) with the same action rows for 1,000 steps, crossing max_steps resets."""
+    import os
+
+    import torch
+    from oracle.oracle_py import OracleVecEnv
+
+    sub_games = 128
+    games = np.linspace(0, n // 2 - 1, sub_games).astype(np.int64)
+    idx = np.stack([2 * games, 2 * games + 1], axis=1).reshape(-1)  # env rows of those games, pair by pair
+    t_idx = torch.as_tensor(idx, device="cuda")
+    env = _env(n, 0, partial_obs=partial, max_steps=max_steps, map_paths=[mp], return_torch=True, seed=11)
+    ref = OracleVecEnv(len(idx), 0, max_steps, partial, templates_for([mp] * len(idx)), [], threads=os.cpu_count() or 1)
+    obs = env.reset()
+    np.testing.assert_array_equal(obs[t_idx].cpu().numpy(), ref.reset())
+    n_done = 0
+    for t in range(1000):
+        if t % 25 == 0:
+            m_ref, _ = ref.get_masks()
+            np.testing.assert_array_equal(env.get_action_mask()[t_idx].cpu().numpy(), m_ref, err_msg=f"mask at step {t}")
+        else:
+            env.get_action_mask()
+        a = env.sample_actions()
+        o_ref, r_ref, d_ref = ref.step(a[t_idx].cpu().numpy())
+        obs, r, d, infos = env.step(a)
+        np.testing.assert_array_equal(infos.raw[t_idx].cpu().numpy(), r_ref, err_msg=f"raw rewards at step {t}")
+        np.testing.assert_array_equal(d[t_idx].cpu().numpy().astype(np.uint8), d_ref, err_msg=f"done at step {t}")
+        if t % 5 == 0 or d_ref.any():
+            np.testing.assert_array_equal(obs[t_idx].cpu().numpy(), o_ref, err_msg=f"observation at step {t}")
+        n_done += int(d_ref.sum())
+    assert n_done >= 2 * sub_games, "every mirrored game was meant to cross a reset"
+    env.close()
+
+
 @pytest.mark.parametrize("staged", [8, 12])
 def test_games_outgrowing_the_staged_capacity_take_the_full_capacity_launch(staged):
     """The warp kernel stages only `staged_units` units per game in shared memory; games that may
