@@ -288,6 +288,25 @@ def kernel_info(L, h):
     return out
 
 
+def pin_rank(local):
+    """Several ranks on one node: give each its own contiguous block of the cores the job may use (threads that float over every
+    core of a two-socket host miss into remote memory, and eight ranks' pools get in one another's way), and size the library's
+    host pool to that block.  Opt-in (MRTS_BENCH_PIN=1): the boxes measured are single-socket VMs without SMT, where it changed
+    nothing (2 GPUs, cfg2 e2e: 18.3 M pinned, 18.9 M floating); any failure leaves the affinity as it was."""
+    lws = int(os.environ.get("LOCAL_WORLD_SIZE", "1"))
+    if lws <= 1 or os.environ.get("MRTS_BENCH_PIN", "0") != "1":
+        return
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        k = len(cores) // lws
+        if k < 1:
+            return
+        os.sched_setaffinity(0, set(cores[local * k:(local + 1) * k]))
+        os.environ.setdefault("MRTS_HOST_THREADS", str(k))
+    except Exception:  # noqa: BLE001
+        pass
+
+
 def gpu_arm(args):
     import ctypes as C
 
@@ -302,6 +321,7 @@ def gpu_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    pin_rank(local)
     dist = None
     if world > 1:
         import torch.distributed as dist

@@ -308,6 +308,17 @@ __attribute__((target("avx2"))) static inline void mask_cell_avx2_32(const uint3
     }
     _mm256_storeu_si256((__m256i*)(o + 70), _mm256_and_si256(_mm256_srlv_epi32(_mm256_set1_epi32((int)(pm[2] >> 6)), s0), one));
 }
+// elements [k0, k1] of a row of `n` int32 one-hot values whose bits are bits[0..2] (n <= 96): whole 8-element chunks, the last
+// one pulled back so that it ends with the row (values outside the changed range are rewritten with what they already hold)
+__attribute__((target("avx2"))) static inline void row_range_avx2_32(const uint32_t* bits, uint32_t k0, uint32_t k1, uint32_t n, int32_t* o) {
+    const __m256i one = _mm256_set1_epi32(1), s0 = _mm256_setr_epi32(0, 1, 2, 3, 4, 5, 6, 7);
+    for (uint32_t c = k0 & ~7u; c <= k1; c += 8) {
+        const uint32_t e0 = c + 8 <= n ? c : n - 8;  // first element of this chunk
+        const uint64_t two = (uint64_t)bits[e0 >> 5] | ((e0 >> 5) + 1 < 3 ? (uint64_t)bits[(e0 >> 5) + 1] << 32 : 0ull);
+        const uint32_t chunk = (uint32_t)(two >> (e0 & 31)) & 0xFFu;
+        _mm256_storeu_si256((__m256i*)(o + e0), _mm256_and_si256(_mm256_srlv_epi32(_mm256_set1_epi32((int)chunk), s0), one));
+    }
+}
 __attribute__((target("avx2"))) static void obs_delta_avx2(const uint32_t* w, uint32_t* sh, size_t cells, int planes, int elem, uint8_t* out) {
     const size_t cell_bytes = (size_t)planes * elem;
     const bool wide = elem == 4 && planes >= 24 && planes <= 32;
@@ -474,6 +485,9 @@ void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int
     parallel_for(p, count, [=](size_t b, size_t e) {
         const size_t obs_cell_bytes = (size_t)planes * elem, mask_cell_bytes = (size_t)78 * elem;
         constexpr size_t AHEAD = 8;
+#if defined(__x86_64__)
+        const bool avx = has_avx2(), wide = avx && planes >= 8 && planes <= 32;
+#endif
         // the changed range of an entry's two rows: byte offsets [lo, hi) inside the tensors, or lo >= hi
         auto obs_range = [&](const uint32_t* en, size_t& lo, size_t& hi) {
             const uint32_t k0 = en[5] & 31u, k1 = (en[5] >> 5) & 31u;
@@ -506,7 +520,13 @@ void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int
                 const uint32_t k0 = en[5] & 31u, k1 = (en[5] >> 5) & 31u, w = en[1];
                 if (elem == 4) {
                     int32_t* o = (int32_t*)obs + g * planes;
-                    for (uint32_t k = k0; k <= k1 && k < (uint32_t)planes; k++) o[k] = (int32_t)((w >> k) & 1u);
+#if defined(__x86_64__)
+                    if (wide && k0 <= k1 && k1 < (uint32_t)planes) {
+                        const uint32_t bits3[3] = {w, 0u, 0u};
+                        row_range_avx2_32(bits3, k0, k1, (uint32_t)planes, o);
+                    } else
+#endif
+                        for (uint32_t k = k0; k <= k1 && k < (uint32_t)planes; k++) o[k] = (int32_t)((w >> k) & 1u);
                 } else {
                     uint8_t* o = (uint8_t*)obs + g * planes;
                     for (uint32_t k = k0; k <= k1 && k < (uint32_t)planes; k++) o[k] = (uint8_t)((w >> k) & 1u);
@@ -517,7 +537,11 @@ void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int
                 const uint32_t* pm = en + 2;
                 if (elem == 4) {
                     int32_t* m = (int32_t*)mask + g * 78;
-                    for (uint32_t k = b0; k <= b1 && k < 78u; k++) m[k] = (int32_t)((pm[k >> 5] >> (k & 31)) & 1u);
+#if defined(__x86_64__)
+                    if (avx && b0 <= b1 && b1 < 78u) row_range_avx2_32(pm, b0, b1, 78u, m);
+                    else
+#endif
+                        for (uint32_t k = b0; k <= b1 && k < 78u; k++) m[k] = (int32_t)((pm[k >> 5] >> (k & 31)) & 1u);
                 } else {
                     uint8_t* m = (uint8_t*)mask + g * 78;
                     for (uint32_t k = b0; k <= b1 && k < 78u; k++) m[k] = (uint8_t)((pm[k >> 5] >> (k & 31)) & 1u);

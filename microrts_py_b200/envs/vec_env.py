@@ -113,6 +113,19 @@ def _ptr(t: Optional[torch.Tensor]):
     return C.c_void_p(t.data_ptr()) if t is not None else None
 
 
+def _huge_empty(shape, dtype):
+    """np.empty whose pages the kernel may back with transparent huge pages (asked for before the first touch)."""
+    a = np.empty(shape, dtype)
+    try:
+        lo = (a.ctypes.data + 4095) & ~4095
+        hi = (a.ctypes.data + a.nbytes) & ~4095
+        if hi - lo >= (1 << 22):
+            C.CDLL(None, use_errno=True).madvise(C.c_void_p(lo), C.c_size_t(hi - lo), 14)  # MADV_HUGEPAGE; failure is harmless
+    except Exception:  # noqa: BLE001
+        pass
+    return a
+
+
 def _np_ptr(a: np.ndarray):
     return C.c_void_p(a.ctypes.data)  # also for arrays handed out read-only
 
@@ -292,9 +305,13 @@ class MicroRTSGridModeVecEnv:
         self._closed = False
         self._sample_seed = int(seed)
         if self.host_transport:
+            # np.empty, not np.zeros: NumPy advises the kernel to back large malloc'ed arrays with huge pages but not
+            # calloc'ed ones, and the patches of the slot calls touch a few scattered cache lines per changed cell of
+            # arrays of hundreds of MB -- on 4 KB pages every one of them is a TLB miss as well.  (The first call on a slot
+            # writes every element.)
             self._hbuf = {
-                "obs": [np.zeros(self._shape_obs, self._np_dtype) for _ in range(2)],
-                "mask": [np.zeros(self._shape_mask, self._np_dtype) for _ in range(2)],
+                "obs": [_huge_empty(self._shape_obs, self._np_dtype) for _ in range(2)],
+                "mask": [_huge_empty(self._shape_mask, self._np_dtype) for _ in range(2)],
                 "raw": [np.zeros((N, 6), np.float64) for _ in range(2)],
                 "done": [np.zeros((N,), np.uint8) for _ in range(2)],
             }
