@@ -96,11 +96,11 @@ def measured_peak():
 
 
 def source_hash():
-    """identity of the kernel sources a capture under profiles/ was taken on (the GPU box has no .git)"""
+    """identity of the kernel sources (device code + launch logic) a capture under profiles/ was taken on (the GPU box has no .git)"""
     h = hashlib.sha1()
     d = os.path.join(ROOT, "microrts_py_b200", "csrc")
     for f in sorted(os.listdir(d)):
-        if f.endswith((".cu", ".cuh", ".h", ".cpp")):
+        if f.endswith((".cu", ".cuh", ".h")) and not f.startswith("mrts_host"):  # device code and launch logic; the host codec moves no DRAM byte
             h.update(f.encode())
             h.update(open(os.path.join(d, f), "rb").read())
     return h.hexdigest()[:16]
@@ -286,6 +286,27 @@ def kernel_info(L, h):
         L.mrts_kernel_info(h, k, C.byref(r), C.byref(g), C.byref(sm))
         out[name] = {"regs": r.value, "games_per_block": g.value, "smem_per_game": sm.value}
     return out
+
+
+def auto_e2e_envs(workload, dtype):
+    """The e2e arm (and the CPU legs beside it) run the workload's own env count when the host can hold the result arrays:
+    two slot pairs + the full-write leg's pair + pinned staging ~ 3.5 x (obs + mask) bytes per env and rank."""
+    wl = workload_setup(workload, 0)
+    if workload.startswith("lit_"):
+        return wl["n"]
+    per_env = CELLS[wl["map"]] * (wl["planes"] + 78) * (4 if dtype == "int32" else 1)
+    lws = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    avail = 64 << 30
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                avail = int(ln.split()[1]) * 1024
+    except Exception:  # noqa: BLE001
+        pass
+    n = wl["n"]
+    while n > 2048 and 3.5 * per_env * n * lws > 0.4 * avail:
+        n //= 2
+    return n
 
 
 def pin_rank(local):
@@ -594,9 +615,11 @@ def main():
     ap.add_argument("--prewarm", type=int, default=-1, help="untimed steps that spread the games over episode phases (default 300; 1,500 for the dense 64x64 workload)")
     ap.add_argument("--cpu-envs", type=int, default=0, help="envs of the CPU legs (default: the e2e arm's)")
     ap.add_argument("--cpu-budget", type=float, default=40.0, help="wall seconds of the cpu_baseline leg incl. its pre-warm (0 = skip)")
-    ap.add_argument("--e2e-envs", type=int, default=8192, help="envs per GPU of the e2e arm (0 = skip)")
+    ap.add_argument("--e2e-envs", type=int, default=-1, help="envs per GPU of the e2e arm and the CPU legs (0 = skip; default: the workload's own count, halved while the host arrays of all local ranks would take more than 40 %% of the available memory)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed steps of the e2e arm (default max(100, steps / 2))")
     args = ap.parse_args()
+    if args.e2e_envs < 0:
+        args.e2e_envs = auto_e2e_envs(args.workload, args.dtype)
     if args.impl == "reference":
         if args.steps == 200 and args.warmup == 20:
             args.steps, args.warmup = 30, 3
