@@ -530,8 +530,8 @@ def e2e_run(args, wl, rank, dist, dev, prewarm):
         ph = (C.c_double * 8)()
         env._lib.mrts_host_timing(env._h, ph, 0)
         calls = max(ph[7], 1.0)
-        phases = {"pack_actions_ms": 1e3 * ph[0] / calls, "h2d_launch_ms": 1e3 * ph[1] / calls, "wait_device_ms": 1e3 * ph[2] / calls, "patch_or_widen_ms": 1e3 * ph[3] / calls,
-                  "copy_out_ms": 1e3 * ph[4] / calls, "changed_cells_per_env_step": ph[5] / calls / k, "d2h_bytes_per_step": ph[6] / calls}
+        phases = {"pack_actions_ms": 1e3 * ph[0] / calls, "h2d_launch_ms": 1e3 * ph[1] / calls, "wait_device_ms": 1e3 * ph[2] / calls, "patch_and_copy_out_ms": 1e3 * ph[3] / calls,
+                  "h2d_bytes_per_step": ph[4] / calls, "changed_cells_per_env_step": ph[5] / calls / k, "d2h_bytes_per_step": ph[6] / calls}
         res = dict(phases=phases, v=k * world * steps / float(t[0].item()), v_loop=k * world * steps / float(t[1].item()), ms=1e3 * float(t[0].item()) / steps,
                    hw=env.height * env.width, threads=env._lib.mrts_host_threads(env._h), nbytes=int(obs.nbytes + m.nbytes), act=a_host.numel() * 4)
         env.close()
@@ -544,7 +544,7 @@ def e2e_run(args, wl, rank, dist, dev, prewarm):
     dflt = run(dict(), max(5, steps // 10), min(prewarm, 20), n_envs=n_dflt)
     hw = slot["hw"]
     d2h = int(slot["phases"]["d2h_bytes_per_step"]) or n * hw * 16 + n * 6 * 8 + n
-    return {"value": slot["v"], "unit": "env-steps/s", "h2d_bytes_per_step": n * hw * 2, "d2h_bytes_per_step": d2h, "d2h_bytes_per_step_full_write": n * hw * 16 + n * 6 * 8 + n,
+    return {"value": slot["v"], "unit": "env-steps/s", "h2d_bytes_per_step": int(slot["phases"]["h2d_bytes_per_step"]) or n * hw * 2, "d2h_bytes_per_step": d2h, "d2h_bytes_per_step_full_write": n * hw * 16 + n * 6 * 8 + n,
             "host_phases": slot["phases"], "envs_per_gpu": n, "steps": steps,
             "prewarm_steps": prewarm, "ms_per_step": slot["ms"], "value_incl_policy_copy": slot["v_loop"], "policy_copy_d2h_bytes_per_step": slot["act"],
             "value_full_write": full["v"], "value_default_numpy": dflt["v"], "default_numpy_envs": n_dflt,

@@ -200,8 +200,8 @@ int mrts_host_expand_mask_delta(const uint32_t* mask_words, uint32_t* shadow, in
 int mrts_host_pack_actions_bitmap(const void* actions, int action_elem_bytes, const uint32_t* bitmap, int64_t cells, uint16_t* out);
 int mrts_host_patch_cells(const uint32_t* entries, int64_t count, int planes, int elem_bytes, void* obs, void* mask);
 int mrts_host_threads(const mrts_env* env); /* worker threads of the widening pool (0 before the first host call) */
-/* profiling aid: accumulated wall seconds of the host-buffer step calls {pack actions, copy + launch, wait for the device,
- * widen / patch, copy-out, changed cells, bytes device->host, calls}; reset != 0 clears them */
+/* profiling aid: accumulated over the host-buffer step calls {seconds packing actions, uploading + launching, waiting for the device,
+ * widening / patching + copying out; bytes host->device, changed cells, bytes device->host, calls}; reset != 0 clears them */
 int mrts_host_timing(mrts_env* env, double* out8, int reset);
 
 /* Introspection (synchronises the stream). */

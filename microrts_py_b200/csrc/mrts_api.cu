@@ -141,9 +141,14 @@ struct mrts_env {
         uint32_t *d_delta = nullptr, *h_delta = nullptr;
         size_t off_rew = 0, off_done = 0, off_bitmap = 0, off_entries = 0, delta_cap = 0;  // byte offsets; capacity in entries
         uint32_t* d_shadow[MRTS_HOST_SLOTS] = {nullptr};
+        // action rows go up as a list of the acting cells {flat cell, packed row} and are scattered on the device
+        uint32_t *h_pairs = nullptr, *d_pairs[2] = {nullptr, nullptr};
+        size_t pairs_cap = 0, pairs_prev_n = 0;
+        int pairs_cur = 0;
+        bool pact_clean = false;  // d_pact is zero except at the cells of d_pairs[pairs_cur]
         size_t last_count = 0;
         bool bitmap_valid = false;  // h_delta's bitmap describes the mask of the current state (else h_pmask does)
-        double t_phase[8] = {0};    // accumulated wall seconds: pack, launch, wait, patch / expand, copy-out; [5] = changed cells, [6] = bytes device->host, [7] = calls
+        double t_phase[8] = {0};    // accumulated wall seconds: pack, upload + launch, wait, patch / expand + copy-out; [4] = bytes host->device, [5] = changed cells, [6] = bytes device->host, [7] = calls
     } hio;
     const uint16_t* cur_pact = nullptr;  // per-launch packed pointers (set by the host / packed entry points)
     uint32_t *cur_pobs = nullptr, *cur_pmask = nullptr, *cur_ment = nullptr;
@@ -623,6 +628,9 @@ void mrts_destroy(mrts_env* e) {
         auto& h = e->hio;
         for (void* p : {(void*)h.h_pact, (void*)h.h_pobs, (void*)h.h_pmask, (void*)h.h_rew, (void*)h.h_done})
             if (p) cudaFreeHost(p);
+        if (h.h_pairs) cudaFreeHost(h.h_pairs);
+        for (uint32_t* p : h.d_pairs)
+            if (p) cudaFree(p);
         if (h.h_delta) cudaFreeHost(h.h_delta);
         if (h.d_delta) cudaFree(h.d_delta);
         for (uint32_t* p : h.d_shadow)
@@ -816,6 +824,12 @@ static int hostio_delta_init(mrts_env* e, int slot) {
         CK(cudaMemset(h.d_delta, 0, h.off_entries));
         memset(h.h_delta, 0, h.off_entries);
     }
+    if (!h.h_pairs) {
+        h.pairs_cap = cells / 8 > 65536 ? cells / 8 : 65536;
+        CK(cudaMallocHost((void**)&h.h_pairs, h.pairs_cap * 8));
+        CK(cudaMalloc((void**)&h.d_pairs[0], h.pairs_cap * 8));
+        CK(cudaMalloc((void**)&h.d_pairs[1], h.pairs_cap * 8));
+    }
     if (!h.d_shadow[slot]) CK(cudaMalloc((void**)&h.d_shadow[slot], cells * 16));
     return MRTS_OK;
 }
@@ -879,7 +893,7 @@ static int hostio_finish_slot(mrts_env* e, void* h_obs, void* h_mask, double* h_
     h.bitmap_valid = true;
     if (h_reward) memcpy(h_reward, hb + h.off_rew, N * 48);
     if (h_done) memcpy(h_done, hb + h.off_done, N);
-    h.t_phase[2] += t1 - t0, h.t_phase[3] += t2 - t1, h.t_phase[4] += now_s() - t2;
+    h.t_phase[2] += t1 - t0, h.t_phase[3] += now_s() - t1;
     return MRTS_OK;
 }
 
@@ -928,10 +942,35 @@ int mrts_step_host_slot(mrts_env* e, const void* h_actions, int action_elem_byte
     const bool slot_path = slot >= 0 && h_obs && h_mask;
     if (slot_path && (rc = hostio_delta_init(e, slot))) return rc;
     const double t0 = now_s();
-    if (h.bitmap_valid) mrts_host::pack_actions_bitmap(h.pool, h_actions, action_elem_bytes, (const uint32_t*)((const uint8_t*)h.h_delta + h.off_bitmap), N * HW, h.h_pact);
-    else mrts_host::pack_actions(h.pool, h_actions, action_elem_bytes, h.h_pmask, N, (int)HW, h.h_pact);
+    const uint32_t* const bitmap = (const uint32_t*)((const uint8_t*)h.h_delta + h.off_bitmap);
+    bool sparse = false;
+    size_t n_pairs = 0;
+    if (h.bitmap_valid && h.h_pairs && env_int("MRTS_HOST_SPARSE_ACTIONS", 1)) {
+        n_pairs = mrts_host::pack_actions_sparse(h.pool, h_actions, action_elem_bytes, bitmap, N * HW, h.h_pairs, h.pairs_cap);
+        sparse = n_pairs <= h.pairs_cap;
+    }
+    if (!sparse) {
+        if (h.bitmap_valid) mrts_host::pack_actions_bitmap(h.pool, h_actions, action_elem_bytes, bitmap, N * HW, h.h_pact);
+        else mrts_host::pack_actions(h.pool, h_actions, action_elem_bytes, h.h_pmask, N, (int)HW, h.h_pact);
+    }
     const double t1 = now_s();
-    CK(cudaMemcpyAsync(h.d_pact, h.h_pact, N * HW * 2, cudaMemcpyHostToDevice, h.stream));
+    if (sparse) {
+        // the cells of the previous list read as NOOP again (a row the reference never forwards), then this step's rows
+        if (!h.pact_clean) {
+            CK(cudaMemsetAsync(h.d_pact, 0, N * HW * 2, h.stream));
+            h.pact_clean = true;
+        } else {
+            CK(launch_scatter_actions(h.d_pairs[h.pairs_cur], (int)h.pairs_prev_n, h.d_pact, 1, h.stream));
+        }
+        h.pairs_cur ^= 1;
+        CK(cudaMemcpyAsync(h.d_pairs[h.pairs_cur], h.h_pairs, n_pairs * 8, cudaMemcpyHostToDevice, h.stream));
+        CK(launch_scatter_actions(h.d_pairs[h.pairs_cur], (int)n_pairs, h.d_pact, 0, h.stream));
+        h.pairs_prev_n = n_pairs;
+    } else {
+        CK(cudaMemcpyAsync(h.d_pact, h.h_pact, N * HW * 2, cudaMemcpyHostToDevice, h.stream));
+        h.pact_clean = false;
+        h.pairs_prev_n = 0;
+    }
     e->cur_pact = h.d_pact;
     e->cur_pobs = h.d_pobs;
     e->cur_pmask = h.d_pmask;
@@ -941,6 +980,7 @@ int mrts_step_host_slot(mrts_env* e, const void* h_actions, int action_elem_byte
     rc = launch(e, MODE_STEP, (const int32_t*)h.d_pact, nullptr, nullptr, d_rew, d_done, h.stream);
     if (rc) return rc;
     h.t_phase[0] += t1 - t0, h.t_phase[1] += now_s() - t1, h.t_phase[7] += 1;
+    h.t_phase[4] += sparse ? (double)(n_pairs * 8) : (double)(N * HW * 2);
     if (slot_path) return hostio_finish_slot(e, h_obs, h_mask, h_reward, h_done, slot);
     h.bitmap_valid = false;
     return hostio_finish(e, h_obs, h_mask, h_reward, h_done, slot);

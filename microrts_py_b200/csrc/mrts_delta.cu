@@ -70,7 +70,22 @@ __global__ void __launch_bounds__(DELTA_THREADS) mrts_delta_kernel(const DeltaPa
     }
 }
 
+// packed action rows of the acting cells, as a list -> the dense (N, HW) array the rules kernels read; `value` < 0: write zeros
+// (the cells of the previous step's list: a cell that no longer acts must read as NOOP, like a row the reference never forwards)
+__global__ void __launch_bounds__(256) mrts_scatter_actions_kernel(const uint2* __restrict__ pairs, int n, uint16_t* __restrict__ pact, int clear) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const uint2 pr = __ldg(pairs + i);
+    pact[pr.x] = clear ? (uint16_t)0 : (uint16_t)pr.y;
+}
+
 }  // namespace
+
+cudaError_t launch_scatter_actions(const uint32_t* pairs, int n, uint16_t* pact, int clear, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    mrts_scatter_actions_kernel<<<(n + 255) / 256, 256, 0, st>>>((const uint2*)pairs, n, pact, clear);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_delta(const DeltaParams& D, int n_sm, cudaStream_t st) {
     long long blocks = (D.cells + DELTA_THREADS - 1) / DELTA_THREADS;

@@ -481,6 +481,43 @@ void pack_actions_bitmap(Pool* p, const void* actions, int action_elem, const ui
     });
 }
 
+size_t pack_actions_sparse(Pool* p, const void* actions, int action_elem, const uint32_t* bitmap, size_t cells, uint32_t* pairs, size_t cap) {
+    const size_t nwords = (cells + 31) / 32;
+    std::atomic<size_t> cursor{0};
+    std::atomic<size_t>* cur = &cursor;
+    parallel_for(p, nwords, [=](size_t b, size_t e) {
+        constexpr int BATCH = 64;
+        size_t idx[BATCH + 32];
+        const size_t row_bytes = (size_t)7 * action_elem;
+        size_t i = b;
+        while (i < e) {
+            int k = 0;
+            while (i < e && k < BATCH) {
+                uint32_t bits = bitmap[i];
+                while (bits) {
+                    const size_t g = i * 32 + (size_t)__builtin_ctz(bits);
+                    bits &= bits - 1;
+                    if (g < cells) idx[k++] = g;
+                }
+                i++;
+            }
+            if (k == 0) continue;
+            for (int j = 0; j < k; j++) {
+                const char* row = (const char*)actions + idx[j] * row_bytes;
+                __builtin_prefetch(row, 0, 0);
+                __builtin_prefetch(row + row_bytes - 1, 0, 0);
+            }
+            const size_t at = cur->fetch_add((size_t)k);  // a run of k slots of the list (the order of the list is irrelevant)
+            for (int j = 0; j < k; j++) {
+                const size_t g = idx[j];
+                const uint32_t v = action_elem == 8 ? pack_row((const int64_t*)actions + g * 7) : pack_row((const int32_t*)actions + g * 7);
+                if (at + j < cap) pairs[2 * (at + j)] = (uint32_t)g, pairs[2 * (at + j) + 1] = v;
+            }
+        }
+    });
+    return cursor.load();
+}
+
 void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int elem, void* obs, void* mask) {
     parallel_for(p, count, [=](size_t b, size_t e) {
         const size_t obs_cell_bytes = (size_t)planes * elem, mask_cell_bytes = (size_t)78 * elem;

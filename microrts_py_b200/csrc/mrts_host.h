@@ -38,6 +38,9 @@ void pack_actions(Pool* p, const void* actions, int action_elem /* 4 or 8 */, co
 // The same with the source cells given as a bitmap over the flat cell index (bit = mask bit 0, mrts_delta.cu): only the
 // rows of set bits are read and only those cells of `out` are written (the device reads no other cell).
 void pack_actions_bitmap(Pool* p, const void* actions, int action_elem, const uint32_t* bitmap, size_t cells, uint16_t* out);
+// The same as a list: pairs (n, 2) {flat cell, packed row} of the set cells, in any order; returns n (pairs beyond `cap` are
+// not written: the caller then falls back to the dense form).  ~4 acting cells per env instead of H*W 16-bit codes cross PCIe.
+size_t pack_actions_sparse(Pool* p, const void* actions, int action_elem, const uint32_t* bitmap, size_t cells, uint32_t* pairs, size_t cap);
 // entries (count, 6) {flat cell, obs word, mask words 0..2, span} -> those cells of obs (cells, planes) and mask (cells, 78).
 // span = first | last << 5 changed plane of the cell's observation row, first << 10 | last << 17 changed entry of its mask
 // row (mrts_delta.cu): only those ranges are rewritten -- usually one cache line per tensor instead of the rows' two to six,

@@ -74,5 +74,7 @@ struct DeltaParams {
     int init;               // 1 = only fill the shadow and the bitmap (the host expands the whole arrays this time)
 };
 cudaError_t launch_delta(const DeltaParams& D, int n_sm, cudaStream_t st);
+// (n, 2) {flat cell, packed row} -> pact[cell] (clear != 0: zeros instead)
+cudaError_t launch_scatter_actions(const uint32_t* pairs, int n, uint16_t* pact, int clear, cudaStream_t st);
 
 }  // namespace mrts
