@@ -199,6 +199,8 @@ int mrts_host_expand_mask_delta(const uint32_t* mask_words, uint32_t* shadow, in
  * span = first | last << 5 changed observation plane, first << 10 | last << 17 changed mask entry (first > last: row unchanged) */
 int mrts_host_pack_actions_bitmap(const void* actions, int action_elem_bytes, const uint32_t* bitmap, int64_t cells, uint16_t* out);
 int mrts_host_patch_cells(const uint32_t* entries, int64_t count, int planes, int elem_bytes, void* obs, void* mask);
+/* the action rows of the set cells as a list: pairs (n, 2) {flat cell, packed row}, any order; *n_pairs = n (pairs beyond `cap` are not written) */
+int mrts_host_pack_actions_sparse(const void* actions, int action_elem_bytes, const uint32_t* bitmap, int64_t cells, uint32_t* pairs, int64_t cap, int64_t* n_pairs);
 int mrts_host_threads(const mrts_env* env); /* worker threads of the widening pool (0 before the first host call) */
 /* profiling aid: accumulated over the host-buffer step calls {seconds packing actions, uploading + launching, waiting for the device,
  * widening / patching + copying out; bytes host->device, changed cells, bytes device->host, calls}; reset != 0 clears them */

@@ -216,6 +216,7 @@ SYMBOLS = [
     "mrts_host_timing",
     "mrts_host_pack_actions_bitmap",
     "mrts_host_patch_cells",
+    "mrts_host_pack_actions_sparse",
     "mrts_pipeline",
     "mrts_chunks",
     "mrts_kernel_info",
@@ -274,6 +275,7 @@ def lib():
         L.mrts_host_timing.argtypes = [vp, vp, C.c_int]
         L.mrts_host_pack_actions_bitmap.argtypes = [vp, C.c_int, vp, C.c_int64, vp]
         L.mrts_host_patch_cells.argtypes = [vp, C.c_int64, C.c_int, C.c_int, vp, vp]
+        L.mrts_host_pack_actions_sparse.argtypes = [vp, C.c_int, vp, C.c_int64, vp, C.c_int64, C.POINTER(C.c_int64)]
         L.mrts_host_expand_obs.argtypes = [vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]
         L.mrts_host_expand_mask.argtypes = [vp, C.c_int64, C.c_int, C.c_int, vp]
         L.mrts_host_pack_actions.argtypes = [vp, C.c_int, vp, C.c_int64, C.c_int, vp]

@@ -11,6 +11,7 @@
 #include <condition_variable>
 #include <functional>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -589,3 +590,17 @@ void patch_cells(Pool* p, const uint32_t* entries, size_t count, int planes, int
 }
 
 }  // namespace mrts_host
+
+// the list form of the action packer on its own, for the CPU test-suite (declared in include/mrts_b200.h with the other codec entry points)
+namespace mrts {
+int api_fail(int code, const std::string& msg);  // mrts_api.cu
+}
+extern "C" int mrts_host_pack_actions_sparse(const void* actions, int action_elem_bytes, const uint32_t* bitmap, int64_t cells, uint32_t* pairs, int64_t cap,
+                                             int64_t* n_pairs) {
+    if (!actions || !bitmap || !pairs || !n_pairs || cells < 0 || cap < 0 || (action_elem_bytes != 4 && action_elem_bytes != 8))
+        return mrts::api_fail(-1, "bad argument");
+    mrts_host::Pool* p = mrts_host::pool_create(0);
+    *n_pairs = (int64_t)mrts_host::pack_actions_sparse(p, actions, action_elem_bytes, bitmap, (size_t)cells, pairs, (size_t)cap);
+    mrts_host::pool_destroy(p);
+    return 0;
+}

@@ -72,7 +72,7 @@ static void pass(hs_env* e, int mode, const int32_t* actions, void* obs, void* m
         }
     };
     for (int g = 0; g < P.n_games; g++) one(P, g);
-    if (rotate) {  // same rule as mrts_cycle_kernel + the reset launch (mrts_kernels.cu)
+    if (rotate) {  // same rule as mrts_cycle_kernel + the reset launch (mrts_api.cu)
         EnvParams R = P;
         R.mode = MODE_RESET;
         R.actions = nullptr;

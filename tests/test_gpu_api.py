@@ -211,8 +211,8 @@ def test_games_outgrowing_the_staged_capacity_take_the_full_capacity_launch(stag
 
 
 def test_large_bot_slab_with_launch_ordering_matches_oracle():
-    """Slabs of >= 2048 scripted-bot games are launched slowest class first (mrts_order_kernel maps
-    launch slots to games).  The permutation must not change any result: a subsample of a 4,096-env
+    """Scripted-bot games are launched slowest class first (the pass appends every heavy game to one of four class lists
+    for the next step, double-buffered; slot_game maps launch slots to games).  The permutation must not change any result: a subsample of a 4,096-env
     slab equals the oracle step by step, and every game is processed exactly once per step (the
     per-env step counters advance together: all dones fire on the same max_steps frame)."""
     import torch

@@ -133,6 +133,33 @@ def test_action_rows_pack_by_bitmap_touch_only_set_cells(dtype):
     np.testing.assert_array_equal(out, want)
 
 
+@pytest.mark.parametrize("dtype", [np.int32, np.int64])
+def test_action_rows_pack_into_a_list_of_the_set_cells(dtype):
+    """what the slot calls upload: {flat cell, packed row} of every set cell, each once, in any order; a short list is refused"""
+    L = _capi.lib()
+    rng = np.random.default_rng(13)
+    cells = 50 * 64 + 11
+    a = rng.integers(-2, 9, size=(cells, 7)).astype(dtype)
+    a[:, 6] = rng.integers(-3, 60, size=cells)
+    src = rng.random(cells) < 0.15
+    bits = np.zeros((cells + 31) // 32 * 32, np.uint8)
+    bits[:cells] = src
+    bitmap = np.packbits(bits.reshape(-1, 32), axis=1, bitorder="little").view(np.uint32).reshape(-1)
+    n_src = int(src.sum())
+    pairs = np.zeros((n_src + 5, 2), np.uint32)
+    n = C.c_int64(0)
+    _capi.check(L.mrts_host_pack_actions_sparse(_p(a), np.dtype(dtype).itemsize, _p(bitmap), cells, _p(pairs), len(pairs), C.byref(n)))
+    assert n.value == n_src
+    got = pairs[: n.value]
+    order = np.argsort(got[:, 0])
+    np.testing.assert_array_equal(got[order, 0], np.nonzero(src)[0])
+    np.testing.assert_array_equal(got[order, 1], [_pack_ref(a[c]) for c in np.nonzero(src)[0]])
+    assert not pairs[n.value:].any()
+    short = np.zeros((10, 2), np.uint32)
+    _capi.check(L.mrts_host_pack_actions_sparse(_p(a), np.dtype(dtype).itemsize, _p(bitmap), cells, _p(short), len(short), C.byref(n)))
+    assert n.value == n_src > len(short)  # the caller sees that the list did not fit and uses the dense form
+
+
 @pytest.mark.parametrize("planes,dtype", [(29, np.int32), (31, np.int32), (29, np.uint8), (31, np.uint8)])
 def test_entries_patch_exactly_the_changed_range_of_their_cells(planes, dtype):
     """entries as mrts_delta_kernel emits them: new words + the first / last changed element per row; the arrays hold the

@@ -47,7 +47,7 @@ def line_table(kernel):
 
 def main():
     path = sys.argv[1]
-    kernel = sys.argv[2] if len(sys.argv) > 2 else "mrts_pass_kernel"
+    kernel = sys.argv[2] if len(sys.argv) > 2 else "mrts_rules_warp_kernel"
     top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
     table = line_table(kernel)
     rows = list(csv.reader(open(path)))
