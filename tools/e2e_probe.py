@@ -65,3 +65,9 @@ calls = max(ph[7], 1)
 names = ["pack actions", "h2d + launch", "wait device", "patch + copy-out"]
 print("  inside mrts_step_host_slot (%d threads): " % env._lib.mrts_host_threads(env._h) + " | ".join(f"{k} {1e3 * ph[i] / calls:.3f} ms" for i, k in enumerate(names))
       + f" | {ph[5] / calls / n:.2f} changed cells/env, {ph[6] / calls / 1e6:.2f} MB d2h, {ph[4] / calls / 1e6:.2f} MB h2d" + f" | inside the C call {1e3 * lib_s[0] / K:.3f} ms" + f" | env.step total {1e3 * T['step'] / K:.3f} ms = {n * K / T['step'] / 1e6:.2f} M env-steps/s")
+try:
+    roll = dict(l.split(":") for l in open("/proc/self/smaps_rollup").read().splitlines()[1:] if ":" in l)
+    print("  process memory: AnonHugePages", roll.get("AnonHugePages", "?").strip(), "of Anonymous", roll.get("Anonymous", "?").strip(),
+          "| THP", open("/sys/kernel/mm/transparent_hugepage/enabled").read().strip(), "defrag", open("/sys/kernel/mm/transparent_hugepage/defrag").read().strip())
+except Exception as ex:  # noqa: BLE001
+    print("  (no smaps_rollup:", ex, ")")
