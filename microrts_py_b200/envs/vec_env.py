@@ -19,8 +19,9 @@ Extra keyword-only arguments (all default to the reference's behaviour):
                 mrts_step_host): results cross PCIe as one bit per element and are widened into the
                 NumPy arrays by the library's thread pool; same values, shapes and dtypes.  Arrays are
                 two alternating buffers per output (as with ``zero_copy``), handed out READ-ONLY: the
-                library remembers what each buffer holds and rewrites only the cells that changed
-                (mrts_*_host_slot), so they must come back unmodified -- copy before editing
+                library remembers (in HBM) what each buffer holds, a kernel finds the cells that changed and only
+                those cross PCIe and are rewritten (mrts_*_host_slot), so the buffers must come back unmodified --
+                copy before editing
   ai1s          scripted player 0 per bot env (``microrts_ai`` factories, ``None`` = the agent): bot vs bot as in
                 the reference's JNIBotClient; the action rows of those envs are ignored
   fuse_mask     compute the action mask of the resulting state inside ``step`` (one launch,
